@@ -1,0 +1,248 @@
+/*
+ * swgpu.h — C ABI of libswgpu.so, the B200 (sm_100a) implementation of SiteWhere's
+ * inbound event hot path: payload decode -> geofence zone test -> device-state merge.
+ *
+ * This is the boundary a JNI / Panama binding in a `sitewhere-gpu` Java module binds to
+ * (see INTEGRATION.md).  Plain pointers and sizes only; no C++ or torch types.
+ *
+ * Reference paths below are relative to the SiteWhere 2.0.rc2 tree (waffcloud/sitewhere):
+ *   ES/ = service-event-sources/src/main/java/com/sitewhere/sources/
+ *   RP/ = service-rule-processing/src/main/java/com/sitewhere/rules/
+ *   DS/ = service-device-state/src/main/java/com/sitewhere/devicestate/
+ *   MS/ = sitewhere-microservice/src/main/java/com/sitewhere/microservice/
+ *
+ * Conventions
+ *   - every function returns int32_t: 0 = ok, <0 = call-level error (text: swgpu_last_error).
+ *   - a bad RECORD never fails a call: each record gets a status byte (SWGPU_ST_*), mirroring
+ *     the reference's per-record try/catch (ES/InboundEventSource.java:208-215,
+ *     DS/processing/DeviceStateProcessingLogic.java:75-85).
+ *   - "_dev" entry points take DEVICE pointers, enqueue on the context's stream and do not
+ *     synchronise; the others take HOST pointers, copy in/out and return when results are
+ *     in the caller's buffers.
+ *   - there is no CPU implementation behind this ABI: without a CUDA device every call fails.
+ */
+#ifndef SWGPU_H
+#define SWGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SWGPU_ABI_VERSION 1
+
+/* ---- call-level error codes ------------------------------------------------------------ */
+#define SWGPU_OK 0
+#define SWGPU_E_INVALID (-1)  /* bad argument */
+#define SWGPU_E_CUDA (-2)     /* CUDA runtime error (text has the CUDA error string) */
+#define SWGPU_E_NOMEM (-3)    /* allocation failed */
+#define SWGPU_E_CAPACITY (-4) /* an output did not fit the caller's capacity; counts are valid */
+#define SWGPU_E_STATE (-5)    /* call not valid in this state (e.g. zone test before set_zones) */
+
+/* ---- per-record decode status (uint8) --------------------------------------------------- */
+/* 0: decoded, rows written.                                                                  */
+#define SWGPU_ST_OK 0
+/* 1: the reference throws EventDecodeException (JsonParseException / JsonMappingException /
+ *    IOException in ES/decoder/json/JsonDeviceRequestDecoder.java:55-61; IOException incl.
+ *    InvalidProtocolBufferException in ES/decoder/protobuf/ProtobufDeviceEventDecoder.java:301-303)
+ *    -> the record goes to the failed-decode topic (ES/InboundEventSource.java:211-213).       */
+#define SWGPU_ST_DECODE_EXCEPTION 1
+/* 2: the reference throws an unchecked exception that is NOT routed to the failed-decode
+ *    topic (NullPointerException when parseDelimitedFrom returns null on an exhausted stream,
+ *    ProtobufDeviceEventDecoder.java:79-81,124,160,194).                                        */
+#define SWGPU_ST_RUNTIME_EXCEPTION 2
+/* 3: valid envelope of a non-event request (registration, acknowledge, stream ...): outside the
+ *    measured path; the binding hands the raw record to the stock decoder.                      */
+#define SWGPU_ST_PASSTHROUGH 3
+
+/* ---- decoded row: `kind` (low byte of meta) ------------------------------------------------ */
+/* numbering = com.sitewhere.spi.device.event.DeviceEventType ordinals                          */
+#define SWGPU_KIND_MEASUREMENT 0
+#define SWGPU_KIND_LOCATION 1
+#define SWGPU_KIND_ALERT 2
+
+/* meta word:  bits 0-7 kind | 8-23 flags | 24-25 alert level | 26 alert source |
+ *             27 eventType present | 28-30 eventType ordinal | 32-63 source record index      */
+#define SWGPU_META_KIND(m) ((uint32_t)((m) & 0xff))
+#define SWGPU_META_FLAGS(m) ((uint32_t)(((m) >> 8) & 0xffff))
+#define SWGPU_META_LEVEL(m) ((uint32_t)(((m) >> 24) & 0x3))
+#define SWGPU_META_SOURCE(m) ((uint32_t)(((m) >> 26) & 0x1))
+#define SWGPU_META_HAS_ETYPE(m) ((uint32_t)(((m) >> 27) & 0x1))
+#define SWGPU_META_ETYPE(m) ((uint32_t)(((m) >> 28) & 0x7))
+#define SWGPU_META_REC(m) ((uint32_t)((m) >> 32))
+
+#define SWGPU_F_UPDATE_STATE (1u << 0)  /* request.updateState                                 */
+#define SWGPU_F_HAS_DATE (1u << 1)      /* event_date valid; else reference uses null / now()  */
+#define SWGPU_F_HAS_ORIGINATOR (1u << 2)
+#define SWGPU_F_HAS_METADATA (1u << 3)
+#define SWGPU_F_HAS_ALT_ID (1u << 4)
+#define SWGPU_F_NULL_TOKEN (1u << 5)    /* JSON deviceToken was not a string -> null token     */
+#define SWGPU_F_HAS_V0 (1u << 6)        /* value / latitude  is non-null                       */
+#define SWGPU_F_HAS_V1 (1u << 7)        /* longitude is non-null                               */
+#define SWGPU_F_HAS_V2 (1u << 8)        /* elevation is non-null                               */
+#define SWGPU_F_STR_ESCAPED (1u << 9)   /* some JSON string span holds backslash escapes       */
+#define SWGPU_F_HAS_NAME (1u << 10)     /* measurement name / alert type is non-null           */
+#define SWGPU_F_HAS_MESSAGE (1u << 11)  /* alert message is non-null                           */
+#define SWGPU_F_NAME_COERCED (1u << 12) /* JSON name/type/message given as number/bool token   */
+
+/* A span is  (offset_in_record | length << 32); bytes are the caller's payload bytes.        */
+#define SWGPU_SPAN_OFF(s) ((uint32_t)((s) & 0xffffffffu))
+#define SWGPU_SPAN_LEN(s) ((uint32_t)((s) >> 32))
+
+/*
+ * Decoded rows, structure-of-arrays, one element per DECODED EVENT (not per record: a protobuf
+ * DeviceMeasurements message yields one row per Measurement, ProtobufDeviceEventDecoder.java:126-157;
+ * a failed record yields none).  Rows are in reference order: record order, then the order in
+ * which the reference appends to its result list.  The first nine columns are mandatory (72 B
+ * per row); the last four may be NULL.
+ *
+ * This is the columnar form of ES/DecodedDeviceRequest.java:17-29 + the request POJOs
+ * (sitewhere-core-api/.../rest/model/device/event/request/Device{Event,Measurement,Location,
+ * Alert}CreateRequest.java).
+ */
+typedef struct swgpu_decoded_cols {
+    uint64_t *meta;        /* see SWGPU_META_*                                               */
+    uint64_t *token_hash;  /* low 32: Kafka murmur2(token bytes); high 32: second hash        */
+    uint64_t *name_hash;   /* same hash of measurement name / alert type (0 if none)          */
+    int64_t *event_date;   /* ms since epoch (valid iff SWGPU_F_HAS_DATE)                      */
+    double *v0;            /* measurement value | latitude                                    */
+    double *v1;            /* longitude                                                       */
+    double *v2;            /* elevation                                                       */
+    uint64_t *token_span;  /* deviceToken / hardwareId bytes                                  */
+    uint64_t *name_span;   /* measurement name / alert type bytes                             */
+    uint64_t *originator_span;   /* optional */
+    uint64_t *message_span;      /* optional: alert message */
+    uint64_t *metadata_span;     /* optional: JSON: text of the metadata object; protobuf:
+                                    offset of first Metadata field | entry count << 32 */
+    uint64_t *alternate_id_span; /* optional (JSON only) */
+} swgpu_decoded_cols;
+
+typedef struct swgpu_ctx swgpu_ctx;
+
+/* ---- context ---------------------------------------------------------------------------- */
+/* One context per GPU and per calling thread.  `stream` is a cudaStream_t to enqueue on, or
+ * NULL to let the library create its own non-blocking stream.                                 */
+int32_t swgpu_create(int32_t device_ordinal, void *stream, swgpu_ctx **out_ctx);
+void swgpu_destroy(swgpu_ctx *ctx);
+const char *swgpu_last_error(swgpu_ctx *ctx); /* ctx may be NULL: error of the last failed create */
+int32_t swgpu_abi_version(void);
+void *swgpu_stream(swgpu_ctx *ctx);
+int32_t swgpu_sync(swgpu_ctx *ctx);
+/* Pinned host staging the Java side wraps as a direct ByteBuffer / MemorySegment.             */
+void *swgpu_alloc_pinned(size_t bytes);
+void swgpu_free_pinned(void *p);
+
+/* ---- zone table --------------------------------------------------------------------------
+ * Replaces the per-token polygon cache of RP/processors/geospatial/ZoneTestRuleProcessor.java:36,72-84
+ * and GeoUtils.createPolygonForLocations (sitewhere-core/.../geospatial/GeoUtils.java:55-67).
+ * Test t uses bounds[vtx_off[t] .. vtx_off[t+1]) as the OPEN ring in zone order (x = longitude,
+ * y = latitude); the library closes it with the first vertex as GeoUtils does.  cond[t] is
+ * ZoneContainment: 0 = Inside, 1 = Outside (RP/processors/geospatial/ZoneTest.java:25).
+ * Host pointers.  Rebuilds the device table and its spatial index; call on configuration change. */
+int32_t swgpu_set_zones(swgpu_ctx *ctx, uint32_t n_tests, const uint32_t *vtx_off,
+                        const double *lon, const double *lat, const uint8_t *cond);
+/* Packed table (one relocatable blob) for replication to other GPUs: export on the rank that
+ * built it, ncclBroadcast the bytes, import on the others.  Device pointers.                   */
+int32_t swgpu_zone_table_bytes(swgpu_ctx *ctx, uint64_t *out_bytes);
+int32_t swgpu_zone_table_export_dev(swgpu_ctx *ctx, void *dst_dev, uint64_t capacity);
+int32_t swgpu_zone_table_import_dev(swgpu_ctx *ctx, const void *src_dev, uint64_t bytes);
+
+/* ---- decode -------------------------------------------------------------------------------
+ * n records; record i is bytes[rec_off[i] .. rec_off[i+1]).  status[i] = SWGPU_ST_*;
+ * first_row[i] = index of record i's first row (rows of record i are first_row[i] ..
+ * first_row[i+1]); first_row has n+1 entries and first_row[n] = total rows.
+ * Rows beyond max_rows are counted but not written and the call returns SWGPU_E_CAPACITY.
+ *
+ * swgpu_decode_pb   replaces ProtobufDeviceEventDecoder.decode(byte[], Map)
+ *                   (ES/decoder/protobuf/ProtobufDeviceEventDecoder.java:75-304) applied to each record.
+ * swgpu_decode_json replaces JsonDeviceRequestDecoder.decode(byte[], Map)
+ *                   (ES/decoder/json/JsonDeviceRequestDecoder.java:48-62 with
+ *                   JsonDeviceRequestMarshaler.java:57-160) applied to each record.
+ * Both implement IDeviceEventDecoder<byte[]>.decode (ES/spi/IDeviceEventDecoder.java:39).       */
+int32_t swgpu_decode_pb(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
+                        uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
+                        uint32_t *first_row, uint32_t *out_rows);
+int32_t swgpu_decode_json(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
+                          uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
+                          uint32_t *first_row, uint32_t *out_rows);
+/* Device-resident variants.  `bytes` must be readable up to rec_off[n] rounded up to 16.
+ * out_rows_dev: one uint32 on the device.                                                       */
+int32_t swgpu_decode_pb_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
+                            uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
+                            uint32_t *first_row, uint32_t *out_rows_dev);
+int32_t swgpu_decode_json_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off,
+                              uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out,
+                              uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev);
+
+/* ---- zone test ------------------------------------------------------------------------------
+ * Replaces ZoneTestRuleProcessor.onLocation (RP/processors/geospatial/ZoneTestRuleProcessor.java:47-63)
+ * applied to each location: for each test t in list order, inside = JTS-1.13
+ * Polygon.contains(Point(lon,lat)); an alert fires iff (cond[t] == Inside) == inside.
+ * Output: pairs (location index << 32 | test index), ordered by location then test — the order
+ * in which the reference calls addDeviceAlerts.  *n_pairs gets the total count even when it
+ * exceeds max_pairs (then SWGPU_E_CAPACITY).  `meta` may be NULL; if given, rows whose kind is
+ * not SWGPU_KIND_LOCATION or that lack latitude/longitude are skipped (the reference only routes
+ * Location events to onLocation, RP/kafka/KafkaRuleProcessorHost.java:205-237).                  */
+int32_t swgpu_zone_test(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta,
+                        uint32_t n, uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs);
+/* Device variant: n_rows_dev (may be NULL -> use n) holds the live row count (<= n), as written
+ * by a *_dev decode; n_pairs_dev is one uint64 on the device.                                    */
+int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const double *lat,
+                            const uint64_t *meta, uint32_t n, const uint32_t *n_rows_dev,
+                            uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev);
+
+/* ---- device-state merge -------------------------------------------------------------------------
+ * Replaces the fold DeviceStateProcessingLogic.processDeviceStateEvent + merge*
+ * (DS/processing/DeviceStateProcessingLogic.java:116-201) with DeviceStatePersistence.deviceStateUpdateLogic
+ * (DS/persistence/DeviceStatePersistence.java:60-85) over a batch, behind
+ * IDeviceStateProcessingLogic.process(List<ConsumerRecord>) (DS/spi/processing/IDeviceStateProcessingLogic.java:30).
+ *
+ * State key = (device token bytes, kind, name bytes) where name is the measurement name, the
+ * alert type, or empty for a location (lastLocationEventId / lastMeasurementEventIds[name] /
+ * lastAlertEventIds[type]).  Per key the winner is the event with the largest sequence number
+ * seq_base + row (arrival order, as the reference's sequential loop).  The table keeps, per key,
+ * the winner's sequence, 128-bit event id, event date and value.  Keys are compared by BYTES
+ * (hashes only pick the bucket).
+ *
+ * rows come from a decode call on the same `bytes`/`rec_off`; id_hi/id_lo are the event ids the
+ * persistence layer assigned (EM/persistence/DeviceEventManagementPersistence.java:82).           */
+int32_t swgpu_state_reserve(swgpu_ctx *ctx, uint64_t max_keys, uint64_t max_key_bytes);
+int32_t swgpu_merge(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n_records,
+                    const swgpu_decoded_cols *rows, uint32_t n_rows, uint64_t seq_base,
+                    const uint64_t *id_hi, const uint64_t *id_lo);
+int32_t swgpu_merge_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off,
+                        uint32_t n_records, const swgpu_decoded_cols *rows, uint32_t n_rows,
+                        const uint32_t *n_rows_dev, uint64_t seq_base, const uint64_t *id_hi,
+                        const uint64_t *id_lo);
+/* Number of live keys and bytes in the key arena.                                             */
+int32_t swgpu_state_size(swgpu_ctx *ctx, uint64_t *n_keys, uint64_t *key_bytes);
+/* Snapshot (host pointers): one row per live key, in unspecified order.  key_off has n_keys+1
+ * entries into key_bytes; a key is  token length (2 bytes LE) | kind byte | token bytes | name bytes.               */
+typedef struct swgpu_state_rows {
+    uint64_t *seq;
+    uint64_t *id_hi;
+    uint64_t *id_lo;
+    int64_t *event_date;
+    double *value;
+    uint64_t *key_off;
+    uint8_t *key_bytes;
+} swgpu_state_rows;
+int32_t swgpu_state_snapshot(swgpu_ctx *ctx, uint64_t max_keys, uint64_t max_key_bytes,
+                             const swgpu_state_rows *out, uint64_t *n_keys);
+int32_t swgpu_state_restore(swgpu_ctx *ctx, const swgpu_state_rows *in, uint64_t n_keys);
+int32_t swgpu_state_clear(swgpu_ctx *ctx);
+
+/* ---- partitioning ----------------------------------------------------------------------------
+ * Kafka DefaultPartitioner for keyed records, which the reference relies on by sending
+ * (key = deviceToken) without a partition (MS/kafka/MicroserviceKafkaProducer.java:89-92,
+ * ES/EventSourcesManager.java:163):  toPositive(murmur2(utf8(key))) % n_partitions.
+ * Host helper (no GPU): the shard a token belongs to.                                          */
+uint32_t swgpu_murmur2(const uint8_t *key, uint32_t len);
+uint32_t swgpu_partition(const uint8_t *key, uint32_t len, uint32_t n_partitions);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SWGPU_H */

@@ -1,0 +1,583 @@
+// decode_pb.cu — batched ProtobufDeviceEventDecoder.decode
+// (reference: service-event-sources/src/main/java/com/sitewhere/sources/decoder/protobuf/
+//  ProtobufDeviceEventDecoder.java:75-304; schema sitewhere-communication/src/main/proto/sitewhere.proto).
+//
+// One CTA decodes a tile of 256 consecutive records.  The tile's byte range is contiguous in the
+// batch buffer, so it is staged into shared memory with coalesced 16-byte streaming loads; each
+// thread then walks its own record out of shared memory (proto2 wire format, protobuf-java lite
+// semantics), and rows are written to the SoA columns at positions given by a single-pass ordered
+// scan (decoupled look-back), so output order is the reference's order with no second pass over
+// the payload.  HBM traffic = payload once + offsets + columns: the kernel is HBM-bound.
+#include "swgpu_common.cuh"
+
+#define PB_THREADS 256
+#define PB_STAGE (40 * 1024)  // bytes of payload staged per tile (avg record may be up to 160 B)
+#define PB_MAX_GROUP_DEPTH 16
+
+struct PbArgs {
+    const uint8_t *bytes;
+    const uint64_t *rec_off;
+    uint32_t n;
+    uint32_t max_rows;
+    swgpu_decoded_cols cols;
+    uint8_t *status;
+    uint32_t *first_row;
+    uint32_t *out_rows;
+    uint32_t *ticket;
+    uint64_t *tile_state;
+};
+
+template <typename B>
+struct PbReader {
+    B b;
+    uint32_t pos, end, limit;
+    uint32_t last_tag;
+    bool err;
+
+    __device__ __forceinline__ bool at_end() const { return pos >= end || pos >= limit; }
+    __device__ __forceinline__ uint32_t take() {
+        if (at_end()) {
+            err = true;  // truncatedMessage
+            return 0;
+        }
+        return b.byte(pos++);
+    }
+    __device__ __forceinline__ uint64_t varint64() {
+        uint64_t v = 0;
+#pragma unroll 1
+        for (int shift = 0; shift < 64; shift += 7) {
+            uint32_t c = take();
+            if (err) return 0;
+            v |= (uint64_t)(c & 0x7f) << shift;
+            if (!(c & 0x80)) return v;
+        }
+        err = true;  // malformedVarint
+        return 0;
+    }
+    __device__ __forceinline__ uint32_t varint32() { return (uint32_t)varint64(); }
+    __device__ __forceinline__ void skip(uint32_t n) {
+        uint32_t lim = end < limit ? end : limit;
+        if (n > lim - pos) {
+            pos = lim;
+            err = true;
+            return;
+        }
+        pos += n;
+    }
+    __device__ __forceinline__ uint64_t fixed64() {
+        uint32_t lim = end < limit ? end : limit;
+        if (lim - pos < 8) {
+            pos = lim;
+            err = true;
+            return 0;
+        }
+        uint64_t v = b.le64(pos);
+        pos += 8;
+        return v;
+    }
+    // readString / readBytes: span of the payload
+    __device__ __forceinline__ void lenfield(uint32_t &off, uint32_t &len) {
+        int32_t size = (int32_t)varint32();
+        off = 0;
+        len = 0;
+        if (err) return;
+        if (size < 0) {
+            err = true;  // negativeSize
+            return;
+        }
+        uint32_t start = pos;
+        skip((uint32_t)size);
+        if (err) return;
+        off = start;
+        len = (uint32_t)size;
+    }
+    __device__ __forceinline__ uint32_t read_tag() {
+        if (at_end()) {
+            last_tag = 0;
+            return 0;
+        }
+        uint32_t t = varint32();
+        if (err) return 0;
+        last_tag = t;
+        if ((t >> 3) == 0) {
+            err = true;  // invalidTag
+            return 0;
+        }
+        return t;
+    }
+    __device__ __forceinline__ void skip_scalar(uint32_t wt) {
+        uint32_t o, l;
+        switch (wt) {
+        case 0: varint64(); break;
+        case 1: skip(8); break;
+        case 2: lenfield(o, l); break;
+        case 5: skip(4); break;
+        default: err = true;  // invalidWireType (6, 7)
+        }
+    }
+    // generated-code default branch (GeneratedMessageLite.parseUnknownField +
+    // UnknownFieldSetLite.mergeFieldFrom); false = END_GROUP, the message stops here.
+    __device__ bool unknown(uint32_t tag) {
+        uint32_t wt = tag & 7;
+        if (wt == 4) return false;
+        if (wt != 3) {
+            skip_scalar(wt);
+            return true;
+        }
+        uint32_t stack[PB_MAX_GROUP_DEPTH];
+        int depth = 1;
+        stack[0] = tag >> 3;
+        while (depth > 0 && !err) {
+            uint32_t t = read_tag();
+            if (err) break;
+            if (t == 0) {  // input ended inside the group: checkLastTagWas(END_GROUP) fails
+                err = true;
+                break;
+            }
+            uint32_t w = t & 7;
+            if (w == 4) {
+                if (t != ((stack[depth - 1] << 3) | 4)) err = true;
+                depth--;
+            } else if (w == 3) {
+                if (depth >= PB_MAX_GROUP_DEPTH)
+                    err = true;
+                else
+                    stack[depth++] = t >> 3;
+            } else {
+                skip_scalar(w);
+            }
+        }
+        return true;
+    }
+    // readMessage prologue: length + pushLimit.  Returns the old limit.
+    __device__ __forceinline__ uint32_t push_message() {
+        int32_t length = (int32_t)varint32();
+        uint32_t old = limit;
+        if (err) return old;
+        if (length < 0) {
+            err = true;
+            return old;
+        }
+        uint64_t nl = (uint64_t)pos + (uint32_t)length;
+        if (nl > old) {
+            err = true;
+            return old;
+        }
+        limit = (uint32_t)nl;
+        return old;
+    }
+    // Model.Metadata { required string name = 1; required string value = 2; }
+    __device__ void metadata_entry() {
+        uint32_t old = push_message();
+        if (err) return;
+        uint32_t has = 0, o, l;
+        while (!err) {
+            uint32_t t = read_tag();
+            if (err || t == 0) break;
+            if (t == 10) {
+                lenfield(o, l);
+                has |= 1;
+            } else if (t == 18) {
+                lenfield(o, l);
+                has |= 2;
+            } else if (!unknown(t))
+                break;
+        }
+        if (!err && (last_tag != 0 || has != 3)) err = true;
+        limit = old;
+    }
+    // Model.Measurement { required string measurementId = 1; required double measurementValue = 2; }
+    __device__ void measurement(uint32_t &noff, uint32_t &nlen, uint64_t &vbits) {
+        uint32_t old = push_message();
+        if (err) return;
+        uint32_t has = 0;
+        while (!err) {
+            uint32_t t = read_tag();
+            if (err || t == 0) break;
+            if (t == 10) {
+                lenfield(noff, nlen);
+                has |= 1;
+            } else if (t == 17) {
+                vbits = fixed64();
+                has |= 2;
+            } else if (!unknown(t))
+                break;
+        }
+        if (!err && (last_tag != 0 || has != 3)) err = true;
+        limit = old;
+    }
+    // AbstractParser.parseDelimitedFrom over the record stream: false = null (stream exhausted)
+    __device__ __forceinline__ bool open_delimited(uint32_t &stream_pos, uint32_t total) {
+        if (stream_pos >= total) return false;
+        pos = stream_pos;
+        end = total;
+        limit = 0xffffffffu;
+        err = false;
+        last_tag = 0;
+        int32_t size = (int32_t)varint32();  // readRawVarint32(firstByte, input)
+        if (err) {
+            stream_pos = total;
+            return true;
+        }
+        uint32_t avail = total - pos;
+        uint32_t takeb = size < 0 ? 0u : ((uint32_t)size < avail ? (uint32_t)size : avail);
+        end = pos + takeb;
+        uint64_t lim = (uint64_t)pos + 0x7fffffffull;  // currentLimit = Integer.MAX_VALUE
+        limit = lim > 0xffffffffull ? 0xffffffffu : (uint32_t)lim;
+        stream_pos = end;
+        return true;
+    }
+};
+
+struct PbOut {
+    uint32_t status, count, cmd, flags;
+    uint32_t hw_off, hw_len, orig_off, orig_len, name_off, name_len, msg_off, msg_len;
+    uint32_t md_first, md_count;
+    uint32_t body_pos, body_end;  // second message body (for re-walking extra measurements)
+    int64_t date;
+    uint64_t v0, v1, v2;  // raw bits
+};
+
+template <typename B>
+__device__ void pb_parse_record(B bytes, uint32_t total, PbOut &o) {
+    PbReader<B> r;
+    r.b = bytes;
+    o.count = 0;
+    uint32_t spos = 0;
+    if (!r.open_delimited(spos, total)) {
+        o.status = SWGPU_ST_RUNTIME_EXCEPTION;  // header == null -> NPE
+        return;
+    }
+    bool has_cmd = false;
+    uint32_t cmd = 0;
+    bool has_orig = false;
+    o.orig_off = o.orig_len = 0;
+    while (!r.err) {
+        uint32_t tag = r.read_tag();
+        if (r.err || tag == 0) break;
+        if (tag == 8) {
+            uint32_t raw = r.varint32();
+            if (!r.err && raw >= 1 && raw <= 8) {
+                has_cmd = true;
+                cmd = raw;
+            }
+        } else if (tag == 18) {
+            r.lenfield(o.orig_off, o.orig_len);
+            has_orig = true;
+        } else if (!r.unknown(tag))
+            break;
+    }
+    if (r.err || r.last_tag != 0 || !has_cmd) {
+        o.status = SWGPU_ST_DECODE_EXCEPTION;
+        return;
+    }
+    if (cmd != 3 && cmd != 4 && cmd != 5) {
+        o.status = SWGPU_ST_PASSTHROUGH;
+        return;
+    }
+    if (!r.open_delimited(spos, total)) {
+        o.status = SWGPU_ST_RUNTIME_EXCEPTION;  // message == null -> NPE
+        return;
+    }
+    o.body_pos = r.pos;
+    o.body_end = r.end;
+    const uint32_t t_date = cmd == 3 ? 41u : (cmd == 4 ? 33u : 25u);
+    const uint32_t t_md = cmd == 3 ? 50u : (cmd == 4 ? 42u : 34u);
+    const uint32_t t_us = cmd == 3 ? 56u : (cmd == 4 ? 48u : 40u);
+    bool has_hw = false, has_lat = false, has_lon = false, has_date = false, us = false;
+    bool has_type = false, has_msg = false;
+    uint32_t nmx = 0;
+    o.hw_off = o.hw_len = o.name_off = o.name_len = o.msg_off = o.msg_len = 0;
+    o.md_first = o.md_count = 0;
+    o.date = 0;
+    o.v0 = o.v1 = o.v2 = 0;
+    while (!r.err) {
+        uint32_t tag_pos = r.pos;
+        uint32_t tag = r.read_tag();
+        if (r.err || tag == 0) break;
+        if (tag == 10) {
+            r.lenfield(o.hw_off, o.hw_len);
+            has_hw = true;
+        } else if (tag == t_date) {
+            o.date = (int64_t)r.fixed64();
+            has_date = true;
+        } else if (tag == t_md) {
+            if (o.md_count == 0) o.md_first = tag_pos;
+            o.md_count++;
+            r.metadata_entry();
+        } else if (tag == t_us) {
+            us = r.varint64() != 0;
+        } else if (cmd == 3 && tag == 17) {
+            o.v0 = r.fixed64();
+            has_lat = true;
+        } else if (cmd == 3 && tag == 25) {
+            o.v1 = r.fixed64();
+            has_lon = true;
+        } else if (cmd == 3 && tag == 33) {
+            o.v2 = r.fixed64();
+        } else if (cmd == 4 && tag == 18) {
+            r.lenfield(o.name_off, o.name_len);
+            has_type = true;
+        } else if (cmd == 4 && tag == 26) {
+            r.lenfield(o.msg_off, o.msg_len);
+            has_msg = true;
+        } else if (cmd == 5 && tag == 18) {
+            uint32_t no = 0, nl = 0;
+            uint64_t vb = 0;
+            r.measurement(no, nl, vb);
+            if (!r.err) {
+                if (nmx == 0) {
+                    o.name_off = no;
+                    o.name_len = nl;
+                    o.v0 = vb;
+                }
+                nmx++;
+            }
+        } else if (!r.unknown(tag))
+            break;
+    }
+    bool ok = !r.err && r.last_tag == 0 && has_hw;
+    if (cmd == 3) ok = ok && has_lat && has_lon;
+    if (cmd == 4) ok = ok && has_type && has_msg;
+    if (!ok) {
+        o.status = SWGPU_ST_DECODE_EXCEPTION;
+        return;
+    }
+    o.status = SWGPU_ST_OK;
+    o.cmd = cmd;
+    uint32_t f = 0;
+    if (us) f |= SWGPU_F_UPDATE_STATE;
+    if (has_date) f |= SWGPU_F_HAS_DATE;
+    if (has_orig) f |= SWGPU_F_HAS_ORIGINATOR;
+    if (o.md_count) f |= SWGPU_F_HAS_METADATA;
+    if (cmd == 3) f |= SWGPU_F_HAS_V0 | SWGPU_F_HAS_V1 | SWGPU_F_HAS_V2;
+    if (cmd == 4) f |= SWGPU_F_HAS_NAME | SWGPU_F_HAS_MESSAGE;
+    if (cmd == 5) f |= SWGPU_F_HAS_NAME | SWGPU_F_HAS_V0;
+    o.flags = f;
+    o.count = cmd == 5 ? nmx : 1u;
+}
+
+// k-th (k >= 1) Measurement of an already validated DeviceMeasurements body
+template <typename B>
+__device__ void pb_nth_measurement(B bytes, const PbOut &o, uint32_t k, uint32_t &noff, uint32_t &nlen,
+                                   uint64_t &vbits) {
+    PbReader<B> r;
+    r.b = bytes;
+    r.pos = o.body_pos;
+    r.end = o.body_end;
+    r.limit = 0xffffffffu;
+    r.err = false;
+    r.last_tag = 0;
+    uint32_t seen = 0;
+    while (!r.err) {
+        uint32_t tag = r.read_tag();
+        if (r.err || tag == 0) break;
+        if (tag == 18) {
+            r.measurement(noff, nlen, vbits);
+            if (seen == k) return;
+            seen++;
+        } else if (tag == 34) {
+            r.metadata_entry();
+        } else if (tag == 10) {
+            uint32_t a, b2;
+            r.lenfield(a, b2);
+        } else if (tag == 25) {
+            r.fixed64();
+        } else if (tag == 40) {
+            r.varint64();
+        } else if (!r.unknown(tag))
+            break;
+    }
+}
+
+template <typename B>
+__device__ __forceinline__ void pb_write_rows(const PbArgs &a, B bytes, const PbOut &o, uint32_t rec,
+                                              uint64_t row0) {
+    const uint32_t kind = o.cmd == 3 ? SWGPU_KIND_LOCATION : (o.cmd == 4 ? SWGPU_KIND_ALERT : SWGPU_KIND_MEASUREMENT);
+    const uint64_t meta = sw_mk_meta(kind, o.flags, 0, 0, 1, kind, rec);
+    const uint64_t th = sw_hash64(bytes, o.hw_off, o.hw_len);
+    const uint64_t tspan = sw_mk_span(o.hw_off, o.hw_len);
+    const uint64_t ospan = (o.flags & SWGPU_F_HAS_ORIGINATOR) ? sw_mk_span(o.orig_off, o.orig_len) : 0;
+    const uint64_t mdspan = o.md_count ? sw_mk_span(o.md_first, o.md_count) : 0;
+    for (uint32_t k = 0; k < o.count; k++) {
+        uint64_t row = row0 + k;
+        if (row >= a.max_rows) return;
+        uint32_t noff = o.name_off, nlen = o.name_len;
+        uint64_t v0 = o.v0;
+        if (k > 0) pb_nth_measurement(bytes, o, k, noff, nlen, v0);
+        a.cols.meta[row] = meta;
+        a.cols.token_hash[row] = th;
+        a.cols.name_hash[row] = (kind == SWGPU_KIND_LOCATION) ? 0 : sw_hash64(bytes, noff, nlen);
+        a.cols.event_date[row] = o.date;
+        a.cols.v0[row] = __longlong_as_double((long long)v0);
+        a.cols.v1[row] = __longlong_as_double((long long)o.v1);
+        a.cols.v2[row] = __longlong_as_double((long long)o.v2);
+        a.cols.token_span[row] = tspan;
+        a.cols.name_span[row] = (kind == SWGPU_KIND_LOCATION) ? 0 : sw_mk_span(noff, nlen);
+        if (a.cols.originator_span) a.cols.originator_span[row] = ospan;
+        if (a.cols.message_span)
+            a.cols.message_span[row] = kind == SWGPU_KIND_ALERT ? sw_mk_span(o.msg_off, o.msg_len) : 0;
+        if (a.cols.metadata_span) a.cols.metadata_span[row] = mdspan;
+        if (a.cols.alternate_id_span) a.cols.alternate_id_span[row] = 0;
+    }
+}
+
+__global__ void __launch_bounds__(PB_THREADS) pb_decode_kernel(PbArgs a) {
+    extern __shared__ __align__(16) uint8_t smem[];  // PB_STAGE + 64
+    __shared__ uint64_t s_warp[PB_THREADS / 32 + 2];
+    __shared__ uint32_t s_tile;
+    const uint32_t tid = threadIdx.x;
+    if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t rec0 = tile * PB_THREADS;
+    const uint32_t nrec = min((uint32_t)PB_THREADS, a.n - rec0);
+    const uint64_t b0 = a.rec_off[rec0], b1 = a.rec_off[rec0 + nrec];
+    const uintptr_t addr = (uintptr_t)(a.bytes + b0);
+    const uint32_t lead = (uint32_t)(addr & 15);
+    const uint64_t span = (uint64_t)lead + (b1 - b0);
+    const bool staged = span <= PB_STAGE;
+    if (staged) {
+        const uint4 *src = (const uint4 *)(addr - lead);
+        uint4 *dst = (uint4 *)smem;
+        const uint32_t nvec = (uint32_t)((span + 15) >> 4);
+        for (uint32_t i = tid; i < nvec; i += PB_THREADS) dst[i] = sw_ld_stream_u4(src + i);
+        __syncthreads();
+    }
+    PbOut o;
+    o.count = 0;
+    o.status = 0;
+    uint64_t r0 = 0;
+    uint32_t len = 0;
+    if (tid < nrec) {
+        r0 = a.rec_off[rec0 + tid];
+        uint64_t l64 = a.rec_off[rec0 + tid + 1] - r0;
+        len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
+        if (staged)
+            pb_parse_record(SmemBytes{smem + lead + (uint32_t)(r0 - b0)}, len, o);
+        else
+            pb_parse_record(GmemBytes{a.bytes + r0}, len, o);
+    }
+    uint64_t tile_total;
+    uint64_t row0 = sw_block_ordered_offset<PB_THREADS>(o.count, a.tile_state, tile, s_warp, &tile_total);
+    if (tid < nrec) {
+        const uint32_t rec = rec0 + tid;
+        a.status[rec] = (uint8_t)o.status;
+        a.first_row[rec] = (uint32_t)row0;
+        if (o.count) {
+            if (staged)
+                pb_write_rows(a, SmemBytes{smem + lead + (uint32_t)(r0 - b0)}, o, rec, row0);
+            else
+                pb_write_rows(a, GmemBytes{a.bytes + r0}, o, rec, row0);
+        }
+    }
+    if (rec0 + nrec == a.n && tid == 0) {
+        uint64_t total = row0 + tile_total;  // thread 0's offset is the tile base
+        a.first_row[a.n] = (uint32_t)total;
+        *a.out_rows = (uint32_t)total;
+    }
+}
+
+static int check_cols(swgpu_ctx *ctx, const swgpu_decoded_cols *c) {
+    if (!c || !c->meta || !c->token_hash || !c->name_hash || !c->event_date || !c->v0 || !c->v1 || !c->v2 ||
+        !c->token_span || !c->name_span) {
+        SW_SET_ERR(ctx, "decoded columns: the nine mandatory column pointers must be non-NULL");
+        return SWGPU_E_INVALID;
+    }
+    return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_decode_pb_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off,
+                                       uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out,
+                                       uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev) {
+    if (!ctx) return SWGPU_E_INVALID;
+    if (int rc = check_cols(ctx, out)) return rc;
+    if (!rec_off || !first_row || !out_rows_dev || (n && (!bytes || !status))) {
+        SW_SET_ERR(ctx, "swgpu_decode_pb_dev: NULL argument");
+        return SWGPU_E_INVALID;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (n == 0) {
+        SW_CUDA(ctx, cudaMemsetAsync(first_row, 0, sizeof(uint32_t), ctx->stream));
+        SW_CUDA(ctx, cudaMemsetAsync(out_rows_dev, 0, sizeof(uint32_t), ctx->stream));
+        return SWGPU_OK;
+    }
+    const uint32_t ntiles = (n + PB_THREADS - 1) / PB_THREADS;
+    const size_t sbytes = SW_SCRATCH_HDR + (size_t)ntiles * 8;
+    if (int rc = sw_ensure_scratch(ctx, sbytes)) return rc;
+    SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, sbytes, ctx->stream));
+    PbArgs a;
+    a.bytes = bytes;
+    a.rec_off = rec_off;
+    a.n = n;
+    a.max_rows = max_rows;
+    a.cols = *out;
+    a.status = status;
+    a.first_row = first_row;
+    a.out_rows = out_rows_dev;
+    a.ticket = (uint32_t *)ctx->scratch;
+    a.tile_state = (uint64_t *)((uint8_t *)ctx->scratch + SW_SCRATCH_HDR);
+    const int smem = PB_STAGE + 64;
+    SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    pb_decode_kernel<<<ntiles, PB_THREADS, smem, ctx->stream>>>(a);
+    SW_CUDA(ctx, cudaGetLastError());
+    return SWGPU_OK;
+}
+
+// ---- host-pointer entry point: stage in, decode, stage out ------------------------------------------
+int sw_stage_decode(swgpu_ctx *ctx, bool json, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
+                    uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row,
+                    uint32_t *out_rows) {
+    if (!ctx) return SWGPU_E_INVALID;
+    if (int rc = check_cols(ctx, out)) return rc;
+    if (!rec_off || !first_row || !out_rows || (n && (!bytes || !status))) {
+        SW_SET_ERR(ctx, "swgpu_decode: NULL argument");
+        return SWGPU_E_INVALID;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    const uint64_t total = rec_off[n];
+    const int NCOL = 13;
+    if (int rc = sw_ensure(ctx, ctx->d_bytes, total + 64)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_off, (size_t)(n + 1) * 8)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_status, (size_t)n + 16)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_first, (size_t)(n + 2) * 4 + 16)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_cols, (size_t)max_rows * 8 * NCOL + 64)) return rc;
+    cudaStream_t st = ctx->stream;
+    if (total) SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_bytes.p, bytes, total, cudaMemcpyHostToDevice, st));
+    SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_off.p, rec_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, st));
+    swgpu_decoded_cols d;
+    uint64_t *base = (uint64_t *)ctx->d_cols.p;
+    uint64_t **dp = (uint64_t **)&d;
+    uint64_t *const *hp = (uint64_t *const *)out;
+    for (int c = 0; c < NCOL; c++) dp[c] = (c < 9 || hp[c]) ? base + (size_t)c * max_rows : nullptr;
+    uint32_t *d_first = (uint32_t *)ctx->d_first.p;
+    uint32_t *d_rows = d_first + (n + 1);
+    int rc = json ? swgpu_decode_json_dev(ctx, (const uint8_t *)ctx->d_bytes.p, (const uint64_t *)ctx->d_off.p,
+                                          n, max_rows, &d, (uint8_t *)ctx->d_status.p, d_first, d_rows)
+                  : swgpu_decode_pb_dev(ctx, (const uint8_t *)ctx->d_bytes.p, (const uint64_t *)ctx->d_off.p, n,
+                                        max_rows, &d, (uint8_t *)ctx->d_status.p, d_first, d_rows);
+    if (rc) return rc;
+    // one D2H for (first_row, out_rows), then the live prefix of each column
+    SW_CUDA(ctx, cudaMemcpyAsync(first_row, d_first, (size_t)(n + 1) * 4, cudaMemcpyDeviceToHost, st));
+    if (n) SW_CUDA(ctx, cudaMemcpyAsync(status, ctx->d_status.p, n, cudaMemcpyDeviceToHost, st));
+    SW_CUDA(ctx, cudaStreamSynchronize(st));
+    const uint32_t rows = first_row[n];
+    *out_rows = rows;
+    const uint32_t live = rows < max_rows ? rows : max_rows;
+    if (live) {
+        for (int c = 0; c < NCOL; c++)
+            if (dp[c]) SW_CUDA(ctx, cudaMemcpyAsync(hp[c], dp[c], (size_t)live * 8, cudaMemcpyDeviceToHost, st));
+        SW_CUDA(ctx, cudaStreamSynchronize(st));
+    }
+    if (rows > max_rows) {
+        SW_SET_ERR(ctx, "decode produced %u rows but max_rows is %u", rows, max_rows);
+        return SWGPU_E_CAPACITY;
+    }
+    return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_decode_pb(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
+                                   uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
+                                   uint32_t *first_row, uint32_t *out_rows) {
+    return sw_stage_decode(ctx, false, bytes, rec_off, n, max_rows, out, status, first_row, out_rows);
+}

@@ -1,0 +1,533 @@
+// merge.cu — batched device-state last-writer merge
+// (reference: service-device-state/src/main/java/com/sitewhere/devicestate/processing/
+//  DeviceStateProcessingLogic.java:116-201 + persistence/DeviceStatePersistence.java:60-85: a sequential
+//  fold in arrival order; lastLocationEventId := id, lastMeasurementEventIds[name] := id,
+//  lastAlertEventIds[type] := id).
+//
+// Sort-free: the sequential "later event overwrites" is, per key, an argmax over the arrival
+// sequence number.  Pass 1 finds/claims the key's slot in an open-addressing table (hash picks the
+// bucket, the key BYTES decide equality) and does atomicMax(slot.best, seq+1); pass 2 lets exactly
+// the winner of each key write its payload (event id, date, value).  HBM-bound: one 64-byte slot and
+// one arena key per event, random access.
+#include "swgpu_common.cuh"
+
+#define MG_THREADS 256
+#define MG_PENDING 2ull
+
+struct MgSlot {  // 64 bytes = two sectors: {tag,best,key_off,key_len} is what pass 1 touches
+    uint64_t tag;   // 0 = empty; else (hash & ~3) | 1, bit1 = key bytes not yet published
+    uint64_t best;  // seq + 1 of the current winner
+    uint64_t key_off;
+    uint32_t key_len, pad;
+    uint64_t id_hi, id_lo;
+    int64_t date;
+    double value;
+};
+static_assert(sizeof(MgSlot) == 64, "MgSlot layout");
+
+struct MgCounters {  // device
+    unsigned long long n_keys, arena_top, table_full, arena_full, key_too_long;
+};
+
+struct MgState {
+    MgSlot *slots = nullptr;
+    uint64_t cap = 0;  // power of two
+    uint8_t *arena = nullptr;
+    uint64_t arena_cap = 0;
+    MgCounters *ctr = nullptr;
+    uint64_t keys_upper = 0;   // host upper bound on live keys
+    uint64_t arena_upper = 0;  // host upper bound on arena bytes
+    swgpu_ctx::Buf slot_idx;   // per-row slot index between pass 1 and 2
+};
+
+__host__ __device__ __forceinline__ uint64_t mg_mix(uint64_t th, uint64_t nh, uint32_t kindbyte) {
+    uint64_t h = th ^ (nh * 0x9e3779b97f4a7c15ull) ^ ((uint64_t)kindbyte << 56);
+    h ^= h >> 33;
+    h *= 0xff51afd7ed558ccdull;
+    h ^= h >> 33;
+    h *= 0xc4ceb9fe1a85ec53ull;
+    h ^= h >> 33;
+    return h;
+}
+
+struct MgArgs {
+    MgSlot *slots;
+    uint64_t mask;
+    uint8_t *arena;
+    uint64_t arena_cap;
+    MgCounters *ctr;
+    const uint8_t *bytes;
+    const uint64_t *rec_off;
+    const uint64_t *meta, *token_hash, *name_hash, *token_span, *name_span;
+    const int64_t *event_date;
+    const double *v0;
+    uint32_t n_rows;
+    const uint32_t *n_rows_dev;
+    uint64_t seq_base;
+    const uint64_t *id_hi, *id_lo;
+    uint64_t *slot_idx;
+};
+
+#define MG_NOSLOT 0xffffffffffffffffull
+
+__device__ __forceinline__ bool mg_key_equal(const uint8_t *arena_key, uint32_t key_len, uint32_t tl,
+                                             uint32_t kindbyte, const uint8_t *tok, const uint8_t *name,
+                                             uint32_t nl) {
+    if (key_len != tl + 3 + nl) return false;
+    if (arena_key[0] != (tl & 0xff) || arena_key[1] != (tl >> 8) || arena_key[2] != kindbyte) return false;
+    for (uint32_t i = 0; i < tl; i++)
+        if (arena_key[3 + i] != __ldg(tok + i)) return false;
+    for (uint32_t i = 0; i < nl; i++)
+        if (arena_key[3 + tl + i] != __ldg(name + i)) return false;
+    return true;
+}
+
+__global__ void __launch_bounds__(MG_THREADS) merge_upsert_kernel(MgArgs a) {
+    const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n_rows) : a.n_rows;
+    const uint32_t r = blockIdx.x * MG_THREADS + threadIdx.x;
+    if (r >= n_live) return;
+    a.slot_idx[r] = MG_NOSLOT;
+    const uint64_t m = __ldg(a.meta + r);
+    const uint32_t kind = SWGPU_META_KIND(m), fl = SWGPU_META_FLAGS(m);
+    if (kind > SWGPU_KIND_ALERT || (fl & SWGPU_F_NULL_TOKEN)) return;
+    const uint8_t *rec = a.bytes + __ldg(a.rec_off + SWGPU_META_REC(m));
+    const uint64_t ts = __ldg(a.token_span + r), ns = __ldg(a.name_span + r);
+    const uint32_t tl = SWGPU_SPAN_LEN(ts);
+    const uint32_t nl = kind == SWGPU_KIND_LOCATION ? 0u : SWGPU_SPAN_LEN(ns);
+    if (tl > 0xffffu) {
+        atomicAdd(&a.ctr->key_too_long, 1ull);
+        return;
+    }
+    const uint8_t *tok = rec + SWGPU_SPAN_OFF(ts), *name = rec + SWGPU_SPAN_OFF(ns);
+    const uint32_t kindbyte = kind | ((kind != SWGPU_KIND_LOCATION && !(fl & SWGPU_F_HAS_NAME)) ? 0x80u : 0u);
+    const uint64_t h = mg_mix(__ldg(a.token_hash + r), kind == SWGPU_KIND_LOCATION ? 0ull : __ldg(a.name_hash + r),
+                              kindbyte);
+    const uint64_t want = (h & ~3ull) | 1ull;
+    uint64_t s = (h >> 2) & a.mask;
+    for (uint64_t probes = 0; probes <= a.mask; probes++, s = (s + 1) & a.mask) {
+        MgSlot *sl = a.slots + s;
+        uint64_t tag = sw_ld_volatile_u64(&sl->tag);
+        if (tag == 0) {
+            unsigned long long old =
+                atomicCAS((unsigned long long *)&sl->tag, 0ull, (unsigned long long)(want | MG_PENDING));
+            if (old == 0) {
+                // claimed: publish the key bytes, then clear the pending bit
+                const uint32_t kl = tl + 3 + nl;
+                unsigned long long off = atomicAdd(&a.ctr->arena_top, (unsigned long long)kl);
+                if (off + kl > a.arena_cap) {
+                    atomicAdd(&a.ctr->arena_full, 1ull);
+                    sl->key_len = 0xffffffffu;  // poisoned slot: never equal to any key
+                    sl->key_off = 0;
+                    __threadfence();
+                    sw_st_volatile_u64(&sl->tag, want);
+                    return;
+                }
+                uint8_t *k = a.arena + off;
+                k[0] = (uint8_t)(tl & 0xff);
+                k[1] = (uint8_t)(tl >> 8);
+                k[2] = (uint8_t)kindbyte;
+                for (uint32_t i = 0; i < tl; i++) k[3 + i] = __ldg(tok + i);
+                for (uint32_t i = 0; i < nl; i++) k[3 + tl + i] = __ldg(name + i);
+                sl->key_off = off;
+                sl->key_len = kl;
+                atomicAdd(&a.ctr->n_keys, 1ull);
+                __threadfence();
+                sw_st_volatile_u64(&sl->tag, want);
+                break;
+            }
+            tag = old;
+        }
+        if ((tag & ~MG_PENDING) == want) {
+            while (tag & MG_PENDING) tag = sw_ld_volatile_u64(&sl->tag);  // the claimer is publishing
+            __threadfence();
+            const uint32_t kl = *(volatile uint32_t *)&sl->key_len;
+            const uint64_t ko = *(volatile uint64_t *)&sl->key_off;
+            if (kl != 0xffffffffu && mg_key_equal(a.arena + ko, kl, tl, kindbyte, tok, name, nl)) break;
+        }
+        if (probes == a.mask) {
+            atomicAdd(&a.ctr->table_full, 1ull);
+            return;
+        }
+    }
+    atomicMax((unsigned long long *)&a.slots[s].best, (unsigned long long)(a.seq_base + r + 1));
+    a.slot_idx[r] = s;
+}
+
+__global__ void __launch_bounds__(MG_THREADS) merge_publish_kernel(MgArgs a) {
+    const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n_rows) : a.n_rows;
+    const uint32_t r = blockIdx.x * MG_THREADS + threadIdx.x;
+    if (r >= n_live) return;
+    const uint64_t s = a.slot_idx[r];
+    if (s == MG_NOSLOT) return;
+    MgSlot *sl = a.slots + s;
+    if (sl->best != a.seq_base + r + 1) return;  // a later event of this key won
+    sl->id_hi = __ldg(a.id_hi + r);
+    sl->id_lo = __ldg(a.id_lo + r);
+    sl->date = __ldg(a.event_date + r);
+    sl->value = __ldg(a.v0 + r);
+}
+
+// re-insert live slots into a larger table (keys are distinct: no byte compare needed)
+__global__ void merge_rehash_kernel(const MgSlot *old_slots, uint64_t old_cap, MgSlot *slots, uint64_t mask) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= old_cap) return;
+    MgSlot v = old_slots[i];
+    if (v.tag == 0) return;
+    uint64_t s = (v.tag >> 2) & mask;
+    for (;;) {
+        unsigned long long old = atomicCAS((unsigned long long *)&slots[s].tag, 0ull, (unsigned long long)v.tag);
+        if (old == 0) break;
+        s = (s + 1) & mask;
+    }
+    MgSlot *d = slots + s;
+    d->best = v.best;
+    d->key_off = v.key_off;
+    d->key_len = v.key_len;
+    d->id_hi = v.id_hi;
+    d->id_lo = v.id_lo;
+    d->date = v.date;
+    d->value = v.value;
+}
+
+void sw_state_free(swgpu_ctx *ctx) {
+    MgState *st = (MgState *)ctx->state;
+    if (!st) return;
+    if (st->slots) cudaFree(st->slots);
+    if (st->arena) cudaFree(st->arena);
+    if (st->ctr) cudaFree(st->ctr);
+    if (st->slot_idx.p) cudaFree(st->slot_idx.p);
+    delete st;
+    ctx->state = nullptr;
+}
+
+static uint64_t pow2_at_least(uint64_t v) {
+    uint64_t p = 1024;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+static int mg_read_counters(swgpu_ctx *ctx, MgState *st, MgCounters *out) {
+    SW_CUDA(ctx, cudaMemcpyAsync(out, st->ctr, sizeof(MgCounters), cudaMemcpyDeviceToHost, ctx->stream));
+    SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SWGPU_OK;
+}
+
+// make room for `max_keys` keys and `max_key_bytes` arena bytes (grows, never shrinks)
+static int mg_reserve(swgpu_ctx *ctx, uint64_t max_keys, uint64_t max_key_bytes) {
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    MgState *st = (MgState *)ctx->state;
+    if (!st) {
+        st = new MgState();
+        ctx->state = st;
+        cudaError_t e = cudaMalloc(&st->ctr, sizeof(MgCounters));
+        if (e != cudaSuccess) {
+            SW_SET_ERR(ctx, "cudaMalloc(state counters) failed: %s", cudaGetErrorString(e));
+            return SWGPU_E_NOMEM;
+        }
+        SW_CUDA(ctx, cudaMemsetAsync(st->ctr, 0, sizeof(MgCounters), ctx->stream));
+    }
+    const uint64_t want_cap = pow2_at_least(max_keys * 2 + 16);
+    if (want_cap > st->cap) {
+        MgSlot *ns = nullptr;
+        cudaError_t e = cudaMalloc(&ns, want_cap * sizeof(MgSlot));
+        if (e != cudaSuccess) {
+            SW_SET_ERR(ctx, "cudaMalloc(state table %llu slots) failed: %s", (unsigned long long)want_cap,
+                       cudaGetErrorString(e));
+            return SWGPU_E_NOMEM;
+        }
+        SW_CUDA(ctx, cudaMemsetAsync(ns, 0, want_cap * sizeof(MgSlot), ctx->stream));
+        if (st->slots) {
+            const uint64_t nb = (st->cap + 255) / 256;
+            merge_rehash_kernel<<<(unsigned)nb, 256, 0, ctx->stream>>>(st->slots, st->cap, ns, want_cap - 1);
+            SW_CUDA(ctx, cudaGetLastError());
+            SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            SW_CUDA(ctx, cudaFree(st->slots));
+        }
+        st->slots = ns;
+        st->cap = want_cap;
+    }
+    if (max_key_bytes > st->arena_cap) {
+        const uint64_t want = max_key_bytes + max_key_bytes / 4 + 4096;
+        uint8_t *na = nullptr;
+        cudaError_t e = cudaMalloc(&na, want);
+        if (e != cudaSuccess) {
+            SW_SET_ERR(ctx, "cudaMalloc(key arena %llu) failed: %s", (unsigned long long)want, cudaGetErrorString(e));
+            return SWGPU_E_NOMEM;
+        }
+        if (st->arena) {
+            MgCounters c;
+            if (int rc = mg_read_counters(ctx, st, &c)) return rc;
+            uint64_t used = c.arena_top < st->arena_cap ? c.arena_top : st->arena_cap;
+            if (used) SW_CUDA(ctx, cudaMemcpyAsync(na, st->arena, used, cudaMemcpyDeviceToDevice, ctx->stream));
+            SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            SW_CUDA(ctx, cudaFree(st->arena));
+        }
+        st->arena = na;
+        st->arena_cap = want;
+    }
+    return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_state_reserve(swgpu_ctx *ctx, uint64_t max_keys, uint64_t max_key_bytes) {
+    if (!ctx) return SWGPU_E_INVALID;
+    return mg_reserve(ctx, max_keys, max_key_bytes);
+}
+
+extern "C" int32_t swgpu_merge_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off,
+                                   uint32_t n_records, const swgpu_decoded_cols *rows, uint32_t n_rows,
+                                   const uint32_t *n_rows_dev, uint64_t seq_base, const uint64_t *id_hi,
+                                   const uint64_t *id_lo) {
+    (void)n_records;
+    if (!ctx) return SWGPU_E_INVALID;
+    if (n_rows == 0) return SWGPU_OK;
+    if (!bytes || !rec_off || !rows || !rows->meta || !rows->token_hash || !rows->name_hash || !rows->token_span ||
+        !rows->name_span || !rows->event_date || !rows->v0 || !id_hi || !id_lo) {
+        SW_SET_ERR(ctx, "swgpu_merge_dev: NULL argument");
+        return SWGPU_E_INVALID;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    MgState *st = (MgState *)ctx->state;
+    // capacity: every row could be a new key of up to (avg) 64 key bytes; tighten the host-side
+    // upper bounds by reading the device counters only when they would force a growth
+    {
+        uint64_t ku = (st ? st->keys_upper : 0) + n_rows;
+        uint64_t au = (st ? st->arena_upper : 0) + (uint64_t)n_rows * 64;
+        if (!st || ku * 2 + 16 > st->cap || au > st->arena_cap) {
+            if (st && st->ctr) {
+                MgCounters c;
+                if (int rc = mg_read_counters(ctx, st, &c)) return rc;
+                st->keys_upper = c.n_keys;
+                st->arena_upper = c.arena_top;
+                ku = st->keys_upper + n_rows;
+                au = st->arena_upper + (uint64_t)n_rows * 64;
+            }
+            if (int rc = mg_reserve(ctx, ku, au)) return rc;
+            st = (MgState *)ctx->state;
+        }
+        st->keys_upper = ku;
+        st->arena_upper = au;
+    }
+    if (int rc = sw_ensure(ctx, st->slot_idx, (size_t)n_rows * 8)) return rc;
+    MgArgs a;
+    a.slots = st->slots;
+    a.mask = st->cap - 1;
+    a.arena = st->arena;
+    a.arena_cap = st->arena_cap;
+    a.ctr = st->ctr;
+    a.bytes = bytes;
+    a.rec_off = rec_off;
+    a.meta = rows->meta;
+    a.token_hash = rows->token_hash;
+    a.name_hash = rows->name_hash;
+    a.token_span = rows->token_span;
+    a.name_span = rows->name_span;
+    a.event_date = rows->event_date;
+    a.v0 = rows->v0;
+    a.n_rows = n_rows;
+    a.n_rows_dev = n_rows_dev;
+    a.seq_base = seq_base;
+    a.id_hi = id_hi;
+    a.id_lo = id_lo;
+    a.slot_idx = (uint64_t *)st->slot_idx.p;
+    const unsigned nb = (n_rows + MG_THREADS - 1) / MG_THREADS;
+    merge_upsert_kernel<<<nb, MG_THREADS, 0, ctx->stream>>>(a);
+    SW_CUDA(ctx, cudaGetLastError());
+    merge_publish_kernel<<<nb, MG_THREADS, 0, ctx->stream>>>(a);
+    SW_CUDA(ctx, cudaGetLastError());
+    return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_merge(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n_records,
+                               const swgpu_decoded_cols *rows, uint32_t n_rows, uint64_t seq_base,
+                               const uint64_t *id_hi, const uint64_t *id_lo) {
+    if (!ctx) return SWGPU_E_INVALID;
+    if (n_rows == 0) return SWGPU_OK;
+    if (!bytes || !rec_off || !rows || !id_hi || !id_lo) {
+        SW_SET_ERR(ctx, "swgpu_merge: NULL argument");
+        return SWGPU_E_INVALID;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    const uint64_t total = rec_off[n_records];
+    if (int rc = sw_ensure(ctx, ctx->d_bytes, total + 64)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_off, (size_t)(n_records + 1) * 8)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_cols, (size_t)n_rows * 8 * 7 + 64)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_ids, (size_t)n_rows * 16 + 64)) return rc;
+    SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_bytes.p, bytes, total, cudaMemcpyHostToDevice, s));
+    SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_off.p, rec_off, (size_t)(n_records + 1) * 8, cudaMemcpyHostToDevice, s));
+    uint64_t *base = (uint64_t *)ctx->d_cols.p;
+    swgpu_decoded_cols d;
+    memset(&d, 0, sizeof d);
+    const void *src[7] = {rows->meta, rows->token_hash, rows->name_hash, rows->event_date,
+                          rows->v0,   rows->token_span, rows->name_span};
+    for (int c = 0; c < 7; c++) {
+        if (!src[c]) {
+            SW_SET_ERR(ctx, "swgpu_merge: missing column");
+            return SWGPU_E_INVALID;
+        }
+        SW_CUDA(ctx, cudaMemcpyAsync(base + (size_t)c * n_rows, src[c], (size_t)n_rows * 8, cudaMemcpyHostToDevice, s));
+    }
+    d.meta = base;
+    d.token_hash = base + (size_t)n_rows;
+    d.name_hash = base + (size_t)2 * n_rows;
+    d.event_date = (int64_t *)(base + (size_t)3 * n_rows);
+    d.v0 = (double *)(base + (size_t)4 * n_rows);
+    d.token_span = base + (size_t)5 * n_rows;
+    d.name_span = base + (size_t)6 * n_rows;
+    uint64_t *ids = (uint64_t *)ctx->d_ids.p;
+    SW_CUDA(ctx, cudaMemcpyAsync(ids, id_hi, (size_t)n_rows * 8, cudaMemcpyHostToDevice, s));
+    SW_CUDA(ctx, cudaMemcpyAsync(ids + n_rows, id_lo, (size_t)n_rows * 8, cudaMemcpyHostToDevice, s));
+    int rc = swgpu_merge_dev(ctx, (const uint8_t *)ctx->d_bytes.p, (const uint64_t *)ctx->d_off.p, n_records, &d,
+                             n_rows, nullptr, seq_base, ids, ids + n_rows);
+    if (rc) return rc;
+    MgState *st = (MgState *)ctx->state;
+    MgCounters c;
+    if (int rc2 = mg_read_counters(ctx, st, &c)) return rc2;
+    st->keys_upper = c.n_keys;
+    st->arena_upper = c.arena_top < st->arena_cap ? c.arena_top : st->arena_cap;
+    if (c.table_full || c.arena_full) {
+        SW_SET_ERR(ctx, "state table capacity exceeded (table_full=%llu arena_full=%llu)", c.table_full, c.arena_full);
+        return SWGPU_E_CAPACITY;
+    }
+    return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_state_size(swgpu_ctx *ctx, uint64_t *n_keys, uint64_t *key_bytes) {
+    if (!ctx) return SWGPU_E_INVALID;
+    MgState *st = (MgState *)ctx->state;
+    if (!st) {
+        if (n_keys) *n_keys = 0;
+        if (key_bytes) *key_bytes = 0;
+        return SWGPU_OK;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    MgCounters c;
+    if (int rc = mg_read_counters(ctx, st, &c)) return rc;
+    if (n_keys) *n_keys = c.n_keys;
+    if (key_bytes) *key_bytes = c.arena_top < st->arena_cap ? c.arena_top : st->arena_cap;
+    if (c.table_full || c.arena_full) {
+        SW_SET_ERR(ctx, "state table capacity exceeded (table_full=%llu arena_full=%llu)", c.table_full, c.arena_full);
+        return SWGPU_E_CAPACITY;
+    }
+    return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_state_clear(swgpu_ctx *ctx) {
+    if (!ctx) return SWGPU_E_INVALID;
+    MgState *st = (MgState *)ctx->state;
+    if (!st) return SWGPU_OK;
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (st->slots) SW_CUDA(ctx, cudaMemsetAsync(st->slots, 0, st->cap * sizeof(MgSlot), ctx->stream));
+    SW_CUDA(ctx, cudaMemsetAsync(st->ctr, 0, sizeof(MgCounters), ctx->stream));
+    st->keys_upper = 0;
+    st->arena_upper = 0;
+    return SWGPU_OK;
+}
+
+// Snapshot / restore are checkpoint operations, not the hot path: the table and arena are copied
+// to the host and (de)compacted there.
+extern "C" int32_t swgpu_state_snapshot(swgpu_ctx *ctx, uint64_t max_keys, uint64_t max_key_bytes,
+                                        const swgpu_state_rows *out, uint64_t *n_keys) {
+    if (!ctx || !out || !n_keys) return SWGPU_E_INVALID;
+    *n_keys = 0;
+    MgState *st = (MgState *)ctx->state;
+    if (!st || !st->slots) {
+        if (out->key_off) out->key_off[0] = 0;
+        return SWGPU_OK;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    MgCounters c;
+    if (int rc = mg_read_counters(ctx, st, &c)) return rc;
+    const uint64_t used = c.arena_top < st->arena_cap ? c.arena_top : st->arena_cap;
+    if (c.n_keys > max_keys || used > max_key_bytes) {
+        *n_keys = c.n_keys;
+        SW_SET_ERR(ctx, "snapshot needs %llu keys / %llu key bytes", c.n_keys, (unsigned long long)used);
+        return SWGPU_E_CAPACITY;
+    }
+    std::vector<MgSlot> slots(st->cap);
+    std::vector<uint8_t> arena(used ? used : 1);
+    SW_CUDA(ctx, cudaMemcpyAsync(slots.data(), st->slots, st->cap * sizeof(MgSlot), cudaMemcpyDeviceToHost, ctx->stream));
+    if (used) SW_CUDA(ctx, cudaMemcpyAsync(arena.data(), st->arena, used, cudaMemcpyDeviceToHost, ctx->stream));
+    SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    uint64_t k = 0, off = 0;
+    for (uint64_t i = 0; i < st->cap; i++) {
+        const MgSlot &s = slots[i];
+        if (s.tag == 0 || s.key_len == 0xffffffffu) continue;
+        out->seq[k] = s.best - 1;
+        out->id_hi[k] = s.id_hi;
+        out->id_lo[k] = s.id_lo;
+        out->event_date[k] = s.date;
+        out->value[k] = s.value;
+        out->key_off[k] = off;
+        memcpy(out->key_bytes + off, arena.data() + s.key_off, s.key_len);
+        off += s.key_len;
+        k++;
+    }
+    out->key_off[k] = off;
+    *n_keys = k;
+    return SWGPU_OK;
+}
+
+static uint64_t host_hash64(const uint8_t *d, uint32_t len) {
+    uint32_t f = 0x811c9dc5u;
+    for (uint32_t i = 0; i < len; i++) f = (f ^ d[i]) * 0x01000193u;
+    f ^= f >> 16;
+    f *= 0x85ebca6bu;
+    f ^= f >> 13;
+    f *= 0xc2b2ae35u;
+    f ^= f >> 16;
+    return ((uint64_t)f << 32) | swgpu_murmur2(d, len);
+}
+
+extern "C" int32_t swgpu_state_restore(swgpu_ctx *ctx, const swgpu_state_rows *in, uint64_t n_keys) {
+    if (!ctx || (n_keys && !in)) return SWGPU_E_INVALID;
+    if (int rc = swgpu_state_clear(ctx)) return rc;
+    if (n_keys == 0) return SWGPU_OK;
+    const uint64_t kbytes = in->key_off[n_keys];
+    if (int rc = mg_reserve(ctx, n_keys, kbytes)) return rc;
+    MgState *st = (MgState *)ctx->state;
+    std::vector<MgSlot> slots(st->cap);
+    memset(slots.data(), 0, slots.size() * sizeof(MgSlot));
+    const uint64_t mask = st->cap - 1;
+    for (uint64_t k = 0; k < n_keys; k++) {
+        const uint8_t *key = in->key_bytes + in->key_off[k];
+        const uint32_t kl = (uint32_t)(in->key_off[k + 1] - in->key_off[k]);
+        if (kl < 3) {
+            SW_SET_ERR(ctx, "swgpu_state_restore: malformed key %llu", (unsigned long long)k);
+            return SWGPU_E_INVALID;
+        }
+        const uint32_t tl = key[0] | ((uint32_t)key[1] << 8);
+        const uint32_t kindbyte = key[2];
+        if (3 + tl > kl) {
+            SW_SET_ERR(ctx, "swgpu_state_restore: malformed key %llu", (unsigned long long)k);
+            return SWGPU_E_INVALID;
+        }
+        const uint32_t nl = kl - 3 - tl;
+        const uint32_t kind = kindbyte & 0x7f;
+        const uint64_t th = host_hash64(key + 3, tl);
+        const uint64_t nh = kind == SWGPU_KIND_LOCATION ? 0 : (((kindbyte & 0x80) && nl == 0) ? 0 : host_hash64(key + 3 + tl, nl));
+        const uint64_t h = mg_mix(th, nh, kindbyte);
+        uint64_t s = (h >> 2) & mask;
+        while (slots[s].tag) s = (s + 1) & mask;
+        MgSlot &d = slots[s];
+        d.tag = (h & ~3ull) | 1ull;
+        d.best = in->seq[k] + 1;
+        d.key_off = in->key_off[k];
+        d.key_len = kl;
+        d.id_hi = in->id_hi[k];
+        d.id_lo = in->id_lo[k];
+        d.date = in->event_date[k];
+        d.value = in->value[k];
+    }
+    MgCounters c;
+    memset(&c, 0, sizeof c);
+    c.n_keys = n_keys;
+    c.arena_top = kbytes;
+    SW_CUDA(ctx, cudaMemcpyAsync(st->slots, slots.data(), slots.size() * sizeof(MgSlot), cudaMemcpyHostToDevice, ctx->stream));
+    SW_CUDA(ctx, cudaMemcpyAsync(st->arena, in->key_bytes, kbytes, cudaMemcpyHostToDevice, ctx->stream));
+    SW_CUDA(ctx, cudaMemcpyAsync(st->ctr, &c, sizeof c, cudaMemcpyHostToDevice, ctx->stream));
+    SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    st->keys_upper = n_keys;
+    st->arena_upper = kbytes;
+    return SWGPU_OK;
+}

@@ -1,0 +1,603 @@
+// zone.cu — batched ZoneTestRuleProcessor.onLocation
+// (reference: service-rule-processing/src/main/java/com/sitewhere/rules/processors/geospatial/
+//  ZoneTestRuleProcessor.java:47-63; polygons per sitewhere-core/.../geospatial/GeoUtils.java:55-67;
+//  containment = JTS 1.13 Polygon.contains(Point): envelope short-circuit, isRectangle ->
+//  RectangleContains, else RayCrossingCounter with RobustDeterminant.signOfDet2x2).
+//
+// Results are bit-identical to the index-free reference loop; two exact accelerations remove work
+// that cannot change the answer:
+//   * a uniform grid over zone envelopes: Geometry.contains starts with an envelope test, so a
+//     test whose envelope misses the point's grid cell is Outside.  Cell ids come from the same
+//     monotone expression on host (registration) and device (lookup), so a point inside an
+//     envelope always finds that zone in its cell.
+//   * per-zone y-slabs over ring edges: an edge whose y-range misses the point's slab is strictly
+//     above or below the ray; RayCrossingCounter.countSegment neither counts it nor flags a boundary.
+// Crossing side = exact sign of x1*y2 - y1*x2 on the translated coordinates via error-free products
+// (fma), the value RobustDeterminant returns.  FP64 pipe bound; the zone table lives in L2.
+#include <math.h>
+
+#include <algorithm>
+
+#include "swgpu_common.cuh"
+
+#define ZN_THREADS 256
+#define ZN_MAXIN 8  // inside-set kept in registers per location; overflow recomputes (exact)
+#define ZN_MAGIC 0x315a4e4f5a575355ull
+
+struct ZoneHeader {  // 128 bytes, start of the packed table
+    uint64_t magic, total_bytes;
+    uint32_t n_tests, n_outside, grid_nx, grid_ny;
+    double gx0, gy0, gx1, gy1;  // union of envelopes
+    double inv_cx, inv_cy;
+    uint64_t off_tests, off_verts, off_cell_start, off_cell_items, off_bin_start, off_bin_items, off_outside;
+};
+static_assert(sizeof(ZoneHeader) == 136, "ZoneHeader layout");
+
+struct ZoneTestRec {  // 64 bytes
+    double minx, maxx, miny, maxy;
+    uint32_t vtx_off, npts;  // closed ring in verts[]
+    uint32_t flags, nbins;   // flags: bit0 cond == Outside, bit1 isRectangle
+    double inv_bin;
+    uint32_t bin_off, pad;
+};
+static_assert(sizeof(ZoneTestRec) == 64, "ZoneTestRec layout");
+
+// monotone cell function shared by host (registration) and device (lookup); separate IEEE
+// sub and mul (no contraction) so both sides round identically.
+__host__ __device__ __forceinline__ uint32_t zn_cell(double v, double v0, double inv, uint32_t n) {
+#ifdef __CUDA_ARCH__
+    double t = __dmul_rn(__dsub_rn(v, v0), inv);
+#else
+    volatile double d = v - v0;
+    volatile double t = d * inv;
+#endif
+    if (!(t >= 0.0)) return 0;
+    if (t >= (double)n) return n - 1;
+    return (uint32_t)t;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host: build the packed table
+static bool host_is_rectangle(const double *x, const double *y, uint32_t npts, double minx, double maxx,
+                              double miny, double maxy) {
+    if (npts != 5) return false;
+    for (int i = 0; i < 5; i++) {
+        if (!(x[i] == minx || x[i] == maxx)) return false;
+        if (!(y[i] == miny || y[i] == maxy)) return false;
+    }
+    double px = x[0], py = y[0];
+    for (int i = 1; i <= 4; i++) {
+        bool xc = x[i] != px, yc = y[i] != py;
+        if (xc == yc) return false;
+        px = x[i];
+        py = y[i];
+    }
+    return true;
+}
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, const double *lon,
+                           const double *lat, const uint8_t *cond, std::vector<uint8_t> &blob) {
+    std::vector<ZoneTestRec> tests(T);
+    std::vector<double> verts;  // x,y interleaved
+    std::vector<uint32_t> outside;
+    uint64_t total_pts = 0;
+    for (uint32_t t = 0; t < T; t++) {
+        if (vtx_off[t + 1] < vtx_off[t]) {
+            SW_SET_ERR(ctx, "swgpu_set_zones: vtx_off not monotone at test %u", t);
+            return SWGPU_E_INVALID;
+        }
+        uint32_t nv = vtx_off[t + 1] - vtx_off[t];
+        if (nv == 0) {  // GeoUtils would throw on locations.get(0)
+            SW_SET_ERR(ctx, "swgpu_set_zones: test %u has no bounds", t);
+            return SWGPU_E_INVALID;
+        }
+        total_pts += nv + 1;
+    }
+    if (total_pts > 0x7fffffffull) {
+        SW_SET_ERR(ctx, "swgpu_set_zones: too many vertices");
+        return SWGPU_E_INVALID;
+    }
+    verts.reserve(total_pts * 2);
+    double gx0 = INFINITY, gy0 = INFINITY, gx1 = -INFINITY, gy1 = -INFINITY;
+    std::vector<uint32_t> bin_start, bin_items;
+    for (uint32_t t = 0; t < T; t++) {
+        ZoneTestRec &z = tests[t];
+        memset(&z, 0, sizeof z);
+        uint32_t a = vtx_off[t], b = vtx_off[t + 1], nv = b - a;
+        z.vtx_off = (uint32_t)(verts.size() / 2);
+        z.npts = nv + 1;
+        for (uint32_t k = a; k < b; k++) {
+            verts.push_back(lon[k]);
+            verts.push_back(lat[k]);
+        }
+        verts.push_back(lon[a]);
+        verts.push_back(lat[a]);
+        const double *xy = &verts[(size_t)z.vtx_off * 2];
+        double minx = xy[0], maxx = xy[0], miny = xy[1], maxy = xy[1];
+        for (uint32_t i = 1; i < z.npts; i++) {
+            double x = xy[2 * i], y = xy[2 * i + 1];
+            if (x < minx) minx = x;
+            if (x > maxx) maxx = x;
+            if (y < miny) miny = y;
+            if (y > maxy) maxy = y;
+        }
+        z.minx = minx;
+        z.maxx = maxx;
+        z.miny = miny;
+        z.maxy = maxy;
+        if (!(std::isfinite(minx) && std::isfinite(maxx) && std::isfinite(miny) && std::isfinite(maxy))) {
+            SW_SET_ERR(ctx, "swgpu_set_zones: test %u has non-finite bounds", t);
+            return SWGPU_E_INVALID;
+        }
+        std::vector<double> xs(z.npts), ys(z.npts);
+        for (uint32_t i = 0; i < z.npts; i++) {
+            xs[i] = xy[2 * i];
+            ys[i] = xy[2 * i + 1];
+        }
+        bool rect = host_is_rectangle(xs.data(), ys.data(), z.npts, minx, maxx, miny, maxy);
+        z.flags = (cond[t] ? 1u : 0u) | (rect ? 2u : 0u);
+        if (cond[t]) outside.push_back(t);
+        gx0 = std::min(gx0, minx);
+        gx1 = std::max(gx1, maxx);
+        gy0 = std::min(gy0, miny);
+        gy1 = std::max(gy1, maxy);
+        // y-slabs over edges i = 1..npts-1 (edge i joins ring[i] and ring[i-1])
+        z.bin_off = (uint32_t)bin_start.size();
+        if (rect) {
+            z.nbins = 0;
+            z.inv_bin = 0;
+        } else {
+            uint32_t nb = std::max(1u, std::min(64u, (z.npts - 1 + 3) / 4));
+            double h = maxy - miny;
+            double inv = (h > 0 && std::isfinite((double)nb / h)) ? (double)nb / h : 0.0;
+            if (inv == 0.0) nb = 1;
+            z.nbins = nb;
+            z.inv_bin = inv;
+            std::vector<std::vector<uint32_t>> bins(nb);
+            for (uint32_t i = 1; i < z.npts; i++) {
+                double y1 = ys[i], y2 = ys[i - 1];
+                uint32_t lo = zn_cell(std::min(y1, y2), miny, inv, nb), hi = zn_cell(std::max(y1, y2), miny, inv, nb);
+                for (uint32_t bb = lo; bb <= hi; bb++) bins[bb].push_back(i);
+            }
+            for (uint32_t bb = 0; bb < nb; bb++) {
+                bin_start.push_back((uint32_t)bin_items.size());
+                for (uint32_t e : bins[bb]) bin_items.push_back(e);
+            }
+            bin_start.push_back((uint32_t)bin_items.size());
+        }
+    }
+    // grid over envelopes
+    uint32_t g = 1;
+    while ((uint64_t)g * g < (uint64_t)T * 4 && g < 1024) g *= 2;
+    uint32_t nx = g, ny = g;
+    std::vector<uint32_t> cell_start, cell_items;
+    double inv_cx = 0, inv_cy = 0;
+    for (;;) {
+        double w = gx1 - gx0, h = gy1 - gy0;
+        inv_cx = (T && w > 0 && std::isfinite((double)nx / w)) ? (double)nx / w : 0.0;
+        inv_cy = (T && h > 0 && std::isfinite((double)ny / h)) ? (double)ny / h : 0.0;
+        if (inv_cx == 0.0) nx = 1;
+        if (inv_cy == 0.0) ny = 1;
+        std::vector<uint32_t> cnt((size_t)nx * ny + 1, 0);
+        uint64_t items = 0;
+        for (uint32_t t = 0; t < T; t++) {
+            const ZoneTestRec &z = tests[t];
+            uint32_t x0 = zn_cell(z.minx, gx0, inv_cx, nx), x1 = zn_cell(z.maxx, gx0, inv_cx, nx);
+            uint32_t y0 = zn_cell(z.miny, gy0, inv_cy, ny), y1 = zn_cell(z.maxy, gy0, inv_cy, ny);
+            items += (uint64_t)(x1 - x0 + 1) * (y1 - y0 + 1);
+        }
+        if (items > (64ull << 20) && (nx > 1 || ny > 1)) {  // large overlapping zones: coarsen
+            nx = std::max(1u, nx / 2);
+            ny = std::max(1u, ny / 2);
+            continue;
+        }
+        for (uint32_t t = 0; t < T; t++) {
+            const ZoneTestRec &z = tests[t];
+            uint32_t x0 = zn_cell(z.minx, gx0, inv_cx, nx), x1 = zn_cell(z.maxx, gx0, inv_cx, nx);
+            uint32_t y0 = zn_cell(z.miny, gy0, inv_cy, ny), y1 = zn_cell(z.maxy, gy0, inv_cy, ny);
+            for (uint32_t cy = y0; cy <= y1; cy++)
+                for (uint32_t cx = x0; cx <= x1; cx++) cnt[(size_t)cy * nx + cx + 1]++;
+        }
+        for (size_t i = 1; i < cnt.size(); i++) cnt[i] += cnt[i - 1];
+        cell_start = cnt;
+        cell_items.assign(items, 0);
+        std::vector<uint32_t> fill(cnt.begin(), cnt.end() - 1);
+        for (uint32_t t = 0; t < T; t++) {  // ascending t => each cell list is in test order
+            const ZoneTestRec &z = tests[t];
+            uint32_t x0 = zn_cell(z.minx, gx0, inv_cx, nx), x1 = zn_cell(z.maxx, gx0, inv_cx, nx);
+            uint32_t y0 = zn_cell(z.miny, gy0, inv_cy, ny), y1 = zn_cell(z.maxy, gy0, inv_cy, ny);
+            for (uint32_t cy = y0; cy <= y1; cy++)
+                for (uint32_t cx = x0; cx <= x1; cx++) cell_items[fill[(size_t)cy * nx + cx]++] = t;
+        }
+        break;
+    }
+    ZoneHeader h;
+    memset(&h, 0, sizeof h);
+    h.magic = ZN_MAGIC;
+    h.n_tests = T;
+    h.n_outside = (uint32_t)outside.size();
+    h.grid_nx = nx;
+    h.grid_ny = ny;
+    h.gx0 = gx0;
+    h.gy0 = gy0;
+    h.gx1 = gx1;
+    h.gy1 = gy1;
+    h.inv_cx = inv_cx;
+    h.inv_cy = inv_cy;
+    size_t off = align_up(sizeof(ZoneHeader), 256);
+    h.off_tests = off;
+    off = align_up(off + tests.size() * sizeof(ZoneTestRec), 256);
+    h.off_verts = off;
+    off = align_up(off + verts.size() * 8, 256);
+    h.off_cell_start = off;
+    off = align_up(off + cell_start.size() * 4, 256);
+    h.off_cell_items = off;
+    off = align_up(off + cell_items.size() * 4, 256);
+    h.off_bin_start = off;
+    off = align_up(off + bin_start.size() * 4, 256);
+    h.off_bin_items = off;
+    off = align_up(off + bin_items.size() * 4, 256);
+    h.off_outside = off;
+    off = align_up(off + outside.size() * 4, 256);
+    h.total_bytes = off;
+    blob.assign(off, 0);
+    memcpy(blob.data(), &h, sizeof h);
+    if (!tests.empty()) memcpy(blob.data() + h.off_tests, tests.data(), tests.size() * sizeof(ZoneTestRec));
+    if (!verts.empty()) memcpy(blob.data() + h.off_verts, verts.data(), verts.size() * 8);
+    memcpy(blob.data() + h.off_cell_start, cell_start.data(), cell_start.size() * 4);
+    if (!cell_items.empty()) memcpy(blob.data() + h.off_cell_items, cell_items.data(), cell_items.size() * 4);
+    if (!bin_start.empty()) memcpy(blob.data() + h.off_bin_start, bin_start.data(), bin_start.size() * 4);
+    if (!bin_items.empty()) memcpy(blob.data() + h.off_bin_items, bin_items.data(), bin_items.size() * 4);
+    if (!outside.empty()) memcpy(blob.data() + h.off_outside, outside.data(), outside.size() * 4);
+    return SWGPU_OK;
+}
+
+void sw_zone_free(swgpu_ctx *ctx) {
+    if (ctx->zone_blob) cudaFree(ctx->zone_blob);
+    ctx->zone_blob = nullptr;
+    ctx->zone_bytes = 0;
+    delete (ZoneHeader *)ctx->zone_hdr;
+    ctx->zone_hdr = nullptr;
+}
+
+static int zone_install(swgpu_ctx *ctx, const void *src, uint64_t bytes, cudaMemcpyKind kind) {
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    void *nb = nullptr;
+    cudaError_t e = cudaMalloc(&nb, bytes);
+    if (e != cudaSuccess) {
+        SW_SET_ERR(ctx, "cudaMalloc(zone table %llu) failed: %s", (unsigned long long)bytes, cudaGetErrorString(e));
+        return SWGPU_E_NOMEM;
+    }
+    e = cudaMemcpyAsync(nb, src, bytes, kind, ctx->stream);
+    ZoneHeader *h = new ZoneHeader();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h, nb, sizeof(ZoneHeader), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess || h->magic != ZN_MAGIC || h->total_bytes != bytes) {
+        if (e != cudaSuccess)
+            SW_SET_ERR(ctx, "zone table upload failed: %s", cudaGetErrorString(e));
+        else
+            SW_SET_ERR(ctx, "zone table blob is not a swgpu zone table (bad magic/size)");
+        cudaFree(nb);
+        delete h;
+        return e != cudaSuccess ? SWGPU_E_CUDA : SWGPU_E_INVALID;
+    }
+    sw_zone_free(ctx);
+    ctx->zone_blob = nb;
+    ctx->zone_bytes = bytes;
+    ctx->zone_hdr = h;
+    return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_set_zones(swgpu_ctx *ctx, uint32_t n_tests, const uint32_t *vtx_off, const double *lon,
+                                   const double *lat, const uint8_t *cond) {
+    if (!ctx) return SWGPU_E_INVALID;
+    if (n_tests && (!vtx_off || !lon || !lat || !cond)) {
+        SW_SET_ERR(ctx, "swgpu_set_zones: NULL argument");
+        return SWGPU_E_INVALID;
+    }
+    std::vector<uint8_t> blob;
+    uint32_t zero_off[1] = {0};
+    if (int rc = build_zone_blob(ctx, n_tests, n_tests ? vtx_off : zero_off, lon, lat, cond, blob)) return rc;
+    return zone_install(ctx, blob.data(), blob.size(), cudaMemcpyHostToDevice);
+}
+
+extern "C" int32_t swgpu_zone_table_bytes(swgpu_ctx *ctx, uint64_t *out_bytes) {
+    if (!ctx || !out_bytes) return SWGPU_E_INVALID;
+    if (!ctx->zone_blob) {
+        SW_SET_ERR(ctx, "no zone table set");
+        return SWGPU_E_STATE;
+    }
+    *out_bytes = ctx->zone_bytes;
+    return SWGPU_OK;
+}
+extern "C" int32_t swgpu_zone_table_export_dev(swgpu_ctx *ctx, void *dst_dev, uint64_t capacity) {
+    if (!ctx || !dst_dev) return SWGPU_E_INVALID;
+    if (!ctx->zone_blob) {
+        SW_SET_ERR(ctx, "no zone table set");
+        return SWGPU_E_STATE;
+    }
+    if (capacity < ctx->zone_bytes) {
+        SW_SET_ERR(ctx, "zone table export: capacity %llu < %llu", (unsigned long long)capacity,
+                   (unsigned long long)ctx->zone_bytes);
+        return SWGPU_E_CAPACITY;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    SW_CUDA(ctx, cudaMemcpyAsync(dst_dev, ctx->zone_blob, ctx->zone_bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SWGPU_OK;
+}
+extern "C" int32_t swgpu_zone_table_import_dev(swgpu_ctx *ctx, const void *src_dev, uint64_t bytes) {
+    if (!ctx || !src_dev || bytes < sizeof(ZoneHeader)) return SWGPU_E_INVALID;
+    return zone_install(ctx, src_dev, bytes, cudaMemcpyDeviceToDevice);
+}
+
+// ---------------------------------------------------------------------------------------------
+// device
+struct ZnArgs {
+    const uint8_t *blob;
+    ZoneHeader h;
+    const double *lon, *lat;
+    const uint64_t *meta;
+    uint32_t n;
+    const uint32_t *n_rows_dev;
+    uint64_t max_pairs;
+    uint64_t *pairs;
+    uint64_t *n_pairs;
+    uint32_t *ticket;
+    uint64_t *tile_state;
+};
+
+// exact sign of x1*y2 - y1*x2: products with their rounding errors (fma), compared as the
+// monotone rounding of two reals; ties broken by the error terms.
+__device__ __forceinline__ int zn_sign_det(double x1, double y1, double x2, double y2) {
+    double p = __dmul_rn(x1, y2), q = __dmul_rn(y1, x2);
+    if (p > q) return 1;
+    if (p < q) return -1;
+    double e = __fma_rn(x1, y2, -p), f = __fma_rn(y1, x2, -q);
+    return (e > f) - (e < f);
+}
+
+// RayCrossingCounter.locatePointInRing(p, ring) == INTERIOR restricted to the slab's edges
+__device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, const ZoneTestRec &z, double px, double py) {
+    const double2 *v = (const double2 *)(a.blob + a.h.off_verts) + z.vtx_off;
+    const uint32_t *bs = (const uint32_t *)(a.blob + a.h.off_bin_start) + z.bin_off;
+    const uint32_t *bi = (const uint32_t *)(a.blob + a.h.off_bin_items);
+    uint32_t b = zn_cell(py, z.miny, z.inv_bin, z.nbins);
+    uint32_t k0 = __ldg(bs + b), k1 = __ldg(bs + b + 1);
+    uint32_t crossings = 0;
+    bool boundary = false;
+    for (uint32_t k = k0; k < k1; k++) {
+        uint32_t i = __ldg(bi + k);
+        double2 p1 = __ldg(v + i), p2 = __ldg(v + i - 1);
+        if (p1.x < px && p2.x < px) continue;
+        if (px == p2.x && py == p2.y) {
+            boundary = true;
+            break;
+        }
+        if (p1.y == py && p2.y == py) {
+            double mn = fmin(p1.x, p2.x), mx = fmax(p1.x, p2.x);
+            if (px >= mn && px <= mx) {
+                boundary = true;
+                break;
+            }
+            continue;
+        }
+        if ((p1.y > py && p2.y <= py) || (p2.y > py && p1.y <= py)) {
+            double x1 = __dsub_rn(p1.x, px), y1 = __dsub_rn(p1.y, py);
+            double x2 = __dsub_rn(p2.x, px), y2 = __dsub_rn(p2.y, py);
+            int s = zn_sign_det(x1, y1, x2, y2);
+            if (s == 0) {
+                boundary = true;
+                break;
+            }
+            if (y2 < y1) s = -s;
+            if (s > 0) crossings++;
+        }
+    }
+    return !boundary && (crossings & 1);
+}
+
+// Visit the tests whose polygon contains (px,py), in ascending test order.
+template <typename F>
+__device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, double py, F f) {
+    const ZoneHeader &h = a.h;
+    if (!(px >= h.gx0 && px <= h.gx1 && py >= h.gy0 && py <= h.gy1)) return;  // outside every envelope (or NaN)
+    uint32_t cx = zn_cell(px, h.gx0, h.inv_cx, h.grid_nx), cy = zn_cell(py, h.gy0, h.inv_cy, h.grid_ny);
+    const uint32_t *cs = (const uint32_t *)(a.blob + h.off_cell_start);
+    const uint32_t *ci = (const uint32_t *)(a.blob + h.off_cell_items);
+    const ZoneTestRec *tests = (const ZoneTestRec *)(a.blob + h.off_tests);
+    uint32_t c = cy * h.grid_nx + cx;
+    uint32_t k0 = __ldg(cs + c), k1 = __ldg(cs + c + 1);
+    for (uint32_t k = k0; k < k1; k++) {
+        uint32_t t = __ldg(ci + k);
+        const ZoneTestRec *zp = tests + t;
+        // envelope first (Geometry.contains short-circuit): one 32-byte sector
+        double2 ex = __ldg((const double2 *)zp), ey = __ldg((const double2 *)zp + 1);
+        if (!(px >= ex.x && px <= ex.y && py >= ey.x && py <= ey.y)) continue;
+        ZoneTestRec z;
+        z.minx = ex.x;
+        z.maxx = ex.y;
+        z.miny = ey.x;
+        z.maxy = ey.y;
+        uint4 m0 = __ldg((const uint4 *)zp + 2);
+        uint4 m1 = __ldg((const uint4 *)zp + 3);
+        z.vtx_off = m0.x;
+        z.npts = m0.y;
+        z.flags = m0.z;
+        z.nbins = m0.w;
+        z.inv_bin = __hiloint2double((int)m1.y, (int)m1.x);
+        z.bin_off = m1.z;
+        bool in;
+        if (z.flags & 2u)  // RectangleContains: not on the envelope border
+            in = !(px == z.minx || px == z.maxx || py == z.miny || py == z.maxy);
+        else
+            in = zn_ring_interior(a, z, px, py);
+        if (in) f(t, z.flags & 1u);
+    }
+}
+
+__global__ void __launch_bounds__(ZN_THREADS) zone_test_kernel(ZnArgs a) {
+    __shared__ uint64_t s_warp[ZN_THREADS / 32 + 2];
+    __shared__ uint32_t s_tile;
+    const uint32_t tid = threadIdx.x;
+    if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
+    const uint32_t i = tile * ZN_THREADS + tid;
+    const uint32_t T_out = a.h.n_outside;
+
+    bool valid = i < n_live;
+    if (valid && a.meta) {
+        uint64_t m = __ldg(a.meta + i);
+        uint32_t fl = SWGPU_META_FLAGS(m);
+        valid = SWGPU_META_KIND(m) == SWGPU_KIND_LOCATION && (fl & SWGPU_F_HAS_V0) && (fl & SWGPU_F_HAS_V1);
+    }
+    double px = 0, py = 0;
+    uint32_t ins[ZN_MAXIN];
+    uint32_t n_in = 0, n_in_icond = 0, n_in_ocond = 0;
+    if (valid) {
+        px = __ldg(a.lon + i);
+        py = __ldg(a.lat + i);
+        zn_for_each_inside(a, px, py, [&](uint32_t t, uint32_t outside_cond) {
+            if (n_in < ZN_MAXIN) ins[n_in] = (t << 1) | outside_cond;
+            n_in++;
+            if (outside_cond)
+                n_in_ocond++;
+            else
+                n_in_icond++;
+        });
+    }
+    // alerts: Inside-condition tests that contain the point + Outside-condition tests that do not
+    uint32_t count = valid ? (n_in_icond + (T_out - n_in_ocond)) : 0;
+    uint64_t tile_total;
+    uint64_t pos = sw_block_ordered_offset<ZN_THREADS>(count, a.tile_state, tile, s_warp, &tile_total);
+    // tiles are ordered by ticket, so the tile with the highest id is last: it publishes the total
+    if (tile == gridDim.x - 1 && tid == 0) *a.n_pairs = pos + tile_total;  // thread 0's offset = tile base
+    if (count) {
+        const uint64_t ev = (uint64_t)i << 32;
+        if (T_out == 0 && n_in <= ZN_MAXIN) {
+            for (uint32_t k = 0; k < n_in; k++, pos++)
+                if (pos < a.max_pairs) a.pairs[pos] = ev | (ins[k] >> 1);
+        } else if (n_in <= ZN_MAXIN) {
+            // merge (ascending): inside hits with Inside condition, and the Outside-condition list
+            // minus the tests that contain the point
+            const uint32_t *ol = (const uint32_t *)(a.blob + a.h.off_outside);
+            uint32_t k = 0, j = 0;
+            while (k < n_in || j < T_out) {
+                uint32_t ti = k < n_in ? (ins[k] >> 1) : 0xffffffffu;
+                uint32_t to = j < T_out ? __ldg(ol + j) : 0xffffffffu;
+                if (ti < to) {
+                    if (!(ins[k] & 1u)) {
+                        if (pos < a.max_pairs) a.pairs[pos] = ev | ti;
+                        pos++;
+                    }
+                    k++;
+                } else if (to < ti) {
+                    if (pos < a.max_pairs) a.pairs[pos] = ev | to;
+                    pos++;
+                    j++;
+                } else {  // same test: Outside condition but the point is inside -> no alert
+                    k++;
+                    j++;
+                }
+            }
+        } else {
+            // more containing zones than the register set holds (rare): walk every test in order and
+            // re-derive containment through the same visitor — slow, exact
+            const ZoneTestRec *tests = (const ZoneTestRec *)(a.blob + a.h.off_tests);
+            for (uint32_t t = 0; t < a.h.n_tests; t++) {
+                bool in = false;
+                zn_for_each_inside(a, px, py, [&](uint32_t tt, uint32_t) {
+                    if (tt == t) in = true;
+                });
+                bool outside_cond = (__ldg(&tests[t].flags) & 1u) != 0;
+                if (in != outside_cond) {
+                    if (pos < a.max_pairs) a.pairs[pos] = ev | t;
+                    pos++;
+                }
+            }
+        }
+    }
+}
+
+extern "C" int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta,
+                                       uint32_t n, const uint32_t *n_rows_dev, uint64_t max_pairs,
+                                       uint64_t *pairs, uint64_t *n_pairs_dev) {
+    if (!ctx) return SWGPU_E_INVALID;
+    if (!ctx->zone_blob) {
+        SW_SET_ERR(ctx, "swgpu_zone_test: no zone table (call swgpu_set_zones first)");
+        return SWGPU_E_STATE;
+    }
+    if (!n_pairs_dev || (n && (!lon || !lat)) || (max_pairs && !pairs)) {
+        SW_SET_ERR(ctx, "swgpu_zone_test_dev: NULL argument");
+        return SWGPU_E_INVALID;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (n == 0) {
+        SW_CUDA(ctx, cudaMemsetAsync(n_pairs_dev, 0, sizeof(uint64_t), ctx->stream));
+        return SWGPU_OK;
+    }
+    const uint32_t ntiles = (n + ZN_THREADS - 1) / ZN_THREADS;
+    const size_t sbytes = SW_SCRATCH_HDR + (size_t)ntiles * 8;
+    if (int rc = sw_ensure_scratch(ctx, sbytes)) return rc;
+    SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, sbytes, ctx->stream));
+    ZnArgs a;
+    a.blob = (const uint8_t *)ctx->zone_blob;
+    a.h = *(const ZoneHeader *)ctx->zone_hdr;
+    a.lon = lon;
+    a.lat = lat;
+    a.meta = meta;
+    a.n = n;
+    a.n_rows_dev = n_rows_dev;
+    a.max_pairs = max_pairs;
+    a.pairs = pairs;
+    a.n_pairs = n_pairs_dev;
+    a.ticket = (uint32_t *)ctx->scratch;
+    a.tile_state = (uint64_t *)((uint8_t *)ctx->scratch + SW_SCRATCH_HDR);
+    zone_test_kernel<<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a);
+    SW_CUDA(ctx, cudaGetLastError());
+    return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_zone_test(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta,
+                                   uint32_t n, uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs) {
+    if (!ctx) return SWGPU_E_INVALID;
+    if (!n_pairs || (n && (!lon || !lat)) || (max_pairs && !pairs)) {
+        SW_SET_ERR(ctx, "swgpu_zone_test: NULL argument");
+        return SWGPU_E_INVALID;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (int rc = sw_ensure(ctx, ctx->d_lon, (size_t)n * 8 + 16)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_lat, (size_t)n * 8 + 16)) return rc;
+    if (meta)
+        if (int rc = sw_ensure(ctx, ctx->d_meta, (size_t)n * 8 + 16)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_pairs, (size_t)max_pairs * 8 + 16)) return rc;
+    if (n) {
+        SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_lon.p, lon, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+        SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_lat.p, lat, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+        if (meta) SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_meta.p, meta, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    }
+    uint64_t *d_np = (uint64_t *)((uint8_t *)ctx->d_pairs.p + (size_t)max_pairs * 8);
+    int rc = swgpu_zone_test_dev(ctx, (const double *)ctx->d_lon.p, (const double *)ctx->d_lat.p,
+                                 meta ? (const uint64_t *)ctx->d_meta.p : nullptr, n, nullptr, max_pairs,
+                                 (uint64_t *)ctx->d_pairs.p, d_np);
+    if (rc) return rc;
+    SW_CUDA(ctx, cudaMemcpyAsync(n_pairs, d_np, 8, cudaMemcpyDeviceToHost, st));
+    SW_CUDA(ctx, cudaStreamSynchronize(st));
+    uint64_t live = *n_pairs < max_pairs ? *n_pairs : max_pairs;
+    if (live) {
+        SW_CUDA(ctx, cudaMemcpyAsync(pairs, ctx->d_pairs.p, live * 8, cudaMemcpyDeviceToHost, st));
+        SW_CUDA(ctx, cudaStreamSynchronize(st));
+    }
+    if (*n_pairs > max_pairs) {
+        SW_SET_ERR(ctx, "zone test produced %llu alerts but max_pairs is %llu", (unsigned long long)*n_pairs,
+                   (unsigned long long)max_pairs);
+        return SWGPU_E_CAPACITY;
+    }
+    return SWGPU_OK;
+}
