@@ -355,6 +355,7 @@ def main():
     ap.add_argument("--events", type=int, default=10_000_000, help="events per GPU per step")
     ap.add_argument("--cpu-events", type=int, default=0, help="CPU baseline sample size")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

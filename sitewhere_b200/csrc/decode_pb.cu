@@ -492,7 +492,7 @@ extern "C" int32_t swgpu_decode_pb_dev(swgpu_ctx *ctx, const uint8_t *bytes, con
                                        uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev) {
     if (!ctx) return SWGPU_E_INVALID;
     if (int rc = check_cols(ctx, out)) return rc;
-    if (!rec_off || !first_row || !out_rows_dev || (n && (!bytes || !status))) {
+    if (!rec_off || !first_row || !out_rows_dev || (n && !status)) {
         SW_SET_ERR(ctx, "swgpu_decode_pb_dev: NULL argument");
         return SWGPU_E_INVALID;
     }
@@ -530,7 +530,7 @@ int sw_stage_decode(swgpu_ctx *ctx, bool json, const uint8_t *bytes, const uint6
                     uint32_t *out_rows) {
     if (!ctx) return SWGPU_E_INVALID;
     if (int rc = check_cols(ctx, out)) return rc;
-    if (!rec_off || !first_row || !out_rows || (n && (!bytes || !status))) {
+    if (!rec_off || !first_row || !out_rows || (n && !status) || (rec_off[n] && !bytes)) {
         SW_SET_ERR(ctx, "swgpu_decode: NULL argument");
         return SWGPU_E_INVALID;
     }
