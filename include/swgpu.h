@@ -193,6 +193,25 @@ int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const double *lat
                             const uint64_t *meta, uint32_t n, const uint32_t *n_rows_dev,
                             uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev);
 
+/* Allocation-free form of swgpu_zone_test_dev.  It has no counterpart in the reference: it exists
+ * for callers of this library that must not allocate device memory while a batch is in flight —
+ * the rule-processing consumer thread when other contexts of the same process have work on the GPU
+ * (cudaMalloc / cudaFree stall every stream of the device), or a deployment whose memory budget is
+ * already spent on the state table, where a late scratch growth could fail mid-partition.
+ * Same arguments, outputs and ordering as swgpu_zone_test_dev; the caller still owns every input
+ * and output buffer.  The scan scratch is a fixed array inside the library image (512 KiB + 64 B
+ * per GPU, held until the process exits), so:
+ *   - n must not exceed SWGPU_NOALLOC_MAX_LOCATIONS, else SWGPU_E_CAPACITY and nothing is launched;
+ *   - the first call on each GPU resolves the array's device address (one-time set-up): make that
+ *     first call before starting any CUDA stream capture;
+ *   - all calls on a GPU share the one array (it is cleared at the start of each call): two calls
+ *     whose kernels can overlap on the GPU — different contexts or streams — race.  Serialise them.
+ * The call itself performs no cudaMalloc/cudaFree; it needs swgpu_set_zones to have been called.   */
+#define SWGPU_NOALLOC_MAX_LOCATIONS 16777216u
+int32_t swgpu_zone_test_noalloc_dev(swgpu_ctx *ctx, const double *lon, const double *lat,
+                                    const uint64_t *meta, uint32_t n, const uint32_t *n_rows_dev,
+                                    uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev);
+
 /* ---- device-state merge -------------------------------------------------------------------------
  * Replaces the fold DeviceStateProcessingLogic.processDeviceStateEvent + merge*
  * (DS/processing/DeviceStateProcessingLogic.java:116-201) with DeviceStatePersistence.deviceStateUpdateLogic

@@ -15,6 +15,7 @@ MANDATORY_COLS = COL_NAMES[:9]
 OK, E_INVALID, E_CUDA, E_NOMEM, E_CAPACITY, E_STATE = 0, -1, -2, -3, -4, -5
 ST_OK, ST_DECODE_EXCEPTION, ST_RUNTIME_EXCEPTION, ST_PASSTHROUGH = 0, 1, 2, 3
 KIND_MEASUREMENT, KIND_LOCATION, KIND_ALERT = 0, 1, 2
+NOALLOC_MAX_LOCATIONS = 1 << 24
 
 F_UPDATE_STATE = 1 << 0
 F_HAS_DATE = 1 << 1
@@ -70,6 +71,7 @@ SIGNATURES = {
     "swgpu_decode_json_dev": (_I32, [_P, _P, _P, _U32, _U32, _COLS, _P, _P, _P]),
     "swgpu_zone_test": (_I32, [_P, _P, _P, _P, _U32, _U64, _P, _P]),
     "swgpu_zone_test_dev": (_I32, [_P, _P, _P, _P, _U32, _P, _U64, _P, _P]),
+    "swgpu_zone_test_noalloc_dev": (_I32, [_P, _P, _P, _P, _U32, _P, _U64, _P, _P]),
     "swgpu_state_reserve": (_I32, [_P, _U64, _U64]),
     "swgpu_merge": (_I32, [_P, _P, _P, _U32, _COLS, _U32, _U64, _P, _P]),
     "swgpu_merge_dev": (_I32, [_P, _P, _P, _U32, _COLS, _U32, _P, _U64, _P, _P]),

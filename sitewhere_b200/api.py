@@ -237,6 +237,14 @@ class Context:
             n_rows_t.data_ptr() if n_rows_t is not None else None, pairs_t.numel(), pairs_t.data_ptr(),
             n_pairs_t.data_ptr()))
 
+    def zone_test_noalloc_dev(self, lon_t, lat_t, meta_t, n, n_rows_t, pairs_t, n_pairs_t):
+        """swgpu_zone_test_noalloc_dev: same as zone_test_dev, but the library allocates nothing
+        (fixed in-library scratch, at most NOALLOC_MAX_LOCATIONS locations per call)."""
+        self._check(self.lib.swgpu_zone_test_noalloc_dev(
+            self.h, lon_t.data_ptr(), lat_t.data_ptr(), meta_t.data_ptr() if meta_t is not None else None, int(n),
+            n_rows_t.data_ptr() if n_rows_t is not None else None, pairs_t.numel(), pairs_t.data_ptr(),
+            n_pairs_t.data_ptr()))
+
     # ---- merge ----------------------------------------------------------------------------------------
     def state_reserve(self, max_keys: int, max_key_bytes: int):
         self._check(self.lib.swgpu_state_reserve(self.h, int(max_keys), int(max_key_bytes)))

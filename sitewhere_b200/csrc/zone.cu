@@ -601,3 +601,93 @@ extern "C" int32_t swgpu_zone_test(swgpu_ctx *ctx, const double *lon, const doub
     }
     return SWGPU_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free zone test.
+//
+// swgpu_zone_test_dev grows the context's scan scratch with cudaMalloc when a batch is larger than
+// any before it.  Some callers of this library must not allocate at the moment they run a batch:
+//   * the rule-processing consumer thread shares the GPU with the decode and state-merge contexts of
+//     the same process; cudaMalloc / cudaFree synchronise the whole device, so a late scratch growth
+//     on this thread would stall every other stream's batches for its duration;
+//   * deployments that size the device-state table to fill the memory budget up front have no room
+//     left: a scratch growth in the middle of consuming a partition could fail with out-of-memory
+//     after offsets were already committed.
+// For them the scan scratch lives in this file-scope device array: it is part of the library image,
+// every GPU that loads libswgpu.so holds its 512 KiB + 64 B until the process exits, and a call
+// never allocates.  The price is a fixed upper bound on the batch (SWGPU_NOALLOC_MAX_LOCATIONS).
+#define ZN_NOALLOC_TILES (SWGPU_NOALLOC_MAX_LOCATIONS / ZN_THREADS)
+#define ZN_NOALLOC_BYTES (SW_SCRATCH_HDR + (size_t)ZN_NOALLOC_TILES * 8)
+static __device__ __align__(256) unsigned char g_zn_noalloc_scratch[ZN_NOALLOC_BYTES];
+
+// The array's name is only a host-side handle; kernels need its device address, which differs per
+// device.  It is looked up once per device (with that device current) and cached here.
+#define ZN_NOALLOC_MAX_DEVICES 64
+static std::mutex g_zn_noalloc_mu;
+static void *g_zn_noalloc_addr[ZN_NOALLOC_MAX_DEVICES] = {nullptr};
+
+extern "C" int32_t swgpu_zone_test_noalloc_dev(swgpu_ctx *ctx, const double *lon, const double *lat,
+                                               const uint64_t *meta, uint32_t n, const uint32_t *n_rows_dev,
+                                               uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev) {
+    if (!ctx) return SWGPU_E_INVALID;
+    if (!ctx->zone_blob) {
+        SW_SET_ERR(ctx, "swgpu_zone_test_noalloc_dev: no zone table (call swgpu_set_zones first)");
+        return SWGPU_E_STATE;
+    }
+    if (!n_pairs_dev || (n && (!lon || !lat)) || (max_pairs && !pairs)) {
+        SW_SET_ERR(ctx, "swgpu_zone_test_noalloc_dev: NULL argument");
+        return SWGPU_E_INVALID;
+    }
+    if (n > SWGPU_NOALLOC_MAX_LOCATIONS) {
+        SW_SET_ERR(ctx,
+                   "swgpu_zone_test_noalloc_dev: %u locations exceed the fixed scratch (at most %u per call); "
+                   "split the batch or use swgpu_zone_test_dev",
+                   n, (unsigned)SWGPU_NOALLOC_MAX_LOCATIONS);
+        return SWGPU_E_CAPACITY;
+    }
+    if (ctx->device < 0 || ctx->device >= ZN_NOALLOC_MAX_DEVICES) {
+        SW_SET_ERR(ctx, "swgpu_zone_test_noalloc_dev: device ordinal %d not supported (max %d)", ctx->device,
+                   ZN_NOALLOC_MAX_DEVICES - 1);
+        return SWGPU_E_INVALID;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    void *scratch = nullptr;
+    {
+        // first call on this device: resolve the device address of the static array (set-up step)
+        std::lock_guard<std::mutex> lk(g_zn_noalloc_mu);
+        if (!g_zn_noalloc_addr[ctx->device]) {
+            void *p = nullptr;
+            cudaError_t e = cudaGetSymbolAddress(&p, g_zn_noalloc_scratch);
+            if (e != cudaSuccess || !p) {
+                SW_SET_ERR(ctx, "cudaGetSymbolAddress(noalloc scratch) failed on device %d: %s", ctx->device,
+                           cudaGetErrorString(e));
+                return SWGPU_E_CUDA;
+            }
+            g_zn_noalloc_addr[ctx->device] = p;
+        }
+        scratch = g_zn_noalloc_addr[ctx->device];
+    }
+    if (n == 0) {
+        SW_CUDA(ctx, cudaMemsetAsync(n_pairs_dev, 0, sizeof(uint64_t), ctx->stream));
+        return SWGPU_OK;
+    }
+    // the array still holds the previous call's ticket and tile states: both must start at zero
+    const uint32_t ntiles = (n + ZN_THREADS - 1) / ZN_THREADS;
+    SW_CUDA(ctx, cudaMemsetAsync(scratch, 0, SW_SCRATCH_HDR + (size_t)ntiles * 8, ctx->stream));
+    ZnArgs a;
+    a.blob = (const uint8_t *)ctx->zone_blob;
+    a.h = *(const ZoneHeader *)ctx->zone_hdr;
+    a.lon = lon;
+    a.lat = lat;
+    a.meta = meta;
+    a.n = n;
+    a.n_rows_dev = n_rows_dev;
+    a.max_pairs = max_pairs;
+    a.pairs = pairs;
+    a.n_pairs = n_pairs_dev;
+    a.ticket = (uint32_t *)scratch;
+    a.tile_state = (uint64_t *)((uint8_t *)scratch + SW_SCRATCH_HDR);
+    zone_test_kernel<<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a);
+    SW_CUDA(ctx, cudaGetLastError());
+    return SWGPU_OK;
+}
