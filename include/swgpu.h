@@ -85,7 +85,12 @@ extern "C" {
 #define SWGPU_F_STR_ESCAPED (1u << 9)   /* some JSON string span holds backslash escapes       */
 #define SWGPU_F_HAS_NAME (1u << 10)     /* measurement name / alert type is non-null           */
 #define SWGPU_F_HAS_MESSAGE (1u << 11)  /* alert message is non-null                           */
-#define SWGPU_F_NAME_COERCED (1u << 12) /* JSON name/type/message given as number/bool token   */
+#define SWGPU_F_NAME_COERCED (1u << 12) /* JSON message/alternateId given as number/bool token:
+                                           the span is the raw token, Jackson re-renders it        */
+#define SWGPU_F_NULL_REQUEST (1u << 13) /* JSON "request":null -> DecodedDeviceRequest with a null
+                                           request (dropped later at ES/EventSourcesManager.java:155) */
+#define SWGPU_F_NULL_LEVEL (1u << 14)   /* JSON alert "level":null                              */
+#define SWGPU_F_NULL_SOURCE (1u << 15)  /* JSON alert "source":null                             */
 
 /* A span is  (offset_in_record | length << 32); bytes are the caller's payload bytes.        */
 #define SWGPU_SPAN_OFF(s) ((uint32_t)((s) & 0xffffffffu))
