@@ -264,6 +264,11 @@ int32_t swgpu_state_clear(swgpu_ctx *ctx);
  * ES/EventSourcesManager.java:163):  toPositive(murmur2(utf8(key))) % n_partitions.
  * Host helper (no GPU): the shard a token belongs to.                                          */
 uint32_t swgpu_murmur2(const uint8_t *key, uint32_t len);
+/* Host helper (no GPU): decimal text -> double with the routine the JSON kernel uses, bit-exact with
+ * java.lang.Double.parseDouble on [+-]?digits[.digits][(e|E)[+-]digits] (what Jackson hands it for a
+ * number token, JsonDeviceRequestMarshaler.java:97-160 via treeToValue).  For bindings that coerce a
+ * numeric string themselves.                                                                      */
+int32_t swgpu_parse_double(const char *text, uint32_t len, double *out);
 uint32_t swgpu_partition(const uint8_t *key, uint32_t len, uint32_t n_partitions);
 
 #ifdef __cplusplus

@@ -80,6 +80,7 @@ SIGNATURES = {
     "swgpu_state_restore": (_I32, [_P, _ROWS, _U64]),
     "swgpu_state_clear": (_I32, [_P]),
     "swgpu_murmur2": (_U32, [_P, _U32]),
+    "swgpu_parse_double": (_I32, [C.c_char_p, _U32, C.POINTER(C.c_double)]),
     "swgpu_partition": (_U32, [_P, _U32, _U32]),
 }
 
