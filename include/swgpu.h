@@ -198,6 +198,25 @@ int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const double *lat
                             const uint64_t *meta, uint32_t n, const uint32_t *n_rows_dev,
                             uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev);
 
+/* ---- fused host-buffer path ------------------------------------------------------------------------
+ * Decode + zone test of one micro-batch held in HOST memory, in one call: what the Java binding's
+ * micro-batcher issues per batch.  Replaces IDeviceEventDecoder.decode per payload
+ * (ES/spi/IDeviceEventDecoder.java:39) followed by ZoneTestRuleProcessor.onLocation per decoded location
+ * (RP/processors/geospatial/ZoneTestRuleProcessor.java:47-63).  The batch is processed in chunks of
+ * `chunk_records` records (0 = default 262,144) through a three-slot device ring so that the copy-in of
+ * the next chunk, the kernels of the current one and the copy-out of the previous one overlap; for
+ * that the caller's buffers should come from swgpu_alloc_pinned (pageable memory works, slower).
+ * Outputs are exactly those of swgpu_decode_{pb,json} followed by swgpu_zone_test on the decoded
+ * lon/lat/meta columns: rows in reference order, `first_row` / `status` per record, alert pairs
+ * (row << 32 | test) in the order the reference would call addDeviceAlerts.  In `out` EVERY column
+ * pointer may be NULL (not copied back); `status` and `first_row` may be NULL too.                  */
+#define SWGPU_FMT_PROTOBUF 0
+#define SWGPU_FMT_JSON 1
+int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off,
+                               uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
+                               uint32_t *first_row, uint32_t *out_rows, uint64_t max_pairs, uint64_t *pairs,
+                               uint64_t *n_pairs, uint32_t chunk_records);
+
 /* Allocation-free form of swgpu_zone_test_dev.  It has no counterpart in the reference: it exists
  * for callers of this library that must not allocate device memory while a batch is in flight —
  * the rule-processing consumer thread when other contexts of the same process have work on the GPU

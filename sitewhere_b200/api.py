@@ -237,6 +237,37 @@ class Context:
             n_rows_t.data_ptr() if n_rows_t is not None else None, pairs_t.numel(), pairs_t.data_ptr(),
             n_pairs_t.data_ptr()))
 
+    # ---- fused host-buffer path (chunked, overlapped) -------------------------------------------------
+    def decode_zone_test(self, fmt: str, data, rec_off, cols: "HostCols" = None, status=None, first_row=None,
+                         pairs=None, chunk_records: int = 0):
+        """swgpu_decode_zone_test: decode + zone test of a host-resident batch in one call.
+        Returns (cols, status, first_row, n_rows, pairs[:n_pairs]).  Pass buffers from
+        :func:`pinned_array` to let copies and kernels overlap."""
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
+        n = rec_off.shape[0] - 1
+        if cols is None:
+            cols = HostCols(max(n, 1))
+        if status is None:
+            status = np.zeros(max(n, 1), dtype=np.uint8)
+        if first_row is None:
+            first_row = np.zeros(n + 1, dtype=np.uint32)
+        if pairs is None:
+            pairs = np.zeros(max(n, 1024), dtype=np.uint64)
+        out_rows, n_pairs = C.c_uint32(), C.c_uint64()
+        s = cols.struct()
+        rc = self.lib.swgpu_decode_zone_test(
+            self.h, 1 if fmt == "json" else 0, data.ctypes.data if data.size else None, rec_off.ctypes.data, n,
+            cols.capacity, C.byref(s), status.ctypes.data, first_row.ctypes.data, C.byref(out_rows), pairs.shape[0],
+            pairs.ctypes.data, C.byref(n_pairs), int(chunk_records))
+        if rc == L.E_CAPACITY:
+            big = HostCols(max(int(out_rows.value), 1))
+            return self.decode_zone_test(fmt, data, rec_off, big, status, first_row,
+                                         np.zeros(max(int(n_pairs.value), 1), np.uint64), chunk_records)
+        self._check(rc)
+        cols.n = int(out_rows.value)
+        return cols, status[:n], first_row, cols.n, pairs[: int(n_pairs.value)]
+
     def zone_test_noalloc_dev(self, lon_t, lat_t, meta_t, n, n_rows_t, pairs_t, n_pairs_t):
         """swgpu_zone_test_noalloc_dev: same as zone_test_dev, but the library allocates nothing
         (fixed in-library scratch, at most NOALLOC_MAX_LOCATIONS locations per call)."""
@@ -307,6 +338,50 @@ class Context:
         for k in arrs:
             setattr(s, k, arrs[k].ctypes.data if arrs[k].size else None)
         self._check(self.lib.swgpu_state_restore(self.h, C.byref(s), n))
+
+
+class _Pinned:
+    """Owner of one swgpu_alloc_pinned block."""
+
+    def __init__(self, nbytes: int):
+        self.lib = L.load()
+        self.ptr = self.lib.swgpu_alloc_pinned(max(int(nbytes), 1))
+        if not self.ptr:
+            raise MemoryError(f"swgpu_alloc_pinned({nbytes}) failed")
+        self.nbytes = int(nbytes)
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                self.lib.swgpu_free_pinned(self.ptr)
+                self.ptr = None
+        except Exception:
+            pass
+
+
+def pinned_array(shape, dtype) -> np.ndarray:
+    """numpy array in page-locked host memory (swgpu_alloc_pinned), as the Java binding's staging
+    segments are.  The block is freed when the array (and its views) are garbage-collected."""
+    dt = np.dtype(dtype)
+    n = int(np.prod(shape))
+    owner = _Pinned(n * dt.itemsize)
+    buf = (C.c_uint8 * max(n * dt.itemsize, 1)).from_address(owner.ptr)
+    arr = np.frombuffer(buf, dtype=dt, count=n).reshape(shape)
+    buf._owner = owner  # the array references buf, buf references the owner: freed with the last view
+    return arr
+
+
+def pinned_cols(capacity: int, names=None) -> "HostCols":
+    """HostCols whose (selected) columns live in pinned memory; unselected columns are None."""
+    hc = HostCols.__new__(HostCols)
+    hc.capacity = int(capacity)
+    hc.n = 0
+    for name in L.COL_NAMES:
+        if names is None or name in names:
+            setattr(hc, name, pinned_array((max(capacity, 1),), _COL_DT.get(name, np.uint64)))
+        else:
+            setattr(hc, name, None)
+    return hc
 
 
 def murmur2(key: bytes) -> int:

@@ -110,17 +110,19 @@ extern "C" int32_t swgpu_create(int32_t device_ordinal, void *stream, swgpu_ctx 
 
 void sw_zone_free(swgpu_ctx *ctx);   // zone.cu
 void sw_state_free(swgpu_ctx *ctx);  // merge.cu
+void sw_pipeline_free(swgpu_ctx *ctx);  // pipeline.cu
 
 extern "C" void swgpu_destroy(swgpu_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     swgpu_ctx::Buf *bufs[] = {&ctx->d_bytes, &ctx->d_off, &ctx->d_status, &ctx->d_first, &ctx->d_cols,
-                              &ctx->d_pairs, &ctx->d_lon, &ctx->d_lat, &ctx->d_meta, &ctx->d_ids};
+                              &ctx->d_pairs, &ctx->d_lon, &ctx->d_lat, &ctx->d_meta, &ctx->d_ids, &ctx->d_zwork};
     for (auto *b : bufs)
         if (b->p) cudaFree(b->p);
     if (ctx->h_small.p) cudaFreeHost(ctx->h_small.p);
     if (ctx->scratch) cudaFree(ctx->scratch);
+    sw_pipeline_free(ctx);
     sw_zone_free(ctx);
     sw_state_free(ctx);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);

@@ -16,7 +16,8 @@
 #include "swgpu_common.cuh"
 
 #define JS_THREADS 128
-#define JS_STAGE (48 * 1024)
+#define JS_WARPS (JS_THREADS / 32)
+#define JS_WSTAGE (12 * 1024)  // bytes staged per warp tile: 32 records of up to 384 B on average
 #define JS_MAX_DEPTH 256
 
 struct JsArgs {
@@ -30,6 +31,10 @@ struct JsArgs {
     uint32_t *out_rows;
     uint32_t *ticket;
     uint64_t *tile_state;
+    uint32_t rec_base;
+    const uint32_t *row_base;
+    uint32_t *row_next;
+    uint32_t *not_dense;
 };
 
 enum { JK_NONE = 0, JK_OBJECT, JK_ARRAY, JK_STRING, JK_INT, JK_FLOAT, JK_TRUE, JK_FALSE, JK_NULL };
@@ -905,46 +910,69 @@ __device__ void json_decode_record(B bytes, uint32_t n, uint32_t rec, JsRow &r) 
     r.status = SWGPU_ST_OK;
 }
 
+template <bool DENSE>
 __global__ void __launch_bounds__(JS_THREADS) json_decode_kernel(JsArgs a) {
-    extern __shared__ __align__(16) uint8_t smem[];  // JS_STAGE + 64
+    // as in the protobuf decoder: the CTA owns a tile of JS_THREADS records in the ordered scan; each warp
+    // stages and decodes its own 32 records (no block barrier for staging)
+    // DENSE = true: optimistic pass, row index = record index, no inter-tile dependency; raises *not_dense
+    // when some record does not decode to exactly one row.  DENSE = false: ordered redo, returns at once
+    // unless *not_dense was raised.  (Same scheme as pb_decode_kernel.)
+    extern __shared__ __align__(16) uint8_t smem[];  // JS_WARPS * (JS_WSTAGE + 32)
     __shared__ uint64_t s_warp[JS_THREADS / 32 + 2];
     __shared__ uint32_t s_tile;
-    const uint32_t tid = threadIdx.x;
-    if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
-    __syncthreads();
-    const uint32_t tile = s_tile;
-    const uint32_t rec0 = tile * JS_THREADS;
-    const uint32_t nrec = min((uint32_t)JS_THREADS, a.n - rec0);
-    const uint64_t b0 = a.rec_off[rec0], b1 = a.rec_off[rec0 + nrec];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (!DENSE) {
+        if (__ldg(a.not_dense) == 0) return;
+        if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
+        __syncthreads();
+    }
+    const uint32_t tile = DENSE ? blockIdx.x : s_tile;
+    const uint64_t rec0_64 = (uint64_t)tile * JS_THREADS + warp * 32;
+    const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
+    const uint32_t nrec = min(32u, a.n - rec0);
+    uint8_t *ws = smem + warp * (JS_WSTAGE + 32);
+    uint64_t r0 = 0, r1 = 0;
+    if (lane < nrec) {
+        r0 = a.rec_off[rec0 + lane];
+        r1 = a.rec_off[rec0 + lane + 1];
+    }
+    const uint64_t b0 = __shfl_sync(SW_FULL, r0, 0);
+    const uint64_t b1 = __shfl_sync(SW_FULL, r1, nrec ? nrec - 1 : 0);
     const uintptr_t addr = (uintptr_t)(a.bytes + b0);
     const uint32_t lead = (uint32_t)(addr & 15);
     const uint64_t span = (uint64_t)lead + (b1 - b0);
-    const bool staged = span <= JS_STAGE;
-    if (staged) {
+    const bool staged = span <= JS_WSTAGE;
+    if (staged && nrec) {
         const uint4 *src = (const uint4 *)(addr - lead);
-        uint4 *dst = (uint4 *)smem;
+        uint4 *dst = (uint4 *)ws;
         const uint32_t nvec = (uint32_t)((span + 15) >> 4);
-        for (uint32_t i = tid; i < nvec; i += JS_THREADS) dst[i] = sw_ld_stream_u4(src + i);
-        __syncthreads();
+        for (uint32_t i = lane; i < nvec; i += 32) dst[i] = sw_ld_stream_u4(src + i);
     }
+    __syncwarp();
     JsRow r;
     r.status = 0;
     uint32_t count = 0;
-    if (tid < nrec) {
-        const uint64_t r0 = a.rec_off[rec0 + tid];
-        const uint64_t l64 = a.rec_off[rec0 + tid + 1] - r0;
+    if (lane < nrec) {
+        const uint64_t l64 = r1 - r0;
         const uint32_t len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
         if (staged)
-            json_decode_record(SmemBytes{smem + lead + (uint32_t)(r0 - b0)}, len, rec0 + tid, r);
+            json_decode_record(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, len, a.rec_base + rec0 + lane, r);
         else
-            json_decode_record(GmemBytes{a.bytes + r0}, len, rec0 + tid, r);
+            json_decode_record(GmemBytes{a.bytes + r0}, len, a.rec_base + rec0 + lane, r);
         count = r.status == SWGPU_ST_OK ? 1u : 0u;
     }
-    uint64_t tile_total;
-    const uint64_t row = sw_block_ordered_offset<JS_THREADS>(count, a.tile_state, tile, s_warp, &tile_total);
-    if (tid < nrec) {
-        a.status[rec0 + tid] = (uint8_t)r.status;
-        a.first_row[rec0 + tid] = (uint32_t)row;
+    uint64_t tile_total = 0, row;
+    if (DENSE) {
+        row = (uint64_t)rec0 + lane;
+        if (lane < nrec && count != 1) atomicOr(a.not_dense, 1u);
+    } else {
+        row = sw_block_ordered_offset<JS_THREADS>(count, a.tile_state, tile, s_warp, &tile_total);
+    }
+    const uint64_t row_base = a.row_base ? (uint64_t)__ldg(a.row_base) : 0ull;
+    const uint32_t tid_rec = lane;  // record index within the tile
+    if (lane < nrec) {
+        a.status[rec0 + tid_rec] = (uint8_t)r.status;
+        a.first_row[rec0 + tid_rec] = (uint32_t)(row_base + row);
         if (count && row < a.max_rows) {
             a.cols.meta[row] = r.meta;
             a.cols.token_hash[row] = r.th;
@@ -961,10 +989,11 @@ __global__ void __launch_bounds__(JS_THREADS) json_decode_kernel(JsArgs a) {
             if (a.cols.alternate_id_span) a.cols.alternate_id_span[row] = r.aspan;
         }
     }
-    if (rec0 + nrec == a.n && tid == 0) {
-        const uint64_t total = row + tile_total;
-        a.first_row[a.n] = (uint32_t)total;
+    if ((uint64_t)tile * JS_THREADS + JS_THREADS >= a.n && tid == 0) {  // the tile holding the last record
+        const uint64_t total = DENSE ? (uint64_t)a.n : row + tile_total;
+        a.first_row[a.n] = (uint32_t)(row_base + total);
         *a.out_rows = (uint32_t)total;
+        if (a.row_next) *a.row_next = (uint32_t)(row_base + total);
     }
 }
 
@@ -972,9 +1001,9 @@ int sw_stage_decode(swgpu_ctx *ctx, bool json, const uint8_t *bytes, const uint6
                     uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row,
                     uint32_t *out_rows);
 
-extern "C" int32_t swgpu_decode_json_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
-                                         uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
-                                         uint32_t *first_row, uint32_t *out_rows_dev) {
+int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
+                          const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev,
+                          uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next) {
     if (!ctx) return SWGPU_E_INVALID;
     if (!out || !out->meta || !out->token_hash || !out->name_hash || !out->event_date || !out->v0 || !out->v1 ||
         !out->v2 || !out->token_span || !out->name_span) {
@@ -992,7 +1021,7 @@ extern "C" int32_t swgpu_decode_json_dev(swgpu_ctx *ctx, const uint8_t *bytes, c
         return SWGPU_OK;
     }
     const uint32_t ntiles = (n + JS_THREADS - 1) / JS_THREADS;
-    const size_t sbytes = SW_SCRATCH_HDR + (size_t)ntiles * 8;
+    const size_t sbytes = SW_SCRATCH_HDR + (size_t)ntiles * 8;  // one scan state per tile
     if (int rc = sw_ensure_scratch(ctx, sbytes)) return rc;
     SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, sbytes, ctx->stream));
     JsArgs a;
@@ -1006,11 +1035,25 @@ extern "C" int32_t swgpu_decode_json_dev(swgpu_ctx *ctx, const uint8_t *bytes, c
     a.out_rows = out_rows_dev;
     a.ticket = (uint32_t *)ctx->scratch;
     a.tile_state = (uint64_t *)((uint8_t *)ctx->scratch + SW_SCRATCH_HDR);
-    const int smem = JS_STAGE + 64;
-    SW_CUDA(ctx, cudaFuncSetAttribute(json_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    json_decode_kernel<<<ntiles, JS_THREADS, smem, ctx->stream>>>(a);
+    a.rec_base = rec_base;
+    a.row_base = row_base;
+    a.row_next = row_next;
+    a.not_dense = (uint32_t *)ctx->scratch + 1;
+    const int smem = JS_WARPS * (JS_WSTAGE + 32);
+    SW_CUDA(ctx, cudaFuncSetAttribute(json_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SW_CUDA(ctx, cudaFuncSetAttribute(json_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    json_decode_kernel<true><<<ntiles, JS_THREADS, smem, ctx->stream>>>(a);   // optimistic: rows = records
+    SW_CUDA(ctx, cudaGetLastError());
+    json_decode_kernel<false><<<ntiles, JS_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_decode_json_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
+                                         uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
+                                         uint32_t *first_row, uint32_t *out_rows_dev) {
+    return sw_decode_json_launch(ctx, bytes, rec_off, n, max_rows, out, status, first_row, out_rows_dev, 0, nullptr,
+                                 nullptr);
 }
 
 extern "C" int32_t swgpu_decode_json(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,

@@ -11,7 +11,8 @@
 #include "swgpu_common.cuh"
 
 #define PB_THREADS 256
-#define PB_STAGE (40 * 1024)  // bytes of payload staged per tile (avg record may be up to 160 B)
+#define PB_WARPS (PB_THREADS / 32)
+#define PB_WSTAGE 4608  // bytes of payload staged per warp tile (32 records of up to 144 B on average)
 #define PB_MAX_GROUP_DEPTH 16
 
 struct PbArgs {
@@ -25,6 +26,11 @@ struct PbArgs {
     uint32_t *out_rows;
     uint32_t *ticket;
     uint64_t *tile_state;
+    // chunked pipeline: global index of record 0, running row total before / after this launch
+    uint32_t rec_base;
+    const uint32_t *row_base;
+    uint32_t *row_next;
+    uint32_t *not_dense;  // raised by the dense pass when some record does not yield exactly one row
 };
 
 template <typename B>
@@ -238,8 +244,73 @@ struct PbOut {
     uint64_t v0, v1, v2;  // raw bits
 };
 
+// Recogniser for the exact byte layouts ProtobufDeviceEventEncoder emits
+// (ES/decoder/protobuf/ProtobufDeviceEventEncoder.java:60-176: Header{command}, then hardwareId, the event
+// fields in field-number order and eventDate; every length below 128).  A record of that shape decodes
+// to the same result through the generic wire walker below; this path only gets there in a few dozen
+// instructions.  Anything else (originator, metadata, updateState, several measurements, long strings,
+// unknown fields, damage) takes the generic path.
+template <typename B>
+__device__ __forceinline__ bool pb_fast_path(const B &bytes, uint32_t total, PbOut &o) {
+    if (total < 15 || total > 131) return false;
+    const uint64_t h = bytes.le64(0);  // 02 08 cmd LL 0A TL ..
+    const uint32_t cmd = (uint32_t)(h >> 16) & 0xff, LL = (uint32_t)(h >> 24) & 0xff, TL = (uint32_t)(h >> 40) & 0xff;
+    if ((h & 0xffff) != 0x0802u || ((h >> 32) & 0xff) != 0x0A || LL != total - 4 || (TL & 0x80)) return false;
+    uint32_t p = 6 + TL;  // first byte after the token
+    o.hw_off = 6;
+    o.hw_len = TL;
+    o.orig_off = o.orig_len = o.name_off = o.name_len = o.msg_off = o.msg_len = 0;
+    o.md_first = o.md_count = 0;
+    o.v0 = o.v1 = o.v2 = 0;
+    o.body_pos = 4;
+    o.body_end = total;
+    if (cmd == 3) {
+        if (LL != TL + 38) return false;
+        if (bytes.byte(p) != 0x11 || bytes.byte(p + 9) != 0x19 || bytes.byte(p + 18) != 0x21 || bytes.byte(p + 27) != 0x29)
+            return false;
+        o.v0 = bytes.le64(p + 1);
+        o.v1 = bytes.le64(p + 10);
+        o.v2 = bytes.le64(p + 19);
+        o.date = (int64_t)bytes.le64(p + 28);
+        o.flags = SWGPU_F_HAS_DATE | SWGPU_F_HAS_V0 | SWGPU_F_HAS_V1 | SWGPU_F_HAS_V2;
+    } else if (cmd == 5) {
+        if (p + 4 > total || bytes.byte(p) != 0x12) return false;
+        const uint32_t ML = bytes.byte(p + 1), NL = bytes.byte(p + 3);
+        if (bytes.byte(p + 2) != 0x0A || ((NL | ML) & 0x80) || ML != NL + 11 || LL != TL + 2 + 2 + ML + 9) return false;
+        const uint32_t q = p + 4 + NL;
+        if (bytes.byte(q) != 0x11 || bytes.byte(q + 9) != 0x19) return false;
+        o.name_off = p + 4;
+        o.name_len = NL;
+        o.v0 = bytes.le64(q + 1);
+        o.date = (int64_t)bytes.le64(q + 10);
+        o.flags = SWGPU_F_HAS_DATE | SWGPU_F_HAS_NAME | SWGPU_F_HAS_V0;
+    } else if (cmd == 4) {
+        if (p + 2 > total || bytes.byte(p) != 0x12) return false;
+        const uint32_t AL = bytes.byte(p + 1);
+        if (AL & 0x80) return false;
+        const uint32_t q = p + 2 + AL;
+        if (q + 2 > total || bytes.byte(q) != 0x1A) return false;
+        const uint32_t ML = bytes.byte(q + 1);
+        if ((ML & 0x80) || LL != TL + 2 + AL + 2 + ML + 2 + 9) return false;
+        const uint32_t d = q + 2 + ML;
+        if (bytes.byte(d) != 0x21) return false;
+        o.name_off = p + 2;
+        o.name_len = AL;
+        o.msg_off = q + 2;
+        o.msg_len = ML;
+        o.date = (int64_t)bytes.le64(d + 1);
+        o.flags = SWGPU_F_HAS_DATE | SWGPU_F_HAS_NAME | SWGPU_F_HAS_MESSAGE;
+    } else
+        return false;
+    o.status = SWGPU_ST_OK;
+    o.cmd = cmd;
+    o.count = 1;
+    return true;
+}
+
 template <typename B>
 __device__ void pb_parse_record(B bytes, uint32_t total, PbOut &o) {
+    if (pb_fast_path(bytes, total, o)) return;
     PbReader<B> r;
     r.b = bytes;
     o.count = 0;
@@ -394,7 +465,7 @@ template <typename B>
 __device__ __forceinline__ void pb_write_rows(const PbArgs &a, B bytes, const PbOut &o, uint32_t rec,
                                               uint64_t row0) {
     const uint32_t kind = o.cmd == 3 ? SWGPU_KIND_LOCATION : (o.cmd == 4 ? SWGPU_KIND_ALERT : SWGPU_KIND_MEASUREMENT);
-    const uint64_t meta = sw_mk_meta(kind, o.flags, 0, 0, 1, kind, rec);
+    const uint64_t meta = sw_mk_meta(kind, o.flags, 0, 0, 1, kind, a.rec_base + rec);
     const uint64_t th = sw_hash64(bytes, o.hw_off, o.hw_len);
     const uint64_t tspan = sw_mk_span(o.hw_off, o.hw_len);
     const uint64_t ospan = (o.flags & SWGPU_F_HAS_ORIGINATOR) ? sw_mk_span(o.orig_off, o.orig_len) : 0;
@@ -422,59 +493,89 @@ __device__ __forceinline__ void pb_write_rows(const PbArgs &a, B bytes, const Pb
     }
 }
 
+// A CTA owns a tile of 256 consecutive records (its position in the ordered scan); inside it every WARP
+// stages the contiguous bytes of its own 32 records into its private slice of shared memory (coalesced
+// 16-byte streaming loads, __syncwarp only) and each lane walks one record.  The only block barriers are
+// the ticket and the two of the ordered scan.
+//
+// Two instantiations, launched back to back on the same stream:
+//   DENSE = true   the optimistic pass.  Almost every batch is "dense": each record decodes to exactly one
+//                  row, so row index = record index and no tile depends on another — no ticket, no scan, no
+//                  waiting; the kernel runs at the speed of its memory traffic.  A record that yields 0 rows
+//                  (failed / pass-through / empty DeviceMeasurements) or several raises *not_dense.
+//   DENSE = false  the ordered pass (ticketed tiles + decoupled look-back).  It returns at once unless
+//                  *not_dense was raised; then it redoes the batch with exact ordered placement.  In that
+//                  pass every tile waits for the slowest of the few hundred tiles in flight, which is why
+//                  it is ~2.5x slower than the dense pass (measured; DESIGN.md "ordered placement").
+template <bool DENSE>
 __global__ void __launch_bounds__(PB_THREADS) pb_decode_kernel(PbArgs a) {
-    extern __shared__ __align__(16) uint8_t smem[];  // PB_STAGE + 64
+    extern __shared__ __align__(16) uint8_t smem[];  // PB_WARPS * (PB_WSTAGE + 32)
     __shared__ uint64_t s_warp[PB_THREADS / 32 + 2];
     __shared__ uint32_t s_tile;
-    const uint32_t tid = threadIdx.x;
-    if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
-    __syncthreads();
-    const uint32_t tile = s_tile;
-    const uint32_t rec0 = tile * PB_THREADS;
-    const uint32_t nrec = min((uint32_t)PB_THREADS, a.n - rec0);
-    const uint64_t b0 = a.rec_off[rec0], b1 = a.rec_off[rec0 + nrec];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (!DENSE) {
+        if (__ldg(a.not_dense) == 0) return;  // the dense pass was exact: nothing to redo
+        if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
+        __syncthreads();
+    }
+    const uint32_t tile = DENSE ? blockIdx.x : s_tile;  // ordered pass: tickets are handed out in start order
+    const uint64_t rec0_64 = (uint64_t)tile * PB_THREADS + warp * 32;
+    const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
+    const uint32_t nrec = min(32u, a.n - rec0);  // 0 for the padding warps of the last CTA
+    uint8_t *ws = smem + warp * (PB_WSTAGE + 32);
+    uint64_t r0 = 0, r1 = 0;
+    if (lane < nrec) {
+        r0 = a.rec_off[rec0 + lane];
+        r1 = a.rec_off[rec0 + lane + 1];
+    }
+    const uint64_t b0 = __shfl_sync(SW_FULL, r0, 0);
+    const uint64_t b1 = __shfl_sync(SW_FULL, r1, nrec ? nrec - 1 : 0);
     const uintptr_t addr = (uintptr_t)(a.bytes + b0);
     const uint32_t lead = (uint32_t)(addr & 15);
     const uint64_t span = (uint64_t)lead + (b1 - b0);
-    const bool staged = span <= PB_STAGE;
-    if (staged) {
+    const bool staged = span <= PB_WSTAGE;
+    if (staged && nrec) {
         const uint4 *src = (const uint4 *)(addr - lead);
-        uint4 *dst = (uint4 *)smem;
+        uint4 *dst = (uint4 *)ws;
         const uint32_t nvec = (uint32_t)((span + 15) >> 4);
-        for (uint32_t i = tid; i < nvec; i += PB_THREADS) dst[i] = sw_ld_stream_u4(src + i);
-        __syncthreads();
+        for (uint32_t i = lane; i < nvec; i += 32) dst[i] = sw_ld_stream_u4(src + i);
     }
+    __syncwarp();
     PbOut o;
     o.count = 0;
     o.status = 0;
-    uint64_t r0 = 0;
-    uint32_t len = 0;
-    if (tid < nrec) {
-        r0 = a.rec_off[rec0 + tid];
-        uint64_t l64 = a.rec_off[rec0 + tid + 1] - r0;
-        len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
+    if (lane < nrec) {
+        const uint64_t l64 = r1 - r0;
+        const uint32_t len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
         if (staged)
-            pb_parse_record(SmemBytes{smem + lead + (uint32_t)(r0 - b0)}, len, o);
+            pb_parse_record(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, len, o);
         else
             pb_parse_record(GmemBytes{a.bytes + r0}, len, o);
     }
-    uint64_t tile_total;
-    uint64_t row0 = sw_block_ordered_offset<PB_THREADS>(o.count, a.tile_state, tile, s_warp, &tile_total);
-    if (tid < nrec) {
-        const uint32_t rec = rec0 + tid;
+    uint64_t tile_total = 0, row0;
+    if (DENSE) {
+        row0 = (uint64_t)rec0 + lane;  // row index = record index
+        if (lane < nrec && o.count != 1) atomicOr(a.not_dense, 1u);
+    } else {
+        row0 = sw_block_ordered_offset<PB_THREADS>(o.count, a.tile_state, tile, s_warp, &tile_total);
+    }
+    const uint64_t row_base = a.row_base ? (uint64_t)__ldg(a.row_base) : 0ull;  // rows of earlier chunks
+    if (lane < nrec) {
+        const uint32_t rec = rec0 + lane;
         a.status[rec] = (uint8_t)o.status;
-        a.first_row[rec] = (uint32_t)row0;
-        if (o.count) {
+        a.first_row[rec] = (uint32_t)(row_base + row0);
+        if (DENSE ? o.count == 1 : o.count != 0) {
             if (staged)
-                pb_write_rows(a, SmemBytes{smem + lead + (uint32_t)(r0 - b0)}, o, rec, row0);
+                pb_write_rows(a, SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, o, rec, row0);
             else
                 pb_write_rows(a, GmemBytes{a.bytes + r0}, o, rec, row0);
         }
     }
-    if (rec0 + nrec == a.n && tid == 0) {
-        uint64_t total = row0 + tile_total;  // thread 0's offset is the tile base
-        a.first_row[a.n] = (uint32_t)total;
+    if ((uint64_t)tile * PB_THREADS + PB_THREADS >= a.n && tid == 0) {  // the tile holding the last record
+        const uint64_t total = DENSE ? (uint64_t)a.n : row0 + tile_total;  // thread 0's offset is the tile base
+        a.first_row[a.n] = (uint32_t)(row_base + total);
         *a.out_rows = (uint32_t)total;
+        if (a.row_next) *a.row_next = (uint32_t)(row_base + total);
     }
 }
 
@@ -487,9 +588,9 @@ static int check_cols(swgpu_ctx *ctx, const swgpu_decoded_cols *c) {
     return SWGPU_OK;
 }
 
-extern "C" int32_t swgpu_decode_pb_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off,
-                                       uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out,
-                                       uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev) {
+int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
+                        const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev,
+                        uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next) {
     if (!ctx) return SWGPU_E_INVALID;
     if (int rc = check_cols(ctx, out)) return rc;
     if (!rec_off || !first_row || !out_rows_dev || (n && !status)) {
@@ -502,8 +603,8 @@ extern "C" int32_t swgpu_decode_pb_dev(swgpu_ctx *ctx, const uint8_t *bytes, con
         SW_CUDA(ctx, cudaMemsetAsync(out_rows_dev, 0, sizeof(uint32_t), ctx->stream));
         return SWGPU_OK;
     }
-    const uint32_t ntiles = (n + PB_THREADS - 1) / PB_THREADS;
-    const size_t sbytes = SW_SCRATCH_HDR + (size_t)ntiles * 8;
+    const uint32_t ntiles = (n + PB_THREADS - 1) / PB_THREADS;             // CTAs
+    const size_t sbytes = SW_SCRATCH_HDR + (size_t)ntiles * 8;              // one scan state per tile
     if (int rc = sw_ensure_scratch(ctx, sbytes)) return rc;
     SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, sbytes, ctx->stream));
     PbArgs a;
@@ -517,11 +618,25 @@ extern "C" int32_t swgpu_decode_pb_dev(swgpu_ctx *ctx, const uint8_t *bytes, con
     a.out_rows = out_rows_dev;
     a.ticket = (uint32_t *)ctx->scratch;
     a.tile_state = (uint64_t *)((uint8_t *)ctx->scratch + SW_SCRATCH_HDR);
-    const int smem = PB_STAGE + 64;
-    SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    pb_decode_kernel<<<ntiles, PB_THREADS, smem, ctx->stream>>>(a);
+    a.rec_base = rec_base;
+    a.row_base = row_base;
+    a.row_next = row_next;
+    a.not_dense = (uint32_t *)ctx->scratch + 1;
+    const int smem = PB_WARPS * (PB_WSTAGE + 32);
+    SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    pb_decode_kernel<true><<<ntiles, PB_THREADS, smem, ctx->stream>>>(a);   // optimistic: rows = records
+    SW_CUDA(ctx, cudaGetLastError());
+    pb_decode_kernel<false><<<ntiles, PB_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_decode_pb_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off,
+                                       uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out,
+                                       uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev) {
+    return sw_decode_pb_launch(ctx, bytes, rec_off, n, max_rows, out, status, first_row, out_rows_dev, 0, nullptr,
+                               nullptr);
 }
 
 // ---- host-pointer entry point: stage in, decode, stage out ------------------------------------------

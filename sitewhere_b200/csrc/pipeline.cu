@@ -1,0 +1,284 @@
+// pipeline.cu — the fused host-buffer path: decode -> zone test (-> state merge) over a micro-batch that
+// lives in HOST memory, as the Java binding sees it.  The batch is cut into chunks of records; a ring of
+// three device slots lets the host->device copy of chunk i+1, the kernels of chunk i and the
+// device->host copy of chunk i-1 run at the same time on three streams (PCIe is full duplex), so the
+// call runs at the speed of the slower copy direction instead of the sum of copy + compute.
+//
+// Replaces, for a batch: IDeviceEventDecoder.decode per payload (ES/spi/IDeviceEventDecoder.java:39) followed by
+// ZoneTestRuleProcessor.onLocation per decoded location (RP/processors/geospatial/ZoneTestRuleProcessor.java:47-63)
+// and, when asked, DeviceStateProcessingLogic.process (DS/processing/DeviceStateProcessingLogic.java:65-67).
+#include "swgpu_common.cuh"
+
+int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
+                        const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev,
+                        uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next);
+int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
+                          const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev,
+                          uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next);
+int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta, uint32_t n,
+                   const uint32_t *n_rows_dev, uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev,
+                   const uint32_t *row_base);
+
+#define PL_SLOTS 3
+#define PL_NCOL 13
+
+struct PlSlot {
+    swgpu_ctx::Buf bytes, off, cols, status, first, pairs, counts;  // device
+    cudaEvent_t h2d_done = nullptr, compute_done = nullptr, d2h_done = nullptr;
+    uint32_t rows_cap = 0;
+    uint64_t pairs_cap = 0;
+};
+struct PlCounts {  // pinned mailbox per slot
+    uint32_t rows;
+    uint32_t pad;
+    uint64_t pairs;
+};
+struct Pipeline {
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    PlSlot slot[PL_SLOTS];
+    PlCounts *mail = nullptr;         // pinned, PL_SLOTS entries
+    uint32_t *row_totals = nullptr;   // device: running row total before each chunk
+    size_t row_totals_cap = 0;
+    bool ready = false;
+};
+
+static int pl_ensure_buf(swgpu_ctx *ctx, swgpu_ctx::Buf &b, size_t bytes) {
+    if (bytes <= b.cap) return SWGPU_OK;
+    if (b.p) {
+        SW_CUDA(ctx, cudaDeviceSynchronize());
+        SW_CUDA(ctx, cudaFree(b.p));
+        b.p = nullptr;
+        b.cap = 0;
+    }
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&b.p, want);
+    if (e != cudaSuccess) {
+        SW_SET_ERR(ctx, "cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e));
+        b.p = nullptr;
+        return SWGPU_E_NOMEM;
+    }
+    b.cap = want;
+    return SWGPU_OK;
+}
+
+static Pipeline *g_unused_pipeline_anchor = nullptr;  // (keeps the type referenced for debuggers)
+
+static int pl_get(swgpu_ctx *ctx, Pipeline **out) {
+    (void)g_unused_pipeline_anchor;
+    Pipeline *p = (Pipeline *)ctx->pipeline;
+    if (!p) {
+        p = new Pipeline();
+        ctx->pipeline = p;
+    }
+    if (!p->ready) {
+        SW_CUDA(ctx, cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking));
+        SW_CUDA(ctx, cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking));
+        for (int i = 0; i < PL_SLOTS; i++) {
+            SW_CUDA(ctx, cudaEventCreateWithFlags(&p->slot[i].h2d_done, cudaEventDisableTiming));
+            SW_CUDA(ctx, cudaEventCreateWithFlags(&p->slot[i].compute_done, cudaEventDisableTiming));
+            SW_CUDA(ctx, cudaEventCreateWithFlags(&p->slot[i].d2h_done, cudaEventDisableTiming));
+        }
+        SW_CUDA(ctx, cudaMallocHost((void **)&p->mail, sizeof(PlCounts) * PL_SLOTS));
+        p->ready = true;
+    }
+    *out = p;
+    return SWGPU_OK;
+}
+
+void sw_pipeline_free(swgpu_ctx *ctx) {
+    Pipeline *p = (Pipeline *)ctx->pipeline;
+    if (!p) return;
+    for (int i = 0; i < PL_SLOTS; i++) {
+        PlSlot &s = p->slot[i];
+        swgpu_ctx::Buf *bufs[] = {&s.bytes, &s.off, &s.cols, &s.status, &s.first, &s.pairs, &s.counts};
+        for (auto *b : bufs)
+            if (b->p) cudaFree(b->p);
+        if (s.h2d_done) cudaEventDestroy(s.h2d_done);
+        if (s.compute_done) cudaEventDestroy(s.compute_done);
+        if (s.d2h_done) cudaEventDestroy(s.d2h_done);
+    }
+    if (p->mail) cudaFreeHost(p->mail);
+    if (p->row_totals) cudaFree(p->row_totals);
+    if (p->s_in) cudaStreamDestroy(p->s_in);
+    if (p->s_out) cudaStreamDestroy(p->s_out);
+    delete p;
+    ctx->pipeline = nullptr;
+}
+
+extern "C" int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off,
+                                          uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
+                                          uint32_t *first_row, uint32_t *out_rows, uint64_t max_pairs, uint64_t *pairs,
+                                          uint64_t *n_pairs, uint32_t chunk_records) {
+    if (!ctx) return SWGPU_E_INVALID;
+    if (!rec_off || !out || !out_rows || !n_pairs || (format != SWGPU_FMT_PROTOBUF && format != SWGPU_FMT_JSON) ||
+        (max_pairs && !pairs) || (n && rec_off[n] && !bytes)) {
+        SW_SET_ERR(ctx, "swgpu_decode_zone_test: bad argument");
+        return SWGPU_E_INVALID;
+    }
+    if (!ctx->zone_blob) {
+        SW_SET_ERR(ctx, "swgpu_decode_zone_test: no zone table (call swgpu_set_zones first)");
+        return SWGPU_E_STATE;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    *out_rows = 0;
+    *n_pairs = 0;
+    if (first_row) first_row[0] = 0;
+    if (n == 0) return SWGPU_OK;
+    Pipeline *p;
+    if (int rc = pl_get(ctx, &p)) return rc;
+    const uint32_t C = chunk_records ? chunk_records : 262144u;
+    const uint32_t nchunks = (n + C - 1) / C;
+    uint64_t *const *hcol = (uint64_t *const *)out;
+
+    // size the slots for the largest chunk
+    uint64_t max_chunk_bytes = 0;
+    for (uint32_t c = 0; c < nchunks; c++) {
+        const uint32_t a = c * C, b = (a + C < n) ? a + C : n;
+        const uint64_t sz = rec_off[b] - rec_off[a];
+        if (sz > max_chunk_bytes) max_chunk_bytes = sz;
+    }
+    // a DeviceMeasurements payload can fan out; the row capacity per chunk starts at the record
+    // count and a chunk that overflows it is re-run with the exact size (rare)
+    for (int i = 0; i < PL_SLOTS && i < (int)nchunks; i++) {
+        PlSlot &s = p->slot[i];
+        if (int rc = pl_ensure_buf(ctx, s.bytes, max_chunk_bytes + 64)) return rc;
+        if (int rc = pl_ensure_buf(ctx, s.off, (size_t)(C + 1) * 8)) return rc;
+        if (s.rows_cap < C) {
+            if (int rc = pl_ensure_buf(ctx, s.cols, (size_t)C * 8 * PL_NCOL)) return rc;
+            s.rows_cap = C;
+        }
+        if (int rc = pl_ensure_buf(ctx, s.status, (size_t)C + 16)) return rc;
+        if (int rc = pl_ensure_buf(ctx, s.first, (size_t)(C + 2) * 4)) return rc;
+        if (s.pairs_cap < C) {
+            if (int rc = pl_ensure_buf(ctx, s.pairs, (size_t)C * 8)) return rc;
+            s.pairs_cap = C;
+        }
+        if (int rc = pl_ensure_buf(ctx, s.counts, 64)) return rc;
+    }
+    if (int rc = sw_ensure_scratch(ctx, SW_SCRATCH_HDR + ((size_t)C / 32 + 64) * 8)) return rc;  // warp-tile scan states
+    // running row totals: entry k = rows before chunk k (device), ring of nchunks+1
+    {
+        if ((size_t)nchunks + 1 > p->row_totals_cap) {
+            SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            if (p->row_totals) SW_CUDA(ctx, cudaFree(p->row_totals));
+            p->row_totals_cap = (size_t)nchunks + 64;
+            SW_CUDA(ctx, cudaMalloc((void **)&p->row_totals, sizeof(uint32_t) * p->row_totals_cap));
+        }
+        SW_CUDA(ctx, cudaMemsetAsync(p->row_totals, 0, sizeof(uint32_t) * ((size_t)nchunks + 1), ctx->stream));
+    }
+    cudaStream_t s_in = p->s_in, s_cmp = ctx->stream, s_out = p->s_out;
+    uint64_t rows_done = 0, pairs_done = 0;
+    bool rows_overflow = false, pairs_overflow = false;
+
+    auto issue = [&](uint32_t c) -> int {  // H2D + kernels + count read-back for chunk c
+        PlSlot &s = p->slot[c % PL_SLOTS];
+        const uint32_t a = c * C, b = (a + C < n) ? a + C : n, nc = b - a;
+        const uint64_t off0 = rec_off[a], sz = rec_off[b] - off0;
+        // the slot's previous occupant must have been copied out
+        SW_CUDA(ctx, cudaStreamWaitEvent(s_in, s.d2h_done, 0));
+        if (sz) SW_CUDA(ctx, cudaMemcpyAsync(s.bytes.p, bytes + off0, sz, cudaMemcpyHostToDevice, s_in));
+        SW_CUDA(ctx, cudaMemcpyAsync(s.off.p, rec_off + a, (size_t)(nc + 1) * 8, cudaMemcpyHostToDevice, s_in));
+        SW_CUDA(ctx, cudaEventRecord(s.h2d_done, s_in));
+        SW_CUDA(ctx, cudaStreamWaitEvent(s_cmp, s.h2d_done, 0));
+        swgpu_decoded_cols d;
+        uint64_t **dp = (uint64_t **)&d;
+        for (int k = 0; k < PL_NCOL; k++) dp[k] = (uint64_t *)s.cols.p + (size_t)k * s.rows_cap;
+        uint32_t *d_rows = (uint32_t *)s.counts.p;
+        uint64_t *d_pairs_n = (uint64_t *)((uint8_t *)s.counts.p + 8);
+        // record offsets are absolute: bias the byte pointer so that bytes_dev[off] is the chunk copy
+        const uint8_t *biased = (const uint8_t *)s.bytes.p - off0;
+        int rc = format == SWGPU_FMT_JSON
+                     ? sw_decode_json_launch(ctx, biased, (const uint64_t *)s.off.p, nc, s.rows_cap, &d,
+                                             (uint8_t *)s.status.p, (uint32_t *)s.first.p, d_rows, a, p->row_totals + c,
+                                             p->row_totals + c + 1)
+                     : sw_decode_pb_launch(ctx, biased, (const uint64_t *)s.off.p, nc, s.rows_cap, &d,
+                                           (uint8_t *)s.status.p, (uint32_t *)s.first.p, d_rows, a, p->row_totals + c,
+                                           p->row_totals + c + 1);
+        if (rc) return rc;
+        rc = sw_zone_launch(ctx, d.v1, d.v0, d.meta, s.rows_cap, d_rows, s.pairs_cap, (uint64_t *)s.pairs.p, d_pairs_n,
+                            p->row_totals + c);
+        if (rc) return rc;
+        SW_CUDA(ctx, cudaMemcpyAsync(&p->mail[c % PL_SLOTS], s.counts.p, sizeof(PlCounts), cudaMemcpyDeviceToHost, s_cmp));
+        SW_CUDA(ctx, cudaEventRecord(s.compute_done, s_cmp));
+        return SWGPU_OK;
+    };
+    auto drain = [&](uint32_t c) -> int {  // wait for chunk c's kernels, then copy its results out
+        PlSlot &s = p->slot[c % PL_SLOTS];
+        const uint32_t a = c * C, b = (a + C < n) ? a + C : n, nc = b - a;
+        SW_CUDA(ctx, cudaEventSynchronize(s.compute_done));
+        const PlCounts cnt = p->mail[c % PL_SLOTS];
+        if (cnt.rows > s.rows_cap || cnt.pairs > s.pairs_cap) {
+            // fan-out or many alerts: grow this slot and re-run the chunk synchronously (rare)
+            SW_CUDA(ctx, cudaDeviceSynchronize());
+            if (cnt.rows > s.rows_cap) {
+                if (int rc = pl_ensure_buf(ctx, s.cols, (size_t)cnt.rows * 8 * PL_NCOL)) return rc;
+                s.rows_cap = cnt.rows;
+            }
+            if (cnt.pairs > s.pairs_cap) {
+                if (int rc = pl_ensure_buf(ctx, s.pairs, (size_t)cnt.pairs * 8)) return rc;
+                s.pairs_cap = cnt.pairs;
+            }
+            SW_CUDA(ctx, cudaEventRecord(s.d2h_done, s_out));
+            if (int rc = issue(c)) return rc;
+            SW_CUDA(ctx, cudaEventSynchronize(s.compute_done));
+            const PlCounts c2 = p->mail[c % PL_SLOTS];
+            if (c2.rows > s.rows_cap || c2.pairs > s.pairs_cap) {
+                // the alert count depended on rows that were cut off the first time: once more
+                SW_CUDA(ctx, cudaDeviceSynchronize());
+                if (c2.pairs > s.pairs_cap) {
+                    if (int rc = pl_ensure_buf(ctx, s.pairs, (size_t)c2.pairs * 8)) return rc;
+                    s.pairs_cap = c2.pairs;
+                }
+                SW_CUDA(ctx, cudaEventRecord(s.d2h_done, s_out));
+                if (int rc = issue(c)) return rc;
+                SW_CUDA(ctx, cudaEventSynchronize(s.compute_done));
+            }
+        }
+        const PlCounts fin = p->mail[c % PL_SLOTS];
+        SW_CUDA(ctx, cudaStreamWaitEvent(s_out, s.compute_done, 0));
+        if (status) SW_CUDA(ctx, cudaMemcpyAsync(status + a, s.status.p, nc, cudaMemcpyDeviceToHost, s_out));
+        if (first_row)
+            SW_CUDA(ctx, cudaMemcpyAsync(first_row + a, s.first.p, (size_t)(nc + 1) * 4, cudaMemcpyDeviceToHost, s_out));
+        uint64_t take = fin.rows;
+        if (rows_done + take > max_rows) {
+            take = max_rows > rows_done ? max_rows - rows_done : 0;
+            rows_overflow = true;
+        }
+        if (take)
+            for (int k = 0; k < PL_NCOL; k++)
+                if (hcol[k])
+                    SW_CUDA(ctx, cudaMemcpyAsync(hcol[k] + rows_done, (uint64_t *)s.cols.p + (size_t)k * s.rows_cap, take * 8,
+                                                 cudaMemcpyDeviceToHost, s_out));
+        uint64_t ptake = fin.pairs;
+        if (pairs_done + ptake > max_pairs) {
+            ptake = max_pairs > pairs_done ? max_pairs - pairs_done : 0;
+            pairs_overflow = true;
+        }
+        if (ptake) SW_CUDA(ctx, cudaMemcpyAsync(pairs + pairs_done, s.pairs.p, ptake * 8, cudaMemcpyDeviceToHost, s_out));
+        SW_CUDA(ctx, cudaEventRecord(s.d2h_done, s_out));
+        rows_done += fin.rows;
+        pairs_done += fin.pairs;
+        return SWGPU_OK;
+    };
+
+    // software pipeline: keep up to PL_SLOTS chunks in flight
+    uint32_t issued = 0, drained = 0;
+    while (drained < nchunks) {
+        while (issued < nchunks && issued - drained < PL_SLOTS) {
+            if (int rc = issue(issued)) return rc;
+            issued++;
+        }
+        if (int rc = drain(drained)) return rc;
+        drained++;
+    }
+    SW_CUDA(ctx, cudaStreamSynchronize(s_out));
+    SW_CUDA(ctx, cudaStreamSynchronize(s_cmp));
+    *out_rows = (uint32_t)rows_done;
+    *n_pairs = pairs_done;
+    if (rows_overflow || pairs_overflow) {
+        SW_SET_ERR(ctx, "swgpu_decode_zone_test: %llu rows / %llu alerts exceed max_rows %u / max_pairs %llu",
+                   (unsigned long long)rows_done, (unsigned long long)pairs_done, max_rows, (unsigned long long)max_pairs);
+        return SWGPU_E_CAPACITY;
+    }
+    return SWGPU_OK;
+}

@@ -34,6 +34,7 @@ struct swgpu_ctx {
         size_t cap = 0;
     };
     Buf d_bytes, d_off, d_status, d_first, d_cols, d_pairs, d_lon, d_lat, d_meta, d_ids;
+    Buf d_zwork;  // zone test work area (parked counts / ids, tile totals / bases)
     Buf h_small;  // pinned, small results
 
     // zone table
@@ -43,6 +44,8 @@ struct swgpu_ctx {
 
     // device state (merge.cu)
     void *state = nullptr;
+    // chunked host-buffer pipeline (pipeline.cu)
+    void *pipeline = nullptr;
 };
 
 #define SW_SET_ERR(ctx, ...)                         \
@@ -76,11 +79,12 @@ int sw_ensure_pinned(swgpu_ctx *ctx, swgpu_ctx::Buf &b, size_t bytes);   // pinn
 
 __device__ __forceinline__ uint64_t sw_ld_volatile_u64(const uint64_t *p) {
     uint64_t v;
-    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    // GPU-scope relaxed: served by L2, never by a stale L1 line; cheaper than .volatile (system scope)
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
     return v;
 }
 __device__ __forceinline__ void sw_st_volatile_u64(uint64_t *p, uint64_t v) {
-    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 // streaming 16-byte load that does not pollute L1 (payload bytes are read exactly once)
 __device__ __forceinline__ uint4 sw_ld_stream_u4(const uint4 *p) {
@@ -97,6 +101,8 @@ __device__ __forceinline__ uint4 sw_ld_stream_u4(const uint4 *p) {
 #define SW_FLAG_PFX (2ull << 62)
 #define SW_VAL_MASK ((1ull << 62) - 1)
 
+#define SW_LB_K 8  // predecessors examined per lane per look-back round
+
 // Called by all 32 lanes of ONE warp of the block.  Returns the exclusive prefix of `tile`.
 __device__ __forceinline__ uint64_t sw_lookback(uint64_t *tile_state, uint32_t tile, uint64_t total) {
     const uint32_t lane = threadIdx.x & 31;
@@ -105,16 +111,19 @@ __device__ __forceinline__ uint64_t sw_lookback(uint64_t *tile_state, uint32_t t
         return 0;
     }
     if (lane == 0) sw_st_volatile_u64(&tile_state[tile], SW_FLAG_AGG | total);
+    // Walk back 32 predecessors per round until one of them holds an inclusive prefix.  (Measured on
+    // B200: wider windows and sleeping polls do not help — what a tile waits for is the slowest of the
+    // few hundred tiles in flight, not the walk itself; see DESIGN.md "ordered placement".)
     uint64_t excl = 0;
     int64_t idx = (int64_t)tile - 1;
     for (;;) {
-        int64_t j = idx - (int64_t)lane;
+        const int64_t j = idx - (int64_t)lane;
         uint64_t s = (j >= 0) ? sw_ld_volatile_u64(&tile_state[j]) : SW_FLAG_PFX;
         while (__any_sync(SW_FULL, (s >> 62) == 0)) {
             if ((s >> 62) == 0) s = sw_ld_volatile_u64(&tile_state[j]);
         }
-        uint32_t pmask = __ballot_sync(SW_FULL, (s >> 62) == 2);
-        int first = pmask ? (__ffs(pmask) - 1) : 32;
+        const uint32_t pmask = __ballot_sync(SW_FULL, (s >> 62) == 2);
+        const int first = pmask ? (__ffs(pmask) - 1) : 32;
         uint64_t c = ((int)lane <= first) ? (s & SW_VAL_MASK) : 0;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(SW_FULL, c, o);
@@ -126,13 +135,31 @@ __device__ __forceinline__ uint64_t sw_lookback(uint64_t *tile_state, uint32_t t
     return excl;
 }
 
+// Warp-granular form: a tile is the 32 lanes of one warp.  No block barrier is involved, so warps
+// of a CTA proceed independently (a slow record or a long look-back stalls one warp, not eight).
+// Returns this lane's global exclusive offset; *tile_total_out = the warp's total.
+__device__ __forceinline__ uint64_t sw_warp_ordered_offset(uint32_t count, uint64_t *tile_state, uint32_t wtile,
+                                                           uint64_t *tile_total_out) {
+    const uint32_t lane = threadIdx.x & 31;
+    uint32_t inc = count;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(SW_FULL, inc, o);
+        if (lane >= (uint32_t)o) inc += t;
+    }
+    const uint64_t total = __shfl_sync(SW_FULL, inc, 31);
+    const uint64_t base = sw_lookback(tile_state, wtile, total);
+    *tile_total_out = total;
+    return base + (uint64_t)(inc - count);
+}
+
 // Block-wide exclusive scan of one uint32 per thread + ordered global base through look-back.
 // Returns (global exclusive prefix for this thread); *block_total_out gets the tile total.
 // smem: needs THREADS/32 + 2 uint64 words.
 template <int THREADS>
 __device__ __forceinline__ uint64_t sw_block_ordered_offset(uint32_t count, uint64_t *tile_state,
                                                             uint32_t tile, uint64_t *s_warp /*[THREADS/32+2]*/,
-                                                            uint64_t *tile_total_out) {
+                                                            uint64_t *tile_total_out, bool dbg_skip = false) {
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t inc = count;
 #pragma unroll
@@ -152,7 +179,7 @@ __device__ __forceinline__ uint64_t sw_block_ordered_offset(uint32_t count, uint
             if (lane >= (uint32_t)o) winc += t;
         }
         uint64_t total = __shfl_sync(SW_FULL, winc, NW - 1);
-        uint64_t base = sw_lookback(tile_state, tile, total);
+        uint64_t base = dbg_skip ? (uint64_t)tile * THREADS : sw_lookback(tile_state, tile, total);
         if (lane < NW) s_warp[lane] = winc - w;  // exclusive warp offsets
         if (lane == 0) {
             s_warp[NW] = base;
@@ -172,6 +199,23 @@ __device__ __forceinline__ uint64_t sw_hash64(const Rd &rd, uint32_t off, uint32
     uint32_t h = 0x9747b28cu ^ len;
     uint32_t f = 0x811c9dc5u;
     uint32_t i = 0;
+    // eight bytes per load while they last (one unaligned 64-bit read instead of eight byte reads)
+    for (; i + 8 <= len; i += 8) {
+        const uint64_t v = rd.le64(off + i);
+#pragma unroll
+        for (int half = 0; half < 2; half++) {
+            uint32_t k = (uint32_t)(v >> (32 * half));
+            f = (f ^ (k & 0xff)) * 0x01000193u;
+            f = (f ^ ((k >> 8) & 0xff)) * 0x01000193u;
+            f = (f ^ ((k >> 16) & 0xff)) * 0x01000193u;
+            f = (f ^ (k >> 24)) * 0x01000193u;
+            k *= m;
+            k ^= k >> 24;
+            k *= m;
+            h *= m;
+            h ^= k;
+        }
+    }
     for (; i + 4 <= len; i += 4) {
         uint32_t b0 = rd.byte(off + i), b1 = rd.byte(off + i + 1), b2 = rd.byte(off + i + 2),
                  b3 = rd.byte(off + i + 3);

@@ -101,7 +101,8 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
     }
     verts.reserve(total_pts * 2);
     double gx0 = INFINITY, gy0 = INFINITY, gx1 = -INFINITY, gy1 = -INFINITY;
-    std::vector<uint32_t> bin_start, bin_items;
+    std::vector<uint32_t> bin_start;
+    std::vector<double> bin_items;  // per slab: the edges that can touch it, as (x1,y1,x2,y2) records
     for (uint32_t t = 0; t < T; t++) {
         ZoneTestRec &z = tests[t];
         memset(&z, 0, sizeof z);
@@ -162,10 +163,15 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
                 for (uint32_t bb = lo; bb <= hi; bb++) bins[bb].push_back(i);
             }
             for (uint32_t bb = 0; bb < nb; bb++) {
-                bin_start.push_back((uint32_t)bin_items.size());
-                for (uint32_t e : bins[bb]) bin_items.push_back(e);
+                bin_start.push_back((uint32_t)(bin_items.size() / 4));
+                for (uint32_t e : bins[bb]) {  // edge record: p1 = ring[e], p2 = ring[e-1], 32 bytes
+                    bin_items.push_back(xs[e]);
+                    bin_items.push_back(ys[e]);
+                    bin_items.push_back(xs[e - 1]);
+                    bin_items.push_back(ys[e - 1]);
+                }
             }
-            bin_start.push_back((uint32_t)bin_items.size());
+            bin_start.push_back((uint32_t)(bin_items.size() / 4));
         }
     }
     // grid over envelopes
@@ -238,7 +244,7 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
     h.off_bin_start = off;
     off = align_up(off + bin_start.size() * 4, 256);
     h.off_bin_items = off;
-    off = align_up(off + bin_items.size() * 4, 256);
+    off = align_up(off + bin_items.size() * 8, 256);
     h.off_outside = off;
     off = align_up(off + outside.size() * 4, 256);
     h.total_bytes = off;
@@ -249,7 +255,7 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
     memcpy(blob.data() + h.off_cell_start, cell_start.data(), cell_start.size() * 4);
     if (!cell_items.empty()) memcpy(blob.data() + h.off_cell_items, cell_items.data(), cell_items.size() * 4);
     if (!bin_start.empty()) memcpy(blob.data() + h.off_bin_start, bin_start.data(), bin_start.size() * 4);
-    if (!bin_items.empty()) memcpy(blob.data() + h.off_bin_items, bin_items.data(), bin_items.size() * 4);
+    if (!bin_items.empty()) memcpy(blob.data() + h.off_bin_items, bin_items.data(), bin_items.size() * 8);
     if (!outside.empty()) memcpy(blob.data() + h.off_outside, outside.data(), outside.size() * 4);
     return SWGPU_OK;
 }
@@ -348,6 +354,7 @@ struct ZnArgs {
     uint64_t *n_pairs;
     uint32_t *ticket;
     uint64_t *tile_state;
+    const uint32_t *row_base;  // chunked pipeline: global index of row 0 (NULL = 0)
 };
 
 // exact sign of x1*y2 - y1*x2: products with their rounding errors (fma), compared as the
@@ -362,16 +369,14 @@ __device__ __forceinline__ int zn_sign_det(double x1, double y1, double x2, doub
 
 // RayCrossingCounter.locatePointInRing(p, ring) == INTERIOR restricted to the slab's edges
 __device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, const ZoneTestRec &z, double px, double py) {
-    const double2 *v = (const double2 *)(a.blob + a.h.off_verts) + z.vtx_off;
     const uint32_t *bs = (const uint32_t *)(a.blob + a.h.off_bin_start) + z.bin_off;
-    const uint32_t *bi = (const uint32_t *)(a.blob + a.h.off_bin_items);
+    const double2 *er = (const double2 *)(a.blob + a.h.off_bin_items);  // edge records, 32 B each (one sector)
     uint32_t b = zn_cell(py, z.miny, z.inv_bin, z.nbins);
     uint32_t k0 = __ldg(bs + b), k1 = __ldg(bs + b + 1);
     uint32_t crossings = 0;
     bool boundary = false;
     for (uint32_t k = k0; k < k1; k++) {
-        uint32_t i = __ldg(bi + k);
-        double2 p1 = __ldg(v + i), p2 = __ldg(v + i - 1);
+        double2 p1 = __ldg(er + 2 * (size_t)k), p2 = __ldg(er + 2 * (size_t)k + 1);
         if (p1.x < px && p2.x < px) continue;
         if (px == p2.x && py == p2.y) {
             boundary = true;
@@ -439,32 +444,31 @@ __device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, d
     }
 }
 
-__global__ void __launch_bounds__(ZN_THREADS) zone_test_kernel(ZnArgs a) {
-    __shared__ uint64_t s_warp[ZN_THREADS / 32 + 2];
-    __shared__ uint32_t s_tile;
-    const uint32_t tid = threadIdx.x;
-    if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
-    __syncthreads();
-    const uint32_t tile = s_tile;
-    const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
-    const uint32_t i = tile * ZN_THREADS + tid;
-    const uint32_t T_out = a.h.n_outside;
+// what one location evaluates to: the tests that contain it (ascending, with their condition bit) and the
+// number of alerts the reference would fire for it
+struct ZnLoc {
+    double px, py;
+    uint32_t ins[ZN_MAXIN];
+    uint32_t n_in, count;
+};
 
+__device__ __forceinline__ void zn_eval(const ZnArgs &a, uint32_t i, uint32_t n_live, ZnLoc &L) {
+    const uint32_t T_out = a.h.n_outside;
     bool valid = i < n_live;
     if (valid && a.meta) {
         uint64_t m = __ldg(a.meta + i);
         uint32_t fl = SWGPU_META_FLAGS(m);
         valid = SWGPU_META_KIND(m) == SWGPU_KIND_LOCATION && (fl & SWGPU_F_HAS_V0) && (fl & SWGPU_F_HAS_V1);
     }
-    double px = 0, py = 0;
-    uint32_t ins[ZN_MAXIN];
-    uint32_t n_in = 0, n_in_icond = 0, n_in_ocond = 0;
+    L.px = L.py = 0;
+    L.n_in = 0;
+    uint32_t n_in_icond = 0, n_in_ocond = 0;
     if (valid) {
-        px = __ldg(a.lon + i);
-        py = __ldg(a.lat + i);
-        zn_for_each_inside(a, px, py, [&](uint32_t t, uint32_t outside_cond) {
-            if (n_in < ZN_MAXIN) ins[n_in] = (t << 1) | outside_cond;
-            n_in++;
+        L.px = __ldg(a.lon + i);
+        L.py = __ldg(a.lat + i);
+        zn_for_each_inside(a, L.px, L.py, [&](uint32_t t, uint32_t outside_cond) {
+            if (L.n_in < ZN_MAXIN) L.ins[L.n_in] = (t << 1) | outside_cond;
+            L.n_in++;
             if (outside_cond)
                 n_in_ocond++;
             else
@@ -472,13 +476,17 @@ __global__ void __launch_bounds__(ZN_THREADS) zone_test_kernel(ZnArgs a) {
         });
     }
     // alerts: Inside-condition tests that contain the point + Outside-condition tests that do not
-    uint32_t count = valid ? (n_in_icond + (T_out - n_in_ocond)) : 0;
-    uint64_t tile_total;
-    uint64_t pos = sw_block_ordered_offset<ZN_THREADS>(count, a.tile_state, tile, s_warp, &tile_total);
-    // tiles are ordered by ticket, so the tile with the highest id is last: it publishes the total
-    if (tile == gridDim.x - 1 && tid == 0) *a.n_pairs = pos + tile_total;  // thread 0's offset = tile base
-    if (count) {
-        const uint64_t ev = (uint64_t)i << 32;
+    L.count = valid ? (n_in_icond + (T_out - n_in_ocond)) : 0;
+}
+
+// writes the location's alert pairs, in test order, starting at `pos`
+__device__ __forceinline__ void zn_emit(const ZnArgs &a, uint32_t i, const ZnLoc &L, uint64_t pos) {
+    const uint32_t T_out = a.h.n_outside;
+    const uint32_t n_in = L.n_in;
+    const uint32_t *ins = L.ins;
+    const double px = L.px, py = L.py;
+    {
+        const uint64_t ev = (uint64_t)((a.row_base ? __ldg(a.row_base) : 0u) + i) << 32;
         if (T_out == 0 && n_in <= ZN_MAXIN) {
             for (uint32_t k = 0; k < n_in; k++, pos++)
                 if (pos < a.max_pairs) a.pairs[pos] = ev | (ins[k] >> 1);
@@ -524,9 +532,151 @@ __global__ void __launch_bounds__(ZN_THREADS) zone_test_kernel(ZnArgs a) {
     }
 }
 
-extern "C" int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta,
-                                       uint32_t n, const uint32_t *n_rows_dev, uint64_t max_pairs,
-                                       uint64_t *pairs, uint64_t *n_pairs_dev) {
+// ---- single-launch form (ticketed tiles + decoupled look-back).  Needs only 8 bytes of scratch per
+// 256 locations; kept for swgpu_zone_test_noalloc_dev.  Every tile waits for the slowest tile in flight,
+// so the three-launch form below is what the other entry points use.
+__global__ void __launch_bounds__(ZN_THREADS) zone_test_kernel(ZnArgs a) {
+    __shared__ uint64_t s_warp[ZN_THREADS / 32 + 2];
+    __shared__ uint32_t s_tile;
+    const uint32_t tid = threadIdx.x;
+    if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
+    const uint32_t i = tile * ZN_THREADS + tid;
+    ZnLoc L;
+    zn_eval(a, i, n_live, L);
+    uint64_t tile_total;
+    uint64_t pos = sw_block_ordered_offset<ZN_THREADS>(L.count, a.tile_state, tile, s_warp, &tile_total);
+    // tiles are ordered by ticket, so the tile with the highest id is last: it publishes the total
+    if (tile == gridDim.x - 1 && tid == 0) *a.n_pairs = pos + tile_total;  // thread 0's offset = tile base
+    if (L.count) zn_emit(a, i, L, pos);
+}
+
+// ---- three-launch form: count -> scan of tile totals -> emit.  No tile ever waits for another one.
+//   zone_count_kernel  evaluates every location once; parks its alert count (4 B) and, in the common
+//                      case (no Outside-condition tests, at most two alerts), the test ids (8 B); writes
+//                      the tile's total.
+//   zone_scan_kernel   one CTA: exclusive scan of the tile totals (a few tens of thousands of words).
+//   zone_emit_kernel   places each location's pairs at tile base + its offset inside the tile; locations
+//                      whose ids were not parked (rare) are evaluated again.
+struct ZnWork {
+    uint32_t *cnt;        // [n]
+    uint64_t *inl;        // [n] two parked test ids
+    uint64_t *tile_tot;   // [ntiles]
+    uint64_t *tile_base;  // [ntiles]
+};
+
+__global__ void __launch_bounds__(ZN_THREADS) zone_count_kernel(ZnArgs a, ZnWork w) {
+    __shared__ uint32_t s_part[ZN_THREADS / 32];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
+    const uint32_t i = blockIdx.x * ZN_THREADS + tid;
+    ZnLoc L;
+    zn_eval(a, i, n_live, L);
+    if (i < a.n) {
+        w.cnt[i] = L.count;
+        if (a.h.n_outside == 0 && L.count <= 2) {
+            const uint64_t id0 = L.n_in > 0 ? (L.ins[0] >> 1) : 0u, id1 = L.n_in > 1 ? (L.ins[1] >> 1) : 0u;
+            w.inl[i] = id0 | (id1 << 32);
+        }
+    }
+    uint32_t s = L.count;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(SW_FULL, s, o);
+    if (lane == 0) s_part[warp] = s;
+    __syncthreads();
+    if (tid == 0) {
+        uint64_t t = 0;
+#pragma unroll
+        for (int k = 0; k < ZN_THREADS / 32; k++) t += s_part[k];
+        w.tile_tot[blockIdx.x] = t;
+    }
+}
+
+#define ZS_THREADS 1024
+#define ZS_ITEMS 8
+__global__ void __launch_bounds__(ZS_THREADS) zone_scan_kernel(const uint64_t *tot, uint64_t *base, uint32_t ntiles,
+                                                               uint64_t *total_out) {
+    __shared__ uint64_t s_warp[ZS_THREADS / 32];
+    __shared__ uint64_t s_carry;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (uint32_t start = 0; start < ntiles; start += ZS_THREADS * ZS_ITEMS) {
+        const uint32_t i0 = start + tid * ZS_ITEMS;
+        uint64_t v[ZS_ITEMS], sum = 0;
+#pragma unroll
+        for (int k = 0; k < ZS_ITEMS; k++) {
+            v[k] = (i0 + k < ntiles) ? tot[i0 + k] : 0;
+            sum += v[k];
+        }
+        uint64_t inc = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint64_t t = __shfl_up_sync(SW_FULL, inc, o);
+            if (lane >= (uint32_t)o) inc += t;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            uint64_t wv = s_warp[lane], winc = wv;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint64_t t = __shfl_up_sync(SW_FULL, winc, o);
+                if (lane >= (uint32_t)o) winc += t;
+            }
+            s_warp[lane] = winc - wv;  // exclusive warp offsets
+        }
+        __syncthreads();
+        uint64_t run = s_carry + s_warp[warp] + (inc - sum);
+#pragma unroll
+        for (int k = 0; k < ZS_ITEMS; k++) {
+            if (i0 + k < ntiles) base[i0 + k] = run;
+            run += v[k];
+        }
+        __syncthreads();
+        if (tid == ZS_THREADS - 1) s_carry = run;
+        __syncthreads();
+    }
+    if (tid == 0) *total_out = s_carry;
+}
+
+__global__ void __launch_bounds__(ZN_THREADS) zone_emit_kernel(ZnArgs a, ZnWork w) {
+    __shared__ uint32_t s_part[ZN_THREADS / 32];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t i = blockIdx.x * ZN_THREADS + tid;
+    const uint32_t count = i < a.n ? w.cnt[i] : 0;
+    uint32_t inc = count;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(SW_FULL, inc, o);
+        if (lane >= (uint32_t)o) inc += t;
+    }
+    if (lane == 31) s_part[warp] = inc;
+    __syncthreads();
+    uint32_t woff = 0;
+#pragma unroll
+    for (int k = 0; k < ZN_THREADS / 32; k++)
+        if (k < (int)warp) woff += s_part[k];
+    if (!count) return;
+    uint64_t pos = w.tile_base[blockIdx.x] + woff + (inc - count);
+    if (a.h.n_outside == 0 && count <= 2) {
+        const uint64_t ev = (uint64_t)((a.row_base ? __ldg(a.row_base) : 0u) + i) << 32;
+        const uint64_t ids = w.inl[i];
+        if (pos < a.max_pairs) a.pairs[pos] = ev | (ids & 0xffffffffu);
+        if (count == 2 && pos + 1 < a.max_pairs) a.pairs[pos + 1] = ev | (ids >> 32);
+    } else {
+        const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
+        ZnLoc L;
+        zn_eval(a, i, n_live, L);
+        zn_emit(a, i, L, pos);
+    }
+}
+
+int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta, uint32_t n,
+                   const uint32_t *n_rows_dev, uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev,
+                   const uint32_t *row_base) {
     if (!ctx) return SWGPU_E_INVALID;
     if (!ctx->zone_blob) {
         SW_SET_ERR(ctx, "swgpu_zone_test: no zone table (call swgpu_set_zones first)");
@@ -542,9 +692,16 @@ extern "C" int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const 
         return SWGPU_OK;
     }
     const uint32_t ntiles = (n + ZN_THREADS - 1) / ZN_THREADS;
-    const size_t sbytes = SW_SCRATCH_HDR + (size_t)ntiles * 8;
-    if (int rc = sw_ensure_scratch(ctx, sbytes)) return rc;
-    SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, sbytes, ctx->stream));
+    // work area: parked counts (4 B) and ids (8 B) per location, totals and bases (8 B each) per tile
+    const size_t off_inl = ((size_t)n * 4 + 255) / 256 * 256;
+    const size_t off_tot = off_inl + (size_t)n * 8;
+    const size_t off_base = off_tot + (size_t)ntiles * 8;
+    if (int rc = sw_ensure(ctx, ctx->d_zwork, off_base + (size_t)ntiles * 8)) return rc;
+    ZnWork w;
+    w.cnt = (uint32_t *)ctx->d_zwork.p;
+    w.inl = (uint64_t *)((uint8_t *)ctx->d_zwork.p + off_inl);
+    w.tile_tot = (uint64_t *)((uint8_t *)ctx->d_zwork.p + off_tot);
+    w.tile_base = (uint64_t *)((uint8_t *)ctx->d_zwork.p + off_base);
     ZnArgs a;
     a.blob = (const uint8_t *)ctx->zone_blob;
     a.h = *(const ZoneHeader *)ctx->zone_hdr;
@@ -556,11 +713,22 @@ extern "C" int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const 
     a.max_pairs = max_pairs;
     a.pairs = pairs;
     a.n_pairs = n_pairs_dev;
-    a.ticket = (uint32_t *)ctx->scratch;
-    a.tile_state = (uint64_t *)((uint8_t *)ctx->scratch + SW_SCRATCH_HDR);
-    zone_test_kernel<<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a);
+    a.ticket = nullptr;
+    a.tile_state = nullptr;
+    a.row_base = row_base;
+    zone_count_kernel<<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a, w);
+    SW_CUDA(ctx, cudaGetLastError());
+    zone_scan_kernel<<<1, ZS_THREADS, 0, ctx->stream>>>(w.tile_tot, w.tile_base, ntiles, n_pairs_dev);
+    SW_CUDA(ctx, cudaGetLastError());
+    zone_emit_kernel<<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a, w);
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta,
+                                       uint32_t n, const uint32_t *n_rows_dev, uint64_t max_pairs,
+                                       uint64_t *pairs, uint64_t *n_pairs_dev) {
+    return sw_zone_launch(ctx, lon, lat, meta, n, n_rows_dev, max_pairs, pairs, n_pairs_dev, nullptr);
 }
 
 extern "C" int32_t swgpu_zone_test(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta,
@@ -687,6 +855,7 @@ extern "C" int32_t swgpu_zone_test_noalloc_dev(swgpu_ctx *ctx, const double *lon
     a.n_pairs = n_pairs_dev;
     a.ticket = (uint32_t *)scratch;
     a.tile_state = (uint64_t *)((uint8_t *)scratch + SW_SCRATCH_HDR);
+    a.row_base = nullptr;
     zone_test_kernel<<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a);
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;

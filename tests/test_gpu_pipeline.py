@@ -1,0 +1,97 @@
+"""GPU parity: the fused host-buffer call swgpu_decode_zone_test (chunked, overlapped copies) must give
+exactly what the oracle's decode followed by its index-free zone loop gives — across chunk
+boundaries, with failed records, measurement fan-out beyond a chunk's row capacity, and more alerts
+per chunk than its pair buffer holds."""
+import numpy as np
+import pytest
+
+import oracle
+from sitewhere_b200 import synth as S
+from sitewhere_b200.api import pinned_array, pinned_cols
+from tests import pb_cases, json_cases
+from tests.helpers import assert_cols_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def check(ctx, fmt, data, rec_off, zones, chunk):
+    ctx.set_zones(*zones)
+    cols, status, first_row, n_rows, pairs = ctx.decode_zone_test(fmt, data, rec_off, chunk_records=chunk)
+    ocols, ostatus, ofirst, ototal = getattr(oracle, "decode_pb" if fmt == "pb" else "decode_json")(data, rec_off)
+    assert n_rows == ototal
+    assert np.array_equal(status, ostatus)
+    assert np.array_equal(first_row, ofirst)
+    assert_cols_equal(cols, ocols, ototal)
+    want, total = oracle.zone_test(*zones, ocols.v1[:ototal], ocols.v0[:ototal], meta=ocols.meta[:ototal])
+    assert pairs.shape[0] == total
+    assert np.array_equal(pairs, want)
+    return n_rows, total
+
+
+def test_pb_locations_many_chunks(ctx):
+    zones = S.star_zones(16)
+    lon, lat = S.locations_for_zones(50_000, *zones[:3], seed=11, boundary_rate=0.01)
+    data, rec_off, _ = S.pb_locations(50_000, 3000, lon, lat, seed=11)
+    rows, alerts = check(ctx, "pb", data, rec_off, zones, chunk=4096)      # 13 chunks, last one ragged
+    assert rows == 50_000 and alerts > 1000
+    check(ctx, "pb", data, rec_off, zones, chunk=0)                        # default chunk: single chunk
+
+
+def test_pb_mixed_with_failures_and_fanout(ctx):
+    zones = S.star_zones(8, cond_mode="alternate")      # 32 Outside-condition tests: ~32 alerts per location
+    good, goff, _ = S.pb_mixed(6000, 200, seed=12, zones=zones)
+    raw = good.tobytes()
+    recs = [raw[int(goff[i]): int(goff[i + 1])] for i in range(6000)]
+    cs = pb_cases.cases()
+    rng = np.random.default_rng(2)
+    for k in range(400):
+        recs.insert(int(rng.integers(0, len(recs))), cs[k % len(cs)][1])
+    # one payload with 900 measurements: more rows than a 512-record chunk has capacity for
+    recs.insert(1000, S.pb_measurements_record("fan", [("m%03d" % k, float(k)) for k in range(900)], date=5))
+    data, rec_off = S.pack_records(recs)
+    check(ctx, "pb", data, rec_off, zones, chunk=512)
+
+
+def test_json_pipeline(ctx):
+    zones = S.star_zones(8)
+    recs = []
+    rng = np.random.default_rng(3)
+    lon, lat = S.locations_for_zones(4000, *zones[:3], seed=13, boundary_rate=0.02)
+    for i in range(4000):
+        recs.append(S.json_location(S.token_str(int(rng.integers(0, 500))), repr(float(lat[i])), repr(float(lon[i])), "0.0",
+                                    S.EVENT_DATE_BASE + i))
+        if i % 7 == 0:
+            recs.append(S.json_measurement("tok", "fuel.level", "1.5", S.EVENT_DATE_BASE + i))
+    for c in json_cases.cases():
+        recs.insert(int(rng.integers(0, len(recs))), c[1])
+    data, rec_off = S.pack_records(recs)
+    check(ctx, "json", data, rec_off, zones, chunk=700)
+
+
+def test_pinned_buffers_and_column_subset(ctx):
+    zones = S.star_zones(8)
+    lon, lat = S.locations_for_zones(20_000, *zones[:3], seed=14)
+    data, rec_off, _ = S.pb_locations(20_000, 1000, lon, lat, seed=14)
+    ctx.set_zones(*zones)
+    p_data = pinned_array((data.shape[0],), np.uint8)
+    p_data[:] = data
+    p_off = pinned_array((rec_off.shape[0],), np.uint64)
+    p_off[:] = rec_off
+    names = ["meta", "v0", "v1", "token_span"]
+    p_cols = pinned_cols(20_000, names)
+    p_pairs = pinned_array((20_000,), np.uint64)
+    for _ in range(2):       # twice: the ring and its events are reused
+        cols, status, first_row, n_rows, pairs = ctx.decode_zone_test("pb", p_data, p_off, p_cols, None, None, p_pairs,
+                                                                      chunk_records=3000)
+        ocols, ostatus, ofirst, ototal = oracle.decode_pb(data, rec_off)
+        assert n_rows == ototal
+        for nm in names:
+            assert np.array_equal(getattr(cols, nm)[:ototal].view(np.uint64), getattr(ocols, nm)[:ototal].view(np.uint64)), nm
+        want, total = oracle.zone_test(*zones, ocols.v1[:ototal], ocols.v0[:ototal], meta=ocols.meta[:ototal])
+        assert np.array_equal(pairs, want)
+
+
+def test_empty_batch(ctx):
+    ctx.set_zones(*S.rect_zones(2))
+    cols, status, first_row, n_rows, pairs = ctx.decode_zone_test("pb", np.zeros(0, np.uint8), np.zeros(1, np.uint64))
+    assert n_rows == 0 and pairs.shape[0] == 0 and first_row.tolist() == [0]
