@@ -190,20 +190,9 @@ def run_ours(args):
     # ---- zone table: built on rank 0, replicated by one NCCL broadcast (configuration change only)
     if rank == 0:
         ctx.set_zones(*zones)
-        nbytes = ctx.zone_table_bytes()
-    else:
-        nbytes = 0
     if world > 1:
-        sz = torch.tensor([nbytes], dtype=torch.int64, device=dev)
-        dist.broadcast(sz, 0)
-        nbytes = int(sz.item())
-        blob = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-        if rank == 0:
-            ctx.zone_table_export(blob)
-        dist.broadcast(blob, 0)
-        if rank != 0:
-            ctx.zone_table_import(blob, nbytes)
-        del blob
+        from sitewhere_b200.shard import broadcast_zone_table
+        broadcast_zone_table(ctx, dist, dev, rank)
 
     # ---- device-resident inputs and outputs
     total_bytes = int(rec_off[-1])
@@ -332,7 +321,9 @@ def run_ours(args):
                        "sharding": "Kafka murmur2(deviceToken) % n_gpus; zone table NCCL-broadcast once"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps},
-            "gpu_launches": 2 * args.steps,
+            # per step: pb_decode_kernel<dense>, pb_decode_kernel<ordered> (returns at once on a dense batch),
+            # zone_count_kernel, zone_scan_kernel, zone_emit_kernel
+            "gpu_launches": 5 * args.steps,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "traffic": None, "peak_source": peak_src},
             "kernels": {"pb_decode_kernel": {"ms": ms_dec, "algorithmic_bytes": bytes_dec, "GBps": gbs_dec,

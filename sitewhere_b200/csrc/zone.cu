@@ -22,7 +22,7 @@
 
 #define ZN_THREADS 256
 #define ZN_MAXIN 8  // inside-set kept in registers per location; overflow recomputes (exact)
-#define ZN_MAGIC 0x315a4e4f5a575355ull
+#define ZN_MAGIC 0x325a4e4f5a575355ull
 
 struct ZoneHeader {  // 128 bytes, start of the packed table
     uint64_t magic, total_bytes;
@@ -237,12 +237,32 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
     off = align_up(off + tests.size() * sizeof(ZoneTestRec), 256);
     h.off_verts = off;
     off = align_up(off + verts.size() * 8, 256);
+    // flattened for the kernel: fewer dependent loads per location.
+    //   cell ranges  {start,end} per grid cell (one 8-byte load instead of two 4-byte ones)
+    //   cell records a full 64-byte copy of the test record per (cell, test), test id in `pad`
+    //                (one indirection less: envelope and slab parameters arrive with the list entry)
+    //   slab ranges  {start,end} per (test, slab)
+    std::vector<uint32_t> cell_ranges((cell_start.size() - 1) * 2);
+    for (size_t c = 0; c + 1 < cell_start.size(); c++) {
+        cell_ranges[2 * c] = cell_start[c];
+        cell_ranges[2 * c + 1] = cell_start[c + 1];
+    }
+    std::vector<ZoneTestRec> cell_recs(cell_items.size());
+    for (size_t k = 0; k < cell_items.size(); k++) {
+        cell_recs[k] = tests[cell_items[k]];
+        cell_recs[k].pad = cell_items[k];
+    }
+    std::vector<uint32_t> bin_ranges(bin_start.size() * 2, 0);
+    for (size_t k = 0; k + 1 < bin_start.size(); k++) {
+        bin_ranges[2 * k] = bin_start[k];
+        bin_ranges[2 * k + 1] = bin_start[k + 1];  // (the entry after a test's last slab is never read)
+    }
     h.off_cell_start = off;
-    off = align_up(off + cell_start.size() * 4, 256);
+    off = align_up(off + cell_ranges.size() * 4, 256);
     h.off_cell_items = off;
-    off = align_up(off + cell_items.size() * 4, 256);
+    off = align_up(off + cell_recs.size() * sizeof(ZoneTestRec), 256);
     h.off_bin_start = off;
-    off = align_up(off + bin_start.size() * 4, 256);
+    off = align_up(off + bin_ranges.size() * 4, 256);
     h.off_bin_items = off;
     off = align_up(off + bin_items.size() * 8, 256);
     h.off_outside = off;
@@ -252,9 +272,10 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
     memcpy(blob.data(), &h, sizeof h);
     if (!tests.empty()) memcpy(blob.data() + h.off_tests, tests.data(), tests.size() * sizeof(ZoneTestRec));
     if (!verts.empty()) memcpy(blob.data() + h.off_verts, verts.data(), verts.size() * 8);
-    memcpy(blob.data() + h.off_cell_start, cell_start.data(), cell_start.size() * 4);
-    if (!cell_items.empty()) memcpy(blob.data() + h.off_cell_items, cell_items.data(), cell_items.size() * 4);
-    if (!bin_start.empty()) memcpy(blob.data() + h.off_bin_start, bin_start.data(), bin_start.size() * 4);
+    if (!cell_ranges.empty()) memcpy(blob.data() + h.off_cell_start, cell_ranges.data(), cell_ranges.size() * 4);
+    if (!cell_recs.empty())
+        memcpy(blob.data() + h.off_cell_items, cell_recs.data(), cell_recs.size() * sizeof(ZoneTestRec));
+    if (!bin_ranges.empty()) memcpy(blob.data() + h.off_bin_start, bin_ranges.data(), bin_ranges.size() * 4);
     if (!bin_items.empty()) memcpy(blob.data() + h.off_bin_items, bin_items.data(), bin_items.size() * 8);
     if (!outside.empty()) memcpy(blob.data() + h.off_outside, outside.data(), outside.size() * 4);
     return SWGPU_OK;
@@ -369,10 +390,11 @@ __device__ __forceinline__ int zn_sign_det(double x1, double y1, double x2, doub
 
 // RayCrossingCounter.locatePointInRing(p, ring) == INTERIOR restricted to the slab's edges
 __device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, const ZoneTestRec &z, double px, double py) {
-    const uint32_t *bs = (const uint32_t *)(a.blob + a.h.off_bin_start) + z.bin_off;
+    const uint2 *bs = (const uint2 *)(a.blob + a.h.off_bin_start) + z.bin_off;
     const double2 *er = (const double2 *)(a.blob + a.h.off_bin_items);  // edge records, 32 B each (one sector)
-    uint32_t b = zn_cell(py, z.miny, z.inv_bin, z.nbins);
-    uint32_t k0 = __ldg(bs + b), k1 = __ldg(bs + b + 1);
+    const uint32_t b = zn_cell(py, z.miny, z.inv_bin, z.nbins);
+    const uint2 br = __ldg(bs + b);
+    const uint32_t k0 = br.x, k1 = br.y;
     uint32_t crossings = 0;
     bool boundary = false;
     for (uint32_t k = k0; k < k1; k++) {
@@ -411,24 +433,24 @@ __device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, d
     const ZoneHeader &h = a.h;
     if (!(px >= h.gx0 && px <= h.gx1 && py >= h.gy0 && py <= h.gy1)) return;  // outside every envelope (or NaN)
     uint32_t cx = zn_cell(px, h.gx0, h.inv_cx, h.grid_nx), cy = zn_cell(py, h.gy0, h.inv_cy, h.grid_ny);
-    const uint32_t *cs = (const uint32_t *)(a.blob + h.off_cell_start);
-    const uint32_t *ci = (const uint32_t *)(a.blob + h.off_cell_items);
-    const ZoneTestRec *tests = (const ZoneTestRec *)(a.blob + h.off_tests);
-    uint32_t c = cy * h.grid_nx + cx;
-    uint32_t k0 = __ldg(cs + c), k1 = __ldg(cs + c + 1);
-    for (uint32_t k = k0; k < k1; k++) {
-        uint32_t t = __ldg(ci + k);
-        const ZoneTestRec *zp = tests + t;
-        // envelope first (Geometry.contains short-circuit): one 32-byte sector
-        double2 ex = __ldg((const double2 *)zp), ey = __ldg((const double2 *)zp + 1);
+    const uint2 *cs = (const uint2 *)(a.blob + h.off_cell_start);
+    const ZoneTestRec *recs = (const ZoneTestRec *)(a.blob + h.off_cell_items);  // per-cell copies of the records
+    const uint32_t c = cy * h.grid_nx + cx;
+    const uint2 cr = __ldg(cs + c);
+    for (uint32_t k = cr.x; k < cr.y; k++) {
+        const ZoneTestRec *zp = recs + k;
+        // all four 16-byte pieces of the record are requested together (two sectors, one round trip)
+        const double2 ex = __ldg((const double2 *)zp), ey = __ldg((const double2 *)zp + 1);
+        const uint4 m0 = __ldg((const uint4 *)zp + 2);
+        const uint4 m1 = __ldg((const uint4 *)zp + 3);
+        // envelope first (Geometry.contains short-circuit)
         if (!(px >= ex.x && px <= ex.y && py >= ey.x && py <= ey.y)) continue;
+        const uint32_t t = m1.w;  // test id rides in the record's pad word
         ZoneTestRec z;
         z.minx = ex.x;
         z.maxx = ex.y;
         z.miny = ey.x;
         z.maxy = ey.y;
-        uint4 m0 = __ldg((const uint4 *)zp + 2);
-        uint4 m1 = __ldg((const uint4 *)zp + 3);
         z.vtx_off = m0.x;
         z.npts = m0.y;
         z.flags = m0.z;
