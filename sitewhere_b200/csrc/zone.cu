@@ -136,6 +136,10 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
         for (uint32_t i = 0; i < z.npts; i++) {
             xs[i] = xy[2 * i];
             ys[i] = xy[2 * i + 1];
+            if (!std::isfinite(xs[i]) || !std::isfinite(ys[i])) {
+                SW_SET_ERR(ctx, "swgpu_set_zones: test %u has a non-finite vertex", t);
+                return SWGPU_E_INVALID;
+            }
         }
         bool rect = host_is_rectangle(xs.data(), ys.data(), z.npts, minx, maxx, miny, maxy);
         z.flags = (cond[t] ? 1u : 0u) | (rect ? 2u : 0u);
@@ -164,6 +168,11 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
             }
             for (uint32_t bb = 0; bb < nb; bb++) {
                 bin_start.push_back((uint32_t)(bin_items.size() / 4));
+                // rightmost edges first: RayCrossingCounter ignores an edge with both ends left of the
+                // point, so the kernel can stop at the first such edge of the slab
+                std::sort(bins[bb].begin(), bins[bb].end(), [&](uint32_t e1, uint32_t e2) {
+                    return std::max(xs[e1], xs[e1 - 1]) > std::max(xs[e2], xs[e2 - 1]);
+                });
                 for (uint32_t e : bins[bb]) {  // edge record: p1 = ring[e], p2 = ring[e-1], 32 bytes
                     bin_items.push_back(xs[e]);
                     bin_items.push_back(ys[e]);
@@ -388,18 +397,31 @@ __device__ __forceinline__ int zn_sign_det(double x1, double y1, double x2, doub
     return (e > f) - (e < f);
 }
 
+// 256-bit read-only load (sm_100: LDG.E.256): a whole 32-byte edge record / half a test record per request
+struct __align__(32) ZnD4 {
+    double x, y, z, w;
+};
+__device__ __forceinline__ ZnD4 zn_ld256(const void *p) {
+    ZnD4 r;
+    asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+    return r;
+}
+
 // RayCrossingCounter.locatePointInRing(p, ring) == INTERIOR restricted to the slab's edges
 __device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, const ZoneTestRec &z, double px, double py) {
     const uint2 *bs = (const uint2 *)(a.blob + a.h.off_bin_start) + z.bin_off;
-    const double2 *er = (const double2 *)(a.blob + a.h.off_bin_items);  // edge records, 32 B each (one sector)
+    const ZnD4 *er = (const ZnD4 *)(a.blob + a.h.off_bin_items);  // edge records, 32 B each (one sector)
     const uint32_t b = zn_cell(py, z.miny, z.inv_bin, z.nbins);
     const uint2 br = __ldg(bs + b);
     const uint32_t k0 = br.x, k1 = br.y;
     uint32_t crossings = 0;
     bool boundary = false;
     for (uint32_t k = k0; k < k1; k++) {
-        double2 p1 = __ldg(er + 2 * (size_t)k), p2 = __ldg(er + 2 * (size_t)k + 1);
-        if (p1.x < px && p2.x < px) continue;
+        // one 256-bit load per edge record: the kernel is bound by L1 wavefronts (every lane reads a
+        // different record), so halving the load instructions per edge halves that cost
+        const ZnD4 e = zn_ld256(er + k);
+        const double2 p1 = make_double2(e.x, e.y), p2 = make_double2(e.z, e.w);
+        if (p1.x < px && p2.x < px) break;  // slab edges are ordered by max x, descending: the rest are left too
         if (px == p2.x && py == p2.y) {
             boundary = true;
             break;
@@ -439,10 +461,19 @@ __device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, d
     const uint2 cr = __ldg(cs + c);
     for (uint32_t k = cr.x; k < cr.y; k++) {
         const ZoneTestRec *zp = recs + k;
-        // all four 16-byte pieces of the record are requested together (two sectors, one round trip)
-        const double2 ex = __ldg((const double2 *)zp), ey = __ldg((const double2 *)zp + 1);
-        const uint4 m0 = __ldg((const uint4 *)zp + 2);
-        const uint4 m1 = __ldg((const uint4 *)zp + 3);
+        // the 64-byte record as two 256-bit loads, requested together (two sectors, one round trip)
+        const ZnD4 env = zn_ld256(zp);
+        const ZnD4 par = zn_ld256((const uint8_t *)zp + 32);
+        const double2 ex = make_double2(env.x, env.y), ey = make_double2(env.z, env.w);
+        uint4 m0, m1;
+        m0.x = (uint32_t)__double2loint(par.x);
+        m0.y = (uint32_t)__double2hiint(par.x);
+        m0.z = (uint32_t)__double2loint(par.y);
+        m0.w = (uint32_t)__double2hiint(par.y);
+        m1.x = (uint32_t)__double2loint(par.z);
+        m1.y = (uint32_t)__double2hiint(par.z);
+        m1.z = (uint32_t)__double2loint(par.w);
+        m1.w = (uint32_t)__double2hiint(par.w);
         // envelope first (Geometry.contains short-circuit)
         if (!(px >= ex.x && px <= ex.y && py >= ey.x && py <= ey.y)) continue;
         const uint32_t t = m1.w;  // test id rides in the record's pad word
@@ -474,20 +505,24 @@ struct ZnLoc {
     uint32_t n_in, count;
 };
 
-__device__ __forceinline__ void zn_eval(const ZnArgs &a, uint32_t i, uint32_t n_live, ZnLoc &L) {
-    const uint32_t T_out = a.h.n_outside;
+// is row i a location the reference would route to onLocation?
+__device__ __forceinline__ bool zn_row_valid(const ZnArgs &a, uint32_t i, uint32_t n_live) {
     bool valid = i < n_live;
     if (valid && a.meta) {
         uint64_t m = __ldg(a.meta + i);
         uint32_t fl = SWGPU_META_FLAGS(m);
         valid = SWGPU_META_KIND(m) == SWGPU_KIND_LOCATION && (fl & SWGPU_F_HAS_V0) && (fl & SWGPU_F_HAS_V1);
     }
-    L.px = L.py = 0;
+    return valid;
+}
+
+__device__ __forceinline__ void zn_eval_point(const ZnArgs &a, bool valid, double px, double py, ZnLoc &L) {
+    const uint32_t T_out = a.h.n_outside;
+    L.px = px;
+    L.py = py;
     L.n_in = 0;
     uint32_t n_in_icond = 0, n_in_ocond = 0;
     if (valid) {
-        L.px = __ldg(a.lon + i);
-        L.py = __ldg(a.lat + i);
         zn_for_each_inside(a, L.px, L.py, [&](uint32_t t, uint32_t outside_cond) {
             if (L.n_in < ZN_MAXIN) L.ins[L.n_in] = (t << 1) | outside_cond;
             L.n_in++;
@@ -499,6 +534,11 @@ __device__ __forceinline__ void zn_eval(const ZnArgs &a, uint32_t i, uint32_t n_
     }
     // alerts: Inside-condition tests that contain the point + Outside-condition tests that do not
     L.count = valid ? (n_in_icond + (T_out - n_in_ocond)) : 0;
+}
+
+__device__ __forceinline__ void zn_eval(const ZnArgs &a, uint32_t i, uint32_t n_live, ZnLoc &L) {
+    const bool valid = zn_row_valid(a, i, n_live);
+    zn_eval_point(a, valid, valid ? __ldg(a.lon + i) : 0.0, valid ? __ldg(a.lat + i) : 0.0, L);
 }
 
 // writes the location's alert pairs, in test order, starting at `pos`
@@ -718,7 +758,8 @@ int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const u
     const size_t off_inl = ((size_t)n * 4 + 255) / 256 * 256;
     const size_t off_tot = off_inl + (size_t)n * 8;
     const size_t off_base = off_tot + (size_t)ntiles * 8;
-    if (int rc = sw_ensure(ctx, ctx->d_zwork, off_base + (size_t)ntiles * 8)) return rc;
+    const size_t work_bytes = off_base + (size_t)ntiles * 8;
+    if (int rc = sw_ensure(ctx, ctx->d_zwork, work_bytes)) return rc;
     ZnWork w;
     w.cnt = (uint32_t *)ctx->d_zwork.p;
     w.inl = (uint64_t *)((uint8_t *)ctx->d_zwork.p + off_inl);
