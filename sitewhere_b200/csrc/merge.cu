@@ -70,22 +70,54 @@ struct MgArgs {
 
 #define MG_NOSLOT 0xffffffffffffffffull
 
-__device__ __forceinline__ bool mg_key_equal(const uint8_t *arena_key, uint32_t key_len, uint32_t tl,
+// Keys live in the arena as 8-byte words so that equality is a handful of 64-bit compares:
+//   word 0            token length | name length << 16 | kind byte << 32
+//   ceil(tl/8) words  token bytes, zero padded
+//   ceil(nl/8) words  name bytes, zero padded
+// (the snapshot converts to the public form  token_len(2) | kind | token | name).
+__host__ __device__ __forceinline__ uint64_t mg_key_hdr(uint32_t tl, uint32_t nl, uint32_t kindbyte) {
+    return (uint64_t)tl | ((uint64_t)nl << 16) | ((uint64_t)kindbyte << 32);
+}
+__host__ __device__ __forceinline__ uint32_t mg_key_bytes(uint32_t tl, uint32_t nl) {
+    return 8u + ((tl + 7u) & ~7u) + ((nl + 7u) & ~7u);
+}
+// 8 payload bytes starting at p (any alignment) as a little-endian word; bytes past `valid` are zero.
+// Reads only the aligned words that hold valid bytes (the payload buffer is 8-byte aligned).
+__device__ __forceinline__ uint64_t mg_payload_word(const uint8_t *p, uint32_t valid) {
+    const uintptr_t a = (uintptr_t)p;
+    const uint64_t *w = (const uint64_t *)(a & ~(uintptr_t)7);
+    const uint32_t mis = (uint32_t)(a & 7);
+    uint64_t v = __ldg(w) >> (8 * mis);
+    if (mis && (8 - mis) < valid) v |= __ldg(w + 1) << (64 - 8 * mis);
+    if (valid < 8) v &= (1ull << (8 * valid)) - 1;
+    return v;
+}
+__device__ __forceinline__ bool mg_key_equal(const uint64_t *arena_key, uint32_t key_len, uint32_t tl,
                                              uint32_t kindbyte, const uint8_t *tok, const uint8_t *name,
                                              uint32_t nl) {
-    if (key_len != tl + 3 + nl) return false;
-    if (arena_key[0] != (tl & 0xff) || arena_key[1] != (tl >> 8) || arena_key[2] != kindbyte) return false;
-    for (uint32_t i = 0; i < tl; i++)
-        if (arena_key[3 + i] != __ldg(tok + i)) return false;
-    for (uint32_t i = 0; i < nl; i++)
-        if (arena_key[3 + tl + i] != __ldg(name + i)) return false;
+    if (key_len != mg_key_bytes(tl, nl)) return false;
+    // arena words were written during this launch by other SMs: read them at L2 (never from a stale L1 line)
+    if (__ldcg(arena_key) != mg_key_hdr(tl, nl, kindbyte)) return false;
+    uint32_t w = 1;
+    for (uint32_t i = 0; i < tl; i += 8, w++)
+        if (__ldcg(arena_key + w) != mg_payload_word(tok + i, min(8u, tl - i))) return false;
+    for (uint32_t i = 0; i < nl; i += 8, w++)
+        if (__ldcg(arena_key + w) != mg_payload_word(name + i, min(8u, nl - i))) return false;
     return true;
+}
+__device__ __forceinline__ uint64_t mg_ld_acquire_u64(const uint64_t *p) {
+    uint64_t v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
 }
 
 __global__ void __launch_bounds__(MG_THREADS) merge_upsert_kernel(MgArgs a) {
     const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n_rows) : a.n_rows;
-    const uint32_t r = blockIdx.x * MG_THREADS + threadIdx.x;
-    if (r >= n_live) return;
+    const uint32_t ridx = blockIdx.x * MG_THREADS + threadIdx.x;
+    if (ridx >= n_live) return;
+    // newest rows first: CTAs start roughly in index order, so for a key with several rows in the batch the
+    // winner tends to arrive first and the older rows lose their atomicMax at once (no publish work for them)
+    const uint32_t r = n_live - 1 - ridx;
     a.slot_idx[r] = MG_NOSLOT;
     const uint64_t m = __ldg(a.meta + r);
     const uint32_t kind = SWGPU_META_KIND(m), fl = SWGPU_META_FLAGS(m);
@@ -94,7 +126,7 @@ __global__ void __launch_bounds__(MG_THREADS) merge_upsert_kernel(MgArgs a) {
     const uint64_t ts = __ldg(a.token_span + r), ns = __ldg(a.name_span + r);
     const uint32_t tl = SWGPU_SPAN_LEN(ts);
     const uint32_t nl = kind == SWGPU_KIND_LOCATION ? 0u : SWGPU_SPAN_LEN(ns);
-    if (tl > 0xffffu) {
+    if (tl > 0xffffu || nl > 0xffffu) {
         atomicAdd(&a.ctr->key_too_long, 1ull);
         return;
     }
@@ -104,15 +136,28 @@ __global__ void __launch_bounds__(MG_THREADS) merge_upsert_kernel(MgArgs a) {
                               kindbyte);
     const uint64_t want = (h & ~3ull) | 1ull;
     uint64_t s = (h >> 2) & a.mask;
+    // The row's key as arena words, fetched BEFORE the table is probed so that the payload loads and the
+    // (random, DRAM-latency) slot load are in flight together.  Keys of up to 32 + 16 bytes stay in
+    // registers; longer ones are compared word by word on demand.
+    const bool fast = tl <= 32 && nl <= 16;
+    const uint32_t tw = (tl + 7) >> 3, nw = (nl + 7) >> 3;
+    uint64_t kw[7];
+    kw[0] = mg_key_hdr(tl, nl, kindbyte);
+    if (fast) {
+#pragma unroll
+        for (uint32_t i = 0; i < 4; i++) kw[1 + i] = i < tw ? mg_payload_word(tok + 8 * i, min(8u, tl - 8 * i)) : 0ull;
+#pragma unroll
+        for (uint32_t i = 0; i < 2; i++) kw[5 + i] = i < nw ? mg_payload_word(name + 8 * i, min(8u, nl - 8 * i)) : 0ull;
+    }
     for (uint64_t probes = 0; probes <= a.mask; probes++, s = (s + 1) & a.mask) {
         MgSlot *sl = a.slots + s;
-        uint64_t tag = sw_ld_volatile_u64(&sl->tag);
+        uint64_t tag = mg_ld_acquire_u64(&sl->tag);  // acquire: a published tag makes the key words visible
         if (tag == 0) {
             unsigned long long old =
                 atomicCAS((unsigned long long *)&sl->tag, 0ull, (unsigned long long)(want | MG_PENDING));
             if (old == 0) {
-                // claimed: publish the key bytes, then clear the pending bit
-                const uint32_t kl = tl + 3 + nl;
+                // claimed: publish the key words, then clear the pending bit
+                const uint32_t kl = mg_key_bytes(tl, nl);
                 unsigned long long off = atomicAdd(&a.ctr->arena_top, (unsigned long long)kl);
                 if (off + kl > a.arena_cap) {
                     atomicAdd(&a.ctr->arena_full, 1ull);
@@ -122,12 +167,11 @@ __global__ void __launch_bounds__(MG_THREADS) merge_upsert_kernel(MgArgs a) {
                     sw_st_volatile_u64(&sl->tag, want);
                     return;
                 }
-                uint8_t *k = a.arena + off;
-                k[0] = (uint8_t)(tl & 0xff);
-                k[1] = (uint8_t)(tl >> 8);
-                k[2] = (uint8_t)kindbyte;
-                for (uint32_t i = 0; i < tl; i++) k[3 + i] = __ldg(tok + i);
-                for (uint32_t i = 0; i < nl; i++) k[3 + tl + i] = __ldg(name + i);
+                uint64_t *k = (uint64_t *)(a.arena + off);
+                uint32_t w = 0;
+                k[w++] = mg_key_hdr(tl, nl, kindbyte);
+                for (uint32_t i = 0; i < tl; i += 8) k[w++] = mg_payload_word(tok + i, min(8u, tl - i));
+                for (uint32_t i = 0; i < nl; i += 8) k[w++] = mg_payload_word(name + i, min(8u, nl - i));
                 sl->key_off = off;
                 sl->key_len = kl;
                 atomicAdd(&a.ctr->n_keys, 1ull);
@@ -138,19 +182,37 @@ __global__ void __launch_bounds__(MG_THREADS) merge_upsert_kernel(MgArgs a) {
             tag = old;
         }
         if ((tag & ~MG_PENDING) == want) {
-            while (tag & MG_PENDING) tag = sw_ld_volatile_u64(&sl->tag);  // the claimer is publishing
-            __threadfence();
-            const uint32_t kl = *(volatile uint32_t *)&sl->key_len;
-            const uint64_t ko = *(volatile uint64_t *)&sl->key_off;
-            if (kl != 0xffffffffu && mg_key_equal(a.arena + ko, kl, tl, kindbyte, tok, name, nl)) break;
+            while (tag & MG_PENDING) tag = mg_ld_acquire_u64(&sl->tag);  // the claimer is publishing (rare)
+            const uint32_t kl = __ldcg(&sl->key_len);
+            const uint64_t ko = __ldcg(&sl->key_off);
+            if (kl == mg_key_bytes(tl, nl)) {  // (a poisoned slot has key_len 0xffffffff)
+                const uint64_t *ak = (const uint64_t *)(a.arena + ko);
+                if (fast) {
+                    // all arena words requested at once, then compared with the registers
+                    uint64_t av[7];
+#pragma unroll
+                    for (uint32_t i = 0; i < 7; i++) {
+                        const bool on = i == 0 || (i >= 1 && i - 1 < tw) || (i >= 5 && i - 5 < nw);
+                        const uint32_t widx = i == 0 ? 0u : (i < 5 ? i : 1 + tw + (i - 5));
+                        av[i] = on ? __ldcg(ak + widx) : 0ull;
+                    }
+                    bool eq = true;
+#pragma unroll
+                    for (uint32_t i = 0; i < 7; i++) eq = eq && av[i] == kw[i];
+                    if (eq) break;
+                } else if (mg_key_equal(ak, kl, tl, kindbyte, tok, name, nl))
+                    break;
+            }
         }
         if (probes == a.mask) {
             atomicAdd(&a.ctr->table_full, 1ull);
             return;
         }
     }
-    atomicMax((unsigned long long *)&a.slots[s].best, (unsigned long long)(a.seq_base + r + 1));
-    a.slot_idx[r] = s;
+    const unsigned long long mine = (unsigned long long)(a.seq_base + r + 1);
+    const unsigned long long old = atomicMax((unsigned long long *)&a.slots[s].best, mine);
+    // a row that did not raise the maximum can never be the final winner: it needs no publish step
+    a.slot_idx[r] = old < mine ? s : MG_NOSLOT;
 }
 
 __global__ void __launch_bounds__(MG_THREADS) merge_publish_kernel(MgArgs a) {
@@ -459,8 +521,18 @@ extern "C" int32_t swgpu_state_snapshot(swgpu_ctx *ctx, uint64_t max_keys, uint6
         out->event_date[k] = s.date;
         out->value[k] = s.value;
         out->key_off[k] = off;
-        memcpy(out->key_bytes + off, arena.data() + s.key_off, s.key_len);
-        off += s.key_len;
+        // arena words -> public key form  token_len(2) | kind | token | name
+        const uint8_t *ak = arena.data() + s.key_off;
+        uint64_t hdr;
+        memcpy(&hdr, ak, 8);
+        const uint32_t tl = (uint32_t)(hdr & 0xffff), nl = (uint32_t)((hdr >> 16) & 0xffff);
+        uint8_t *pk = out->key_bytes + off;
+        pk[0] = (uint8_t)(tl & 0xff);
+        pk[1] = (uint8_t)(tl >> 8);
+        pk[2] = (uint8_t)(hdr >> 32);
+        memcpy(pk + 3, ak + 8, tl);
+        memcpy(pk + 3 + tl, ak + 8 + ((tl + 7u) & ~7u), nl);
+        off += 3 + tl + nl;
         k++;
     }
     out->key_off[k] = off;
@@ -483,11 +555,14 @@ extern "C" int32_t swgpu_state_restore(swgpu_ctx *ctx, const swgpu_state_rows *i
     if (!ctx || (n_keys && !in)) return SWGPU_E_INVALID;
     if (int rc = swgpu_state_clear(ctx)) return rc;
     if (n_keys == 0) return SWGPU_OK;
-    const uint64_t kbytes = in->key_off[n_keys];
+    // arena bytes in the internal word form: at most 8 (header) + 14 (padding) more than the public key
+    const uint64_t kbytes = in->key_off[n_keys] + 24 * n_keys;
     if (int rc = mg_reserve(ctx, n_keys, kbytes)) return rc;
     MgState *st = (MgState *)ctx->state;
     std::vector<MgSlot> slots(st->cap);
     memset(slots.data(), 0, slots.size() * sizeof(MgSlot));
+    std::vector<uint8_t> arena;
+    arena.reserve(kbytes);
     const uint64_t mask = st->cap - 1;
     for (uint64_t k = 0; k < n_keys; k++) {
         const uint8_t *key = in->key_bytes + in->key_off[k];
@@ -512,8 +587,18 @@ extern "C" int32_t swgpu_state_restore(swgpu_ctx *ctx, const swgpu_state_rows *i
         MgSlot &d = slots[s];
         d.tag = (h & ~3ull) | 1ull;
         d.best = in->seq[k] + 1;
-        d.key_off = in->key_off[k];
-        d.key_len = kl;
+        if (tl > 0xffffu || nl > 0xffffu) {
+            SW_SET_ERR(ctx, "swgpu_state_restore: key %llu too long", (unsigned long long)k);
+            return SWGPU_E_INVALID;
+        }
+        d.key_off = arena.size();
+        d.key_len = mg_key_bytes(tl, nl);
+        arena.resize(arena.size() + d.key_len, 0);
+        uint8_t *ak = arena.data() + d.key_off;
+        const uint64_t hdr = mg_key_hdr(tl, nl, kindbyte);
+        memcpy(ak, &hdr, 8);
+        memcpy(ak + 8, key + 3, tl);
+        memcpy(ak + 8 + ((tl + 7u) & ~7u), key + 3 + tl, nl);
         d.id_hi = in->id_hi[k];
         d.id_lo = in->id_lo[k];
         d.date = in->event_date[k];
@@ -522,9 +607,9 @@ extern "C" int32_t swgpu_state_restore(swgpu_ctx *ctx, const swgpu_state_rows *i
     MgCounters c;
     memset(&c, 0, sizeof c);
     c.n_keys = n_keys;
-    c.arena_top = kbytes;
+    c.arena_top = arena.size();
     SW_CUDA(ctx, cudaMemcpyAsync(st->slots, slots.data(), slots.size() * sizeof(MgSlot), cudaMemcpyHostToDevice, ctx->stream));
-    SW_CUDA(ctx, cudaMemcpyAsync(st->arena, in->key_bytes, kbytes, cudaMemcpyHostToDevice, ctx->stream));
+    SW_CUDA(ctx, cudaMemcpyAsync(st->arena, arena.data(), arena.size(), cudaMemcpyHostToDevice, ctx->stream));
     SW_CUDA(ctx, cudaMemcpyAsync(st->ctr, &c, sizeof c, cudaMemcpyHostToDevice, ctx->stream));
     SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     st->keys_upper = n_keys;
