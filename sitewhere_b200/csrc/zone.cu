@@ -22,9 +22,9 @@
 
 #define ZN_THREADS 256
 #define ZN_MAXIN 8  // inside-set kept in registers per location; overflow recomputes (exact)
-#define ZN_MAGIC 0x325a4e4f5a575355ull
+#define ZN_MAGIC 0x335a4e4f5a575355ull  // "USWZONZ3": table layout version 3
 
-struct ZoneHeader {  // 128 bytes, start of the packed table
+struct ZoneHeader {  // start of the packed table
     uint64_t magic, total_bytes;
     uint32_t n_tests, n_outside, grid_nx, grid_ny;
     double gx0, gy0, gx1, gy1;  // union of envelopes
@@ -33,7 +33,7 @@ struct ZoneHeader {  // 128 bytes, start of the packed table
 };
 static_assert(sizeof(ZoneHeader) == 136, "ZoneHeader layout");
 
-struct ZoneTestRec {  // 64 bytes
+struct ZoneTestRec {  // 64 bytes, one per test (exact envelope first: the rectangle path reads it as one 256-bit load)
     double minx, maxx, miny, maxy;
     uint32_t vtx_off, npts;  // closed ring in verts[]
     uint32_t flags, nbins;   // flags: bit0 cond == Outside, bit1 isRectangle
@@ -41,6 +41,31 @@ struct ZoneTestRec {  // 64 bytes
     uint32_t bin_off, pad;
 };
 static_assert(sizeof(ZoneTestRec) == 64, "ZoneTestRec layout");
+
+// What one location needs in order to test one zone: 32 bytes = one 256-bit load = one L1 wavefront.
+// The grid holds one of these per cell, so the common case (a cell overlapped by a single zone
+// envelope) costs a single dependent load before the edges.  A cell overlapped by several envelopes
+// holds a list head instead (ZC_LIST: `bin_off` = first entry in the list array, `t` = entries).
+//   minx..maxy  the zone's envelope rounded OUTWARD to float.  Only ever used to reject: a point
+//               between the rounded and the exact border goes on to the ring test, which gives the
+//               same answer Geometry.contains' envelope short-circuit would (outside).
+//   miny, inv_bin  also the y-slab function: slab = zn_cell(py, (double)miny, (double)inv_bin, nbins).
+//               Any origin/scale works as long as registration and lookup use the same one.
+//   bin_off     first edge record of slab 0 (slabs `stride` records apart, each list ended by a
+//               sentinel edge at x = -inf), or with ZC_RANGES the first {start,end} slab range.
+struct ZnCellRec {
+    float minx, maxx, miny, maxy;
+    float inv_bin;
+    uint32_t bin_off;
+    uint32_t t;
+    uint32_t info;  // bits 0..7 flags, 8..19 slab count, 20..31 slab stride
+};
+static_assert(sizeof(ZnCellRec) == 32, "ZnCellRec layout");
+#define ZC_OUTSIDE 1u   // alert condition == Outside
+#define ZC_RECT 2u      // JTS isRectangle: RectangleContains on the exact envelope
+#define ZC_RANGES 4u    // uneven slabs: {start,end} ranges instead of a fixed stride
+#define ZC_LIST 0x80u   // list head
+#define ZC_MAX_STRIDE 4095u
 
 // monotone cell function shared by host (registration) and device (lookup); separate IEEE
 // sub and mul (no contraction) so both sides round identically.
@@ -77,6 +102,18 @@ static bool host_is_rectangle(const double *x, const double *y, uint32_t npts, d
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// nearest floats at or below / at or above v (±inf when v is beyond the float range: still a valid bound)
+static float f_down(double v) {
+    float f = (float)v;
+    if ((double)f > v) f = nextafterf(f, -INFINITY);
+    return f;
+}
+static float f_up(double v) {
+    float f = (float)v;
+    if ((double)f < v) f = nextafterf(f, INFINITY);
+    return f;
+}
+
 static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, const double *lon,
                            const double *lat, const uint8_t *cond, std::vector<uint8_t> &blob) {
     std::vector<ZoneTestRec> tests(T);
@@ -101,8 +138,9 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
     }
     verts.reserve(total_pts * 2);
     double gx0 = INFINITY, gy0 = INFINITY, gx1 = -INFINITY, gy1 = -INFINITY;
-    std::vector<uint32_t> bin_start;
-    std::vector<double> bin_items;  // per slab: the edges that can touch it, as (x1,y1,x2,y2) records
+    std::vector<uint32_t> bin_ranges;  // {start,end} per slab, for tests with ZC_RANGES
+    std::vector<double> bin_items;     // per slab: the edges that can touch it, as (x1,y1,x2,y2) records
+    std::vector<ZnCellRec> crecs(T);
     for (uint32_t t = 0; t < T; t++) {
         ZoneTestRec &z = tests[t];
         memset(&z, 0, sizeof z);
@@ -148,39 +186,89 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
         gx1 = std::max(gx1, maxx);
         gy0 = std::min(gy0, miny);
         gy1 = std::max(gy1, maxy);
+        // the compact record the grid cells carry
+        ZnCellRec &cr = crecs[t];
+        memset(&cr, 0, sizeof cr);
+        cr.minx = f_down(minx);
+        cr.maxx = f_up(maxx);
+        cr.miny = f_down(miny);
+        cr.maxy = f_up(maxy);
+        cr.t = t;
         // y-slabs over edges i = 1..npts-1 (edge i joins ring[i] and ring[i-1])
-        z.bin_off = (uint32_t)bin_start.size();
         if (rect) {
             z.nbins = 0;
             z.inv_bin = 0;
+            cr.info = z.flags;
         } else {
             uint32_t nb = std::max(1u, std::min(64u, (z.npts - 1 + 3) / 4));
-            double h = maxy - miny;
-            double inv = (h > 0 && std::isfinite((double)nb / h)) ? (double)nb / h : 0.0;
-            if (inv == 0.0) nb = 1;
+            const double y0 = (double)cr.miny;  // slab origin: at or below every vertex
+            const double h = maxy - y0;
+            float invf = 0.f;
+            if (h > 0 && std::isfinite(h)) {
+                double invd = (double)nb / h;
+                invf = (float)invd;
+                if ((double)invf > invd) invf = nextafterf(invf, 0.f);
+                if (!std::isfinite(invf) || !(invf > 0.f)) invf = 0.f;
+            }
+            if (invf == 0.f) nb = 1;
+            const double inv = (double)invf;
             z.nbins = nb;
             z.inv_bin = inv;
+            cr.inv_bin = invf;
             std::vector<std::vector<uint32_t>> bins(nb);
+            size_t refs = 0, longest = 0;
             for (uint32_t i = 1; i < z.npts; i++) {
                 double y1 = ys[i], y2 = ys[i - 1];
-                uint32_t lo = zn_cell(std::min(y1, y2), miny, inv, nb), hi = zn_cell(std::max(y1, y2), miny, inv, nb);
+                uint32_t lo = zn_cell(std::min(y1, y2), y0, inv, nb), hi = zn_cell(std::max(y1, y2), y0, inv, nb);
                 for (uint32_t bb = lo; bb <= hi; bb++) bins[bb].push_back(i);
             }
             for (uint32_t bb = 0; bb < nb; bb++) {
-                bin_start.push_back((uint32_t)(bin_items.size() / 4));
+                refs += bins[bb].size();
+                longest = std::max(longest, bins[bb].size());
                 // rightmost edges first: RayCrossingCounter ignores an edge with both ends left of the
                 // point, so the kernel can stop at the first such edge of the slab
                 std::sort(bins[bb].begin(), bins[bb].end(), [&](uint32_t e1, uint32_t e2) {
                     return std::max(xs[e1], xs[e1 - 1]) > std::max(xs[e2], xs[e2 - 1]);
                 });
-                for (uint32_t e : bins[bb]) {  // edge record: p1 = ring[e], p2 = ring[e-1], 32 bytes
-                    bin_items.push_back(xs[e]);
-                    bin_items.push_back(ys[e]);
-                    bin_items.push_back(xs[e - 1]);
-                    bin_items.push_back(ys[e - 1]);
-                }
             }
-            bin_start.push_back((uint32_t)(bin_items.size() / 4));
+            auto put_edge = [&](uint32_t e) {  // edge record: p1 = ring[e], p2 = ring[e-1], 32 bytes
+                bin_items.push_back(xs[e]);
+                bin_items.push_back(ys[e]);
+                bin_items.push_back(xs[e - 1]);
+                bin_items.push_back(ys[e - 1]);
+            };
+            // Slabs of similar length are stored a fixed stride apart, each ended by a sentinel edge
+            // whose ends are at x = -inf ("both ends left of the point": the loop's own exit test), so
+            // the kernel needs no slab range.  Very uneven slabs would waste the padding: they keep
+            // ranges.
+            const size_t stride = longest + 1;
+            const bool fixed = stride <= ZC_MAX_STRIDE && (size_t)nb * stride <= 4 * refs + 64 &&
+                               bin_items.size() / 4 + (size_t)nb * stride < 0xffffffffull;
+            if (fixed) {
+                cr.bin_off = z.bin_off = (uint32_t)(bin_items.size() / 4);
+                for (uint32_t bb = 0; bb < nb; bb++) {
+                    for (uint32_t e : bins[bb]) put_edge(e);
+                    for (size_t k = bins[bb].size(); k < stride; k++) {
+                        bin_items.push_back(-INFINITY);
+                        bin_items.push_back(0.0);
+                        bin_items.push_back(-INFINITY);
+                        bin_items.push_back(0.0);
+                    }
+                }
+                cr.info = z.flags | (nb << 8) | ((uint32_t)stride << 20);
+            } else {
+                cr.bin_off = z.bin_off = (uint32_t)(bin_ranges.size() / 2);
+                for (uint32_t bb = 0; bb < nb; bb++) {
+                    bin_ranges.push_back((uint32_t)(bin_items.size() / 4));
+                    for (uint32_t e : bins[bb]) put_edge(e);
+                    bin_ranges.push_back((uint32_t)(bin_items.size() / 4));
+                }
+                cr.info = z.flags | ZC_RANGES | (nb << 8);
+            }
+            if (bin_items.size() / 4 >= 0xffffffffull) {
+                SW_SET_ERR(ctx, "swgpu_set_zones: edge table too large");
+                return SWGPU_E_INVALID;
+            }
         }
     }
     // grid over envelopes
@@ -246,30 +334,32 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
     off = align_up(off + tests.size() * sizeof(ZoneTestRec), 256);
     h.off_verts = off;
     off = align_up(off + verts.size() * 8, 256);
-    // flattened for the kernel: fewer dependent loads per location.
-    //   cell ranges  {start,end} per grid cell (one 8-byte load instead of two 4-byte ones)
-    //   cell records a full 64-byte copy of the test record per (cell, test), test id in `pad`
-    //                (one indirection less: envelope and slab parameters arrive with the list entry)
-    //   slab ranges  {start,end} per (test, slab)
-    std::vector<uint32_t> cell_ranges((cell_start.size() - 1) * 2);
+    // flattened for the kernel: as few dependent loads per location as the data allows.
+    //   cell table   one ZnCellRec per grid cell: the only zone whose envelope overlaps the cell, or a
+    //                record no point passes (empty cell), or the head of a list
+    //   cell lists   ZnCellRec copies, in test order, for cells overlapped by several envelopes
+    //   slab ranges  {start,end} per slab, only for tests with ZC_RANGES
+    std::vector<ZnCellRec> cell_tab(cell_start.size() - 1), cell_list;
     for (size_t c = 0; c + 1 < cell_start.size(); c++) {
-        cell_ranges[2 * c] = cell_start[c];
-        cell_ranges[2 * c + 1] = cell_start[c + 1];
-    }
-    std::vector<ZoneTestRec> cell_recs(cell_items.size());
-    for (size_t k = 0; k < cell_items.size(); k++) {
-        cell_recs[k] = tests[cell_items[k]];
-        cell_recs[k].pad = cell_items[k];
-    }
-    std::vector<uint32_t> bin_ranges(bin_start.size() * 2, 0);
-    for (size_t k = 0; k + 1 < bin_start.size(); k++) {
-        bin_ranges[2 * k] = bin_start[k];
-        bin_ranges[2 * k + 1] = bin_start[k + 1];  // (the entry after a test's last slab is never read)
+        const uint32_t k0 = cell_start[c], k1 = cell_start[c + 1];
+        ZnCellRec &e = cell_tab[c];
+        memset(&e, 0, sizeof e);
+        if (k1 == k0) {
+            e.minx = e.miny = INFINITY;  // rejects every point
+            e.maxx = e.maxy = -INFINITY;
+        } else if (k1 - k0 == 1) {
+            e = crecs[cell_items[k0]];
+        } else {
+            e.info = ZC_LIST;
+            e.bin_off = (uint32_t)cell_list.size();
+            e.t = k1 - k0;
+            for (uint32_t k = k0; k < k1; k++) cell_list.push_back(crecs[cell_items[k]]);
+        }
     }
     h.off_cell_start = off;
-    off = align_up(off + cell_ranges.size() * 4, 256);
+    off = align_up(off + cell_tab.size() * sizeof(ZnCellRec), 256);
     h.off_cell_items = off;
-    off = align_up(off + cell_recs.size() * sizeof(ZoneTestRec), 256);
+    off = align_up(off + cell_list.size() * sizeof(ZnCellRec), 256);
     h.off_bin_start = off;
     off = align_up(off + bin_ranges.size() * 4, 256);
     h.off_bin_items = off;
@@ -281,9 +371,9 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
     memcpy(blob.data(), &h, sizeof h);
     if (!tests.empty()) memcpy(blob.data() + h.off_tests, tests.data(), tests.size() * sizeof(ZoneTestRec));
     if (!verts.empty()) memcpy(blob.data() + h.off_verts, verts.data(), verts.size() * 8);
-    if (!cell_ranges.empty()) memcpy(blob.data() + h.off_cell_start, cell_ranges.data(), cell_ranges.size() * 4);
-    if (!cell_recs.empty())
-        memcpy(blob.data() + h.off_cell_items, cell_recs.data(), cell_recs.size() * sizeof(ZoneTestRec));
+    if (!cell_tab.empty()) memcpy(blob.data() + h.off_cell_start, cell_tab.data(), cell_tab.size() * sizeof(ZnCellRec));
+    if (!cell_list.empty())
+        memcpy(blob.data() + h.off_cell_items, cell_list.data(), cell_list.size() * sizeof(ZnCellRec));
     if (!bin_ranges.empty()) memcpy(blob.data() + h.off_bin_start, bin_ranges.data(), bin_ranges.size() * 4);
     if (!bin_items.empty()) memcpy(blob.data() + h.off_bin_items, bin_items.data(), bin_items.size() * 8);
     if (!outside.empty()) memcpy(blob.data() + h.off_outside, outside.data(), outside.size() * 4);
@@ -389,10 +479,40 @@ struct ZnArgs {
 
 // exact sign of x1*y2 - y1*x2: products with their rounding errors (fma), compared as the
 // monotone rounding of two reals; ties broken by the error terms.
+// Rounding is monotone, so rounded products that differ already order the exact ones — even when a
+// product over- or underflowed.  Only a tie needs the rounding errors, and those are exact (fma) only
+// while the products are well inside the normal range; a tie outside it (0 == -0 from an underflow,
+// inf == inf) takes the scaled comparison below.
+__device__ __noinline__ int zn_sign_det_scaled(double x1, double y1, double x2, double y2) {
+    const int sp = ((x1 > 0) - (x1 < 0)) * ((y2 > 0) - (y2 < 0));
+    const int sq = ((y1 > 0) - (y1 < 0)) * ((x2 > 0) - (x2 < 0));
+    if (sp != sq) return sp > sq ? 1 : -1;
+    if (sp == 0) return 0;
+    // same sign: compare |x1*y2| with |y1*x2| as (double-double mantissa product, exponent sum)
+    int ea, eb, ec, ed;
+    const double ma = frexp(fabs(x1), &ea), md = frexp(fabs(y2), &ed);
+    const double mb = frexp(fabs(y1), &eb), mc = frexp(fabs(x2), &ec);
+    const double hp = __dmul_rn(ma, md), lp = __fma_rn(ma, md, -hp);  // in [0.25, 1): no underflow, exact
+    double hq = __dmul_rn(mb, mc), lq = __fma_rn(mb, mc, -hq);
+    const int d = (ea + ed) - (eb + ec);
+    int cmp;
+    if (d >= 2)
+        cmp = 1;
+    else if (d <= -2)
+        cmp = -1;
+    else {
+        hq = ldexp(hq, -d);  // by 1/2, 1 or 2: exact
+        lq = ldexp(lq, -d);
+        cmp = hp > hq ? 1 : hp < hq ? -1 : (lp > lq) - (lp < lq);
+    }
+    return sp * cmp;
+}
 __device__ __forceinline__ int zn_sign_det(double x1, double y1, double x2, double y2) {
     double p = __dmul_rn(x1, y2), q = __dmul_rn(y1, x2);
     if (p > q) return 1;
     if (p < q) return -1;
+    const double ap = fabs(p);
+    if (!(ap >= 0x1p-960 && ap <= 0x1p1000)) return zn_sign_det_scaled(x1, y1, x2, y2);
     double e = __fma_rn(x1, y2, -p), f = __fma_rn(y1, x2, -q);
     return (e > f) - (e < f);
 }
@@ -407,47 +527,50 @@ __device__ __forceinline__ ZnD4 zn_ld256(const void *p) {
     return r;
 }
 
-// RayCrossingCounter.locatePointInRing(p, ring) == INTERIOR restricted to the slab's edges
-__device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, const ZoneTestRec &z, double px, double py) {
-    const uint2 *bs = (const uint2 *)(a.blob + a.h.off_bin_start) + z.bin_off;
+// RayCrossingCounter.locatePointInRing(p, ring) == INTERIOR restricted to the slab's edges.
+// countSegment's tests (RayCrossingCounter.java:121-161), regrouped so that an edge that does not
+// straddle the ray costs five comparisons instead of ten:
+//   both ends left of p                        -> ignored (and, by the x ordering, so is the rest)
+//   the ends are on different sides of y = py  -> the crossing test; a zero determinant is "on the
+//       segment", which is also what the reference's earlier `p == p2` test reports for such an edge
+//   otherwise p can only touch the edge if p2.y == py (then p1.y <= py): at p2, or on a horizontal edge
+__device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, uint32_t info, uint32_t bin_off, double y0, double inv,
+                                                 double px, double py) {
     const ZnD4 *er = (const ZnD4 *)(a.blob + a.h.off_bin_items);  // edge records, 32 B each (one sector)
-    const uint32_t b = zn_cell(py, z.miny, z.inv_bin, z.nbins);
-    const uint2 br = __ldg(bs + b);
-    const uint32_t k0 = br.x, k1 = br.y;
+    const uint32_t b = zn_cell(py, y0, inv, (info >> 8) & 0xfffu);
+    uint32_t k, k1;
+    if (info & ZC_RANGES) {
+        const uint2 br = __ldg((const uint2 *)(a.blob + a.h.off_bin_start) + bin_off + b);
+        k = br.x;
+        k1 = br.y;
+    } else {  // fixed stride; the slab's sentinel ends the loop
+        k = bin_off + b * (info >> 20);
+        k1 = 0xffffffffu;
+    }
     uint32_t crossings = 0;
-    bool boundary = false;
-    for (uint32_t k = k0; k < k1; k++) {
-        // one 256-bit load per edge record: the kernel is bound by L1 wavefronts (every lane reads a
-        // different record), so halving the load instructions per edge halves that cost
-        const ZnD4 e = zn_ld256(er + k);
-        const double2 p1 = make_double2(e.x, e.y), p2 = make_double2(e.z, e.w);
-        if (p1.x < px && p2.x < px) break;  // slab edges are ordered by max x, descending: the rest are left too
-        if (px == p2.x && py == p2.y) {
-            boundary = true;
-            break;
-        }
-        if (p1.y == py && p2.y == py) {
-            double mn = fmin(p1.x, p2.x), mx = fmax(p1.x, p2.x);
-            if (px >= mn && px <= mx) {
-                boundary = true;
-                break;
-            }
-            continue;
-        }
-        if ((p1.y > py && p2.y <= py) || (p2.y > py && p1.y <= py)) {
-            double x1 = __dsub_rn(p1.x, px), y1 = __dsub_rn(p1.y, py);
-            double x2 = __dsub_rn(p2.x, px), y2 = __dsub_rn(p2.y, py);
+    for (; k < k1; k++) {
+        // one 256-bit load per edge record: every lane reads a different record, so the cost is L1
+        // wavefronts per load instruction, not bytes
+        const ZnD4 e = zn_ld256(er + k);  // p1 = (x,y)  p2 = (z,w)
+        if (e.x < px && e.z < px) break;  // slab edges are ordered by max x, descending: the rest are left too
+        const bool up1 = e.y > py, up2 = e.w > py;
+        if (up1 != up2) {
+            double x1 = __dsub_rn(e.x, px), y1 = __dsub_rn(e.y, py);
+            double x2 = __dsub_rn(e.z, px), y2 = __dsub_rn(e.w, py);
             int s = zn_sign_det(x1, y1, x2, y2);
-            if (s == 0) {
-                boundary = true;
-                break;
-            }
+            if (s == 0) return false;  // on the boundary
             if (y2 < y1) s = -s;
             if (s > 0) crossings++;
+        } else if (e.w == py) {
+            if (px == e.z) return false;  // p is the vertex p2
+            if (e.y == py && px >= fmin(e.x, e.z) && px <= fmax(e.x, e.z)) return false;  // on a horizontal edge
         }
     }
-    return !boundary && (crossings & 1);
+    return crossings & 1;
 }
+
+__device__ __forceinline__ float zn_lo_f(double v) { return __int_as_float(__double2loint(v)); }
+__device__ __forceinline__ float zn_hi_f(double v) { return __int_as_float(__double2hiint(v)); }
 
 // Visit the tests whose polygon contains (px,py), in ascending test order.
 template <typename F>
@@ -455,45 +578,32 @@ __device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, d
     const ZoneHeader &h = a.h;
     if (!(px >= h.gx0 && px <= h.gx1 && py >= h.gy0 && py <= h.gy1)) return;  // outside every envelope (or NaN)
     uint32_t cx = zn_cell(px, h.gx0, h.inv_cx, h.grid_nx), cy = zn_cell(py, h.gy0, h.inv_cy, h.grid_ny);
-    const uint2 *cs = (const uint2 *)(a.blob + h.off_cell_start);
-    const ZoneTestRec *recs = (const ZoneTestRec *)(a.blob + h.off_cell_items);  // per-cell copies of the records
-    const uint32_t c = cy * h.grid_nx + cx;
-    const uint2 cr = __ldg(cs + c);
-    for (uint32_t k = cr.x; k < cr.y; k++) {
-        const ZoneTestRec *zp = recs + k;
-        // the 64-byte record as two 256-bit loads, requested together (two sectors, one round trip)
-        const ZnD4 env = zn_ld256(zp);
-        const ZnD4 par = zn_ld256((const uint8_t *)zp + 32);
-        const double2 ex = make_double2(env.x, env.y), ey = make_double2(env.z, env.w);
-        uint4 m0, m1;
-        m0.x = (uint32_t)__double2loint(par.x);
-        m0.y = (uint32_t)__double2hiint(par.x);
-        m0.z = (uint32_t)__double2loint(par.y);
-        m0.w = (uint32_t)__double2hiint(par.y);
-        m1.x = (uint32_t)__double2loint(par.z);
-        m1.y = (uint32_t)__double2hiint(par.z);
-        m1.z = (uint32_t)__double2loint(par.w);
-        m1.w = (uint32_t)__double2hiint(par.w);
-        // envelope first (Geometry.contains short-circuit)
-        if (!(px >= ex.x && px <= ex.y && py >= ey.x && py <= ey.y)) continue;
-        const uint32_t t = m1.w;  // test id rides in the record's pad word
-        ZoneTestRec z;
-        z.minx = ex.x;
-        z.maxx = ex.y;
-        z.miny = ey.x;
-        z.maxy = ey.y;
-        z.vtx_off = m0.x;
-        z.npts = m0.y;
-        z.flags = m0.z;
-        z.nbins = m0.w;
-        z.inv_bin = __hiloint2double((int)m1.y, (int)m1.x);
-        z.bin_off = m1.z;
-        bool in;
-        if (z.flags & 2u)  // RectangleContains: not on the envelope border
-            in = !(px == z.minx || px == z.maxx || py == z.miny || py == z.maxy);
-        else
-            in = zn_ring_interior(a, z, px, py);
-        if (in) f(t, z.flags & 1u);
+    const ZnD4 *ct = (const ZnD4 *)(a.blob + h.off_cell_start);
+    ZnD4 r = zn_ld256(ct + (cy * h.grid_nx + cx));
+    uint32_t n = 1;
+    const ZnD4 *lp = nullptr;
+    if ((uint32_t)__double2hiint(r.w) & ZC_LIST) {
+        n = (uint32_t)__double2loint(r.w);
+        lp = (const ZnD4 *)(a.blob + h.off_cell_items) + (uint32_t)__double2hiint(r.z);
+        r = zn_ld256(lp);
+    }
+    for (uint32_t k = 0;;) {
+        // conservative (float, rounded outward) envelope: rejects only what Geometry.contains' envelope test rejects
+        const double minx = (double)zn_lo_f(r.x), maxx = (double)zn_hi_f(r.x);
+        const double miny = (double)zn_lo_f(r.y), maxy = (double)zn_hi_f(r.y);
+        if (px >= minx && px <= maxx && py >= miny && py <= maxy) {
+            const uint32_t t = (uint32_t)__double2loint(r.w), info = (uint32_t)__double2hiint(r.w);
+            bool in;
+            if (info & ZC_RECT) {  // RectangleContains: inside the exact envelope and not on its border
+                const ZnD4 ev = zn_ld256((const ZoneTestRec *)(a.blob + h.off_tests) + t);
+                in = px > ev.x && px < ev.y && py > ev.z && py < ev.w;
+            } else {
+                in = zn_ring_interior(a, info, (uint32_t)__double2hiint(r.z), miny, (double)zn_lo_f(r.z), px, py);
+            }
+            if (in) f(t, info & ZC_OUTSIDE);
+        }
+        if (++k >= n) break;
+        r = zn_ld256(lp + k);
     }
 }
 

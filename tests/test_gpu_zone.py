@@ -117,3 +117,59 @@ def test_degenerate_zones(ctx):
     lon = np.concatenate([zlon, rng.uniform(-1, 5, 500), [1.0, 0.5, 3.0]])
     lat = np.concatenate([zlat, rng.uniform(-1, 3, 500), [1.0, 0.5, 0.0]])
     run_both(ctx, (vo, zlon, zlat, cond), lon, lat)
+
+
+def _comb(x0, y0, teeth, tall):
+    """a comb: `teeth` tiny teeth along the bottom (all their edges fall into the lowest y-slab) and one
+    tall spike, so the slabs are very uneven and the table keeps {start,end} ranges for this zone"""
+    xs, ys = [x0], [y0]
+    for k in range(teeth):
+        xs += [x0 + k + 0.5, x0 + k + 1.0]
+        ys += [y0 + 0.01, y0]
+    xs += [x0 + teeth, x0 + teeth / 2.0]
+    ys += [y0 - 1.0, y0 + tall]
+    xs += [x0]
+    ys += [y0 - 1.0]
+    return xs, ys
+
+
+def test_uneven_slabs_use_ranges(ctx):
+    rng = np.random.default_rng(11)
+    vo, zlon, zlat = [0], [], []
+    for j in range(3):
+        xs, ys = _comb(10.0 * j, 5.0 * j, 120, 400.0)
+        zlon += xs; zlat += ys
+        vo.append(len(zlon))
+    star = S.star_zones(3, nvert=32, lon0=0.0, lon1=30.0, lat0=0.0, lat1=30.0, seed=5)
+    zlon += list(star[1]); zlat += list(star[2])
+    vo += [vo[-1] + int(v) for v in star[0][1:]]
+    zones = (np.array(vo, np.uint32), np.array(zlon), np.array(zlat), (np.arange(len(vo) - 1) % 2).astype(np.uint8))
+    lon, lat = adversarial_points(zones[0], zones[1], zones[2], rng, n_extra=6000)
+    run_both(ctx, zones, lon, lat)
+
+
+def test_coordinates_beyond_float_range_and_float_envelope_margin(ctx):
+    """the cell records hold the envelope as outward-rounded floats: zones beyond the float range, and
+    points between the exact and the rounded border, must still match"""
+    rng = np.random.default_rng(12)
+    vo = np.array([0, 4, 8, 12, 15, 20, 23], np.uint32)
+    big = 1e300
+    tiny = 1e-310                           # subnormal: products of differences underflow
+    zlon = np.array([-big, big, big, -big,   0.1, 0.3, 0.3, 0.1,   1e-300, 3e-300, 2e-300, 0.5e-300,   1e39, 2e39, 1.5e39,
+                     -big, big, big, 0.0, -big,   0.0, tiny, 0.0])
+    zlat = np.array([-big, -big, big, big,   0.1, 0.1, 0.7, 0.7,   1e-300, 1e-300, 3e-300, 2e-300,    1e39, 1e39, 3e39,
+                     -big, -big, big, 1.5 * big, big,   0.0, 0.0, tiny])
+    cond = np.array([0, 1, 0, 0, 0, 0], np.uint8)
+    xs = [0.0, 0.1, np.nextafter(0.1, 0), np.nextafter(0.1, 1), 0.3, np.nextafter(0.3, 1), np.nextafter(0.3, 0), 0.2,
+          1.5e-300, 2e-300, 0.0, big, -big, np.nextafter(big, 0), 1.5e39, 1.2e39, 1e39,
+          0.0, big / 2, big / 2, np.nextafter(big / 2, 0), 0.9 * big,
+          5e-324, 5e-324, tiny / 2, tiny / 4, np.nextafter(tiny / 2, 0), tiny / 2, tiny, 0.0]
+    ys = [0.0, 0.1, 0.4, 0.4, 0.7, 0.4, 0.4, np.nextafter(0.7, 0),
+          1.5e-300, 2e-300, 1e-300, big, 0.0, 0.0, 1.5e39, 1.0000001e39, 1e39,
+          1.5 * big, 1.25 * big, 1.2 * big, 1.25 * big, 1.04 * big,
+          5e-324, 0.0, tiny / 2, tiny / 4, tiny / 2, np.nextafter(tiny / 2, 0), 0.0, tiny]
+    lon = np.concatenate([xs, rng.uniform(0.09, 0.31, 2000), rng.uniform(-2, 2, 500) * 1e39,
+                          rng.uniform(-1.1, 1.1, 500) * big, rng.uniform(-0.1, 1.1, 500) * tiny])
+    lat = np.concatenate([ys, rng.uniform(0.09, 0.71, 2000), rng.uniform(-1, 4, 500) * 1e39,
+                          rng.uniform(0.9, 1.6, 500) * big, rng.uniform(-0.1, 1.1, 500) * tiny])
+    run_both(ctx, (vo, zlon, zlat, cond), lon, lat)

@@ -82,6 +82,12 @@ def test_sign_det_exact_random_and_degenerate():
         else:  # tiny / huge magnitudes
             v = [rnd.uniform(-1, 1) * 10.0 ** rnd.randint(-150, 150) for _ in range(4)]
         assert oracle.sign_det2x2(*v) == exact_sign(*v), v
+    for _ in range(4000):  # products that underflow to (sub)zero or overflow in double arithmetic
+        if rnd.random() < 0.5:
+            v = [rnd.choice([5e-324, 1e-310, 3e-200, 0.5, 0.01]) * rnd.choice([1, -1, 3, 0.5]) for _ in range(4)]
+        else:
+            v = [rnd.uniform(-1, 1) * 10.0 ** rnd.choice([-320, -300, -160, 0, 155, 290, 307]) for _ in range(4)]
+        assert oracle.sign_det2x2(*v) == exact_sign(*v), v
     assert oracle.sign_det2x2(0.0, 0.0, 1.0, 1.0) == 0
     assert oracle.sign_det2x2(5e-324, 5e-324, 5e-324, 5e-324) == 0
     assert oracle.sign_det2x2(5e-324, 0.0, 0.0, 5e-324) == 1
