@@ -225,17 +225,25 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
             for (uint32_t bb = 0; bb < nb; bb++) {
                 refs += bins[bb].size();
                 longest = std::max(longest, bins[bb].size());
-                // rightmost edges first: RayCrossingCounter ignores an edge with both ends left of the
-                // point, so the kernel can stop at the first such edge of the slab
-                std::sort(bins[bb].begin(), bins[bb].end(), [&](uint32_t e1, uint32_t e2) {
-                    return std::max(xs[e1], xs[e1 - 1]) > std::max(xs[e2], xs[e2 - 1]);
-                });
             }
-            auto put_edge = [&](uint32_t e) {  // edge record: p1 = ring[e], p2 = ring[e-1], 32 bytes
-                bin_items.push_back(xs[e]);
-                bin_items.push_back(ys[e]);
-                bin_items.push_back(xs[e - 1]);
-                bin_items.push_back(ys[e - 1]);
+            // Every slab is stored twice, once per ray direction (the kernel walks the shorter side):
+            //   side 0  edges as they are, rightmost first.  RayCrossingCounter ignores an edge with both
+            //           ends left of the point, so the walk stops at the first such edge.
+            //   side 1  the mirror image (x negated), again "rightmost" first: the same walk on (-px, py)
+            //           counts the crossings LEFT of the point.  A closed ring crosses the line y = py an
+            //           even number of times, so the parity is the same, and an edge the point lies on is
+            //           met from either side.
+            auto put_slab = [&](std::vector<uint32_t> &v, int side) {
+                const double sg = side ? -1.0 : 1.0;
+                std::sort(v.begin(), v.end(), [&](uint32_t e1, uint32_t e2) {
+                    return std::max(sg * xs[e1], sg * xs[e1 - 1]) > std::max(sg * xs[e2], sg * xs[e2 - 1]);
+                });
+                for (uint32_t e : v) {  // edge record: p1 = ring[e], p2 = ring[e-1], 32 bytes
+                    bin_items.push_back(sg * xs[e]);
+                    bin_items.push_back(ys[e]);
+                    bin_items.push_back(sg * xs[e - 1]);
+                    bin_items.push_back(ys[e - 1]);
+                }
             };
             // Slabs of similar length are stored a fixed stride apart, each ended by a sentinel edge
             // whose ends are at x = -inf ("both ends left of the point": the loop's own exit test), so
@@ -243,26 +251,28 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
             // ranges.
             const size_t stride = longest + 1;
             const bool fixed = stride <= ZC_MAX_STRIDE && (size_t)nb * stride <= 4 * refs + 64 &&
-                               bin_items.size() / 4 + (size_t)nb * stride < 0xffffffffull;
+                               bin_items.size() / 4 + 2 * (size_t)nb * stride < 0xffffffffull;
             if (fixed) {
                 cr.bin_off = z.bin_off = (uint32_t)(bin_items.size() / 4);
-                for (uint32_t bb = 0; bb < nb; bb++) {
-                    for (uint32_t e : bins[bb]) put_edge(e);
-                    for (size_t k = bins[bb].size(); k < stride; k++) {
-                        bin_items.push_back(-INFINITY);
-                        bin_items.push_back(0.0);
-                        bin_items.push_back(-INFINITY);
-                        bin_items.push_back(0.0);
+                for (uint32_t bb = 0; bb < nb; bb++)
+                    for (int side = 0; side < 2; side++) {
+                        put_slab(bins[bb], side);
+                        for (size_t k = bins[bb].size(); k < stride; k++) {
+                            bin_items.push_back(-INFINITY);
+                            bin_items.push_back(0.0);
+                            bin_items.push_back(-INFINITY);
+                            bin_items.push_back(0.0);
+                        }
                     }
-                }
                 cr.info = z.flags | (nb << 8) | ((uint32_t)stride << 20);
             } else {
                 cr.bin_off = z.bin_off = (uint32_t)(bin_ranges.size() / 2);
-                for (uint32_t bb = 0; bb < nb; bb++) {
-                    bin_ranges.push_back((uint32_t)(bin_items.size() / 4));
-                    for (uint32_t e : bins[bb]) put_edge(e);
-                    bin_ranges.push_back((uint32_t)(bin_items.size() / 4));
-                }
+                for (uint32_t bb = 0; bb < nb; bb++)
+                    for (int side = 0; side < 2; side++) {
+                        bin_ranges.push_back((uint32_t)(bin_items.size() / 4));
+                        put_slab(bins[bb], side);
+                        bin_ranges.push_back((uint32_t)(bin_items.size() / 4));
+                    }
                 cr.info = z.flags | ZC_RANGES | (nb << 8);
             }
             if (bin_items.size() / 4 >= 0xffffffffull) {
@@ -534,10 +544,15 @@ __device__ __forceinline__ ZnD4 zn_ld256(const void *p) {
 //   the ends are on different sides of y = py  -> the crossing test; a zero determinant is "on the
 //       segment", which is also what the reference's earlier `p == p2` test reports for such an edge
 //   otherwise p can only touch the edge if p2.y == py (then p1.y <= py): at p2, or on a horizontal edge
+//
+// `side` picks the ray direction (1: the slab's mirrored copy, walked with -px; see put_slab).  Both give
+// the same answer for every point, so the choice is free: the caller takes the side of the envelope the
+// point is nearer to, which is the shorter walk on average.
 __device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, uint32_t info, uint32_t bin_off, double y0, double inv,
-                                                 double px, double py) {
+                                                 uint32_t side, double px, double py) {
     const ZnD4 *er = (const ZnD4 *)(a.blob + a.h.off_bin_items);  // edge records, 32 B each (one sector)
-    const uint32_t b = zn_cell(py, y0, inv, (info >> 8) & 0xfffu);
+    const uint32_t b = 2u * zn_cell(py, y0, inv, (info >> 8) & 0xfffu) + side;
+    if (side) px = -px;
     uint32_t k, k1;
     if (info & ZC_RANGES) {
         const uint2 br = __ldg((const uint2 *)(a.blob + a.h.off_bin_start) + bin_off + b);
@@ -598,7 +613,8 @@ __device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, d
                 const ZnD4 ev = zn_ld256((const ZoneTestRec *)(a.blob + h.off_tests) + t);
                 in = px > ev.x && px < ev.y && py > ev.z && py < ev.w;
             } else {
-                in = zn_ring_interior(a, info, (uint32_t)__double2hiint(r.z), miny, (double)zn_lo_f(r.z), px, py);
+                in = zn_ring_interior(a, info, (uint32_t)__double2hiint(r.z), miny, (double)zn_lo_f(r.z),
+                                      (px - minx < maxx - px) ? 1u : 0u, px, py);
             }
             if (in) f(t, info & ZC_OUTSIDE);
         }
@@ -739,7 +755,7 @@ struct ZnWork {
     uint64_t *tile_base;  // [ntiles]
 };
 
-__global__ void __launch_bounds__(ZN_THREADS) zone_count_kernel(ZnArgs a, ZnWork w) {
+__global__ void __launch_bounds__(ZN_THREADS, 6) zone_count_kernel(ZnArgs a, ZnWork w) {
     __shared__ uint32_t s_part[ZN_THREADS / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
