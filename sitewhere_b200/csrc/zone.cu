@@ -49,13 +49,14 @@ static_assert(sizeof(ZoneTestRec) == 64, "ZoneTestRec layout");
 //   minx..maxy  the zone's envelope rounded OUTWARD to float.  Only ever used to reject: a point
 //               between the rounded and the exact border goes on to the ring test, which gives the
 //               same answer Geometry.contains' envelope short-circuit would (outside).
-//   miny, inv_bin  also the y-slab function: slab = zn_cell(py, (double)miny, (double)inv_bin, nbins).
-//               Any origin/scale works as long as registration and lookup use the same one.
+//   miny, minx, inv16  also the slab functions: y-slab = zn_cell(py, (double)miny, scale_y, nbins) and
+//               x-slab = zn_cell(px, (double)minx, scale_x, nbins).  Any origin/scale works as long as
+//               registration and lookup use the same one, so 16 bits of scale are plenty.
 //   bin_off     first edge record of slab 0 (slabs `stride` records apart, each list ended by a
-//               sentinel edge at x = -inf), or with ZC_RANGES the first {start,end} slab range.
+//               sentinel edge at -inf), or with ZC_RANGES the first {start,end} slab range.
 struct ZnCellRec {
     float minx, maxx, miny, maxy;
-    float inv_bin;
+    uint32_t inv16;  // slab scales as the top 16 bits of a float: low half for y-slabs, high half for x-slabs
     uint32_t bin_off;
     uint32_t t;
     uint32_t info;  // bits 0..7 flags, 8..19 slab count, 20..31 slab stride
@@ -107,6 +108,21 @@ static float f_down(double v) {
     float f = (float)v;
     if ((double)f > v) f = nextafterf(f, -INFINITY);
     return f;
+}
+// slab scale kept as the top 16 bits of its float value (sign, exponent, 7 mantissa bits)
+static uint32_t inv_bits16(double invd) {
+    if (!(invd > 0) || !std::isfinite(invd)) return 0;
+    float f = (float)invd;
+    if (!std::isfinite(f)) return 0;
+    uint32_t b;
+    memcpy(&b, &f, 4);
+    return b >> 16;
+}
+static double inv_from16(uint32_t b16) {
+    uint32_t b = b16 << 16;
+    float f;
+    memcpy(&f, &b, 4);
+    return (double)f;
 }
 static float f_up(double v) {
     float f = (float)v;
@@ -194,85 +210,91 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
         cr.miny = f_down(miny);
         cr.maxy = f_up(maxy);
         cr.t = t;
-        // y-slabs over edges i = 1..npts-1 (edge i joins ring[i] and ring[i-1])
+        // slabs over edges i = 1..npts-1 (edge i joins ring[i] and ring[i-1])
         if (rect) {
             z.nbins = 0;
             z.inv_bin = 0;
             cr.info = z.flags;
         } else {
-            uint32_t nb = std::max(1u, std::min(64u, (z.npts - 1 + 3) / 4));
-            const double y0 = (double)cr.miny;  // slab origin: at or below every vertex
-            const double h = maxy - y0;
-            float invf = 0.f;
-            if (h > 0 && std::isfinite(h)) {
-                double invd = (double)nb / h;
-                invf = (float)invd;
-                if ((double)invf > invd) invf = nextafterf(invf, 0.f);
-                if (!std::isfinite(invf) || !(invf > 0.f)) invf = 0.f;
-            }
-            if (invf == 0.f) nb = 1;
-            const double inv = (double)invf;
-            z.nbins = nb;
-            z.inv_bin = inv;
-            cr.inv_bin = invf;
-            std::vector<std::vector<uint32_t>> bins(nb);
+            // The ring is stored four times, once per axis-parallel ray direction; the kernel walks the
+            // copy whose ray leaves the envelope soonest, which is the shortest walk on average:
+            //   +x  edges as they are, cut into y-slabs, rightmost first.  RayCrossingCounter ignores an
+            //       edge with both ends left of the point, so the walk stops at the first such edge.
+            //   -x  the mirror image (x negated), again "rightmost" first: the same walk on (-px, py)
+            //       counts the crossings LEFT of the point.
+            //   +y, -y  the same two with the axes exchanged (x-slabs; the walk sees (py, px), (-py, px)).
+            // A closed ring crosses any line an even number of times (with the walk's half-open rule for
+            // vertices on the line), so all four parities agree, and an edge the point lies on is in the
+            // point's slab and is met before the walk stops, whichever way it goes.
+            const uint32_t nb = std::max(1u, std::min(64u, (z.npts - 1 + 3) / 4));
+            const double *uc[2] = {xs.data(), ys.data()};  // axis 0: ray along x, slabs along y
+            const double v0[2] = {(double)cr.miny, (double)cr.minx};  // slab origins: at or below every vertex
+            const double vmax[2] = {maxy, maxx};
+            uint32_t inv16[2];
+            double inv[2];
+            std::vector<std::vector<uint32_t>> bins[2];
             size_t refs = 0, longest = 0;
-            for (uint32_t i = 1; i < z.npts; i++) {
-                double y1 = ys[i], y2 = ys[i - 1];
-                uint32_t lo = zn_cell(std::min(y1, y2), y0, inv, nb), hi = zn_cell(std::max(y1, y2), y0, inv, nb);
-                for (uint32_t bb = lo; bb <= hi; bb++) bins[bb].push_back(i);
+            for (int ax = 0; ax < 2; ax++) {
+                inv16[ax] = inv_bits16((double)nb / (vmax[ax] - v0[ax]));
+                inv[ax] = inv_from16(inv16[ax]);
+                const double *vc = uc[1 - ax];
+                bins[ax].assign(nb, std::vector<uint32_t>());
+                for (uint32_t i = 1; i < z.npts; i++) {
+                    double a1 = vc[i], a2 = vc[i - 1];
+                    uint32_t lo = zn_cell(std::min(a1, a2), v0[ax], inv[ax], nb), hi = zn_cell(std::max(a1, a2), v0[ax], inv[ax], nb);
+                    for (uint32_t bb = lo; bb <= hi; bb++) bins[ax][bb].push_back(i);
+                }
+                for (uint32_t bb = 0; bb < nb; bb++) {
+                    refs += bins[ax][bb].size();
+                    longest = std::max(longest, bins[ax][bb].size());
+                }
             }
-            for (uint32_t bb = 0; bb < nb; bb++) {
-                refs += bins[bb].size();
-                longest = std::max(longest, bins[bb].size());
-            }
-            // Every slab is stored twice, once per ray direction (the kernel walks the shorter side):
-            //   side 0  edges as they are, rightmost first.  RayCrossingCounter ignores an edge with both
-            //           ends left of the point, so the walk stops at the first such edge.
-            //   side 1  the mirror image (x negated), again "rightmost" first: the same walk on (-px, py)
-            //           counts the crossings LEFT of the point.  A closed ring crosses the line y = py an
-            //           even number of times, so the parity is the same, and an edge the point lies on is
-            //           met from either side.
-            auto put_slab = [&](std::vector<uint32_t> &v, int side) {
+            z.nbins = nb;
+            z.inv_bin = inv[0];
+            cr.inv16 = inv16[0] | (inv16[1] << 16);
+            auto put_slab = [&](std::vector<uint32_t> &v, int ax, int side) {
                 const double sg = side ? -1.0 : 1.0;
+                const double *u = uc[ax], *vc = uc[1 - ax];
                 std::sort(v.begin(), v.end(), [&](uint32_t e1, uint32_t e2) {
-                    return std::max(sg * xs[e1], sg * xs[e1 - 1]) > std::max(sg * xs[e2], sg * xs[e2 - 1]);
+                    return std::max(sg * u[e1], sg * u[e1 - 1]) > std::max(sg * u[e2], sg * u[e2 - 1]);
                 });
                 for (uint32_t e : v) {  // edge record: p1 = ring[e], p2 = ring[e-1], 32 bytes
-                    bin_items.push_back(sg * xs[e]);
-                    bin_items.push_back(ys[e]);
-                    bin_items.push_back(sg * xs[e - 1]);
-                    bin_items.push_back(ys[e - 1]);
+                    bin_items.push_back(sg * u[e]);
+                    bin_items.push_back(vc[e]);
+                    bin_items.push_back(sg * u[e - 1]);
+                    bin_items.push_back(vc[e - 1]);
                 }
             };
             // Slabs of similar length are stored a fixed stride apart, each ended by a sentinel edge
-            // whose ends are at x = -inf ("both ends left of the point": the loop's own exit test), so
-            // the kernel needs no slab range.  Very uneven slabs would waste the padding: they keep
-            // ranges.
+            // whose ends are at -inf ("both ends behind the point": the loop's own exit test), so the
+            // kernel needs no slab range.  Very uneven slabs would waste the padding: they keep ranges.
+            // Slab (ax, bb, side) is number (ax * nb + bb) * 2 + side.
             const size_t stride = longest + 1;
-            const bool fixed = stride <= ZC_MAX_STRIDE && (size_t)nb * stride <= 4 * refs + 64 &&
-                               bin_items.size() / 4 + 2 * (size_t)nb * stride < 0xffffffffull;
+            const bool fixed = stride <= ZC_MAX_STRIDE && 2 * (size_t)nb * stride <= 4 * refs + 64 &&
+                               bin_items.size() / 4 + 4 * (size_t)nb * stride < 0xffffffffull;
             if (fixed) {
                 cr.bin_off = z.bin_off = (uint32_t)(bin_items.size() / 4);
-                for (uint32_t bb = 0; bb < nb; bb++)
-                    for (int side = 0; side < 2; side++) {
-                        put_slab(bins[bb], side);
-                        for (size_t k = bins[bb].size(); k < stride; k++) {
-                            bin_items.push_back(-INFINITY);
-                            bin_items.push_back(0.0);
-                            bin_items.push_back(-INFINITY);
-                            bin_items.push_back(0.0);
+                for (int ax = 0; ax < 2; ax++)
+                    for (uint32_t bb = 0; bb < nb; bb++)
+                        for (int side = 0; side < 2; side++) {
+                            put_slab(bins[ax][bb], ax, side);
+                            for (size_t k = bins[ax][bb].size(); k < stride; k++) {
+                                bin_items.push_back(-INFINITY);
+                                bin_items.push_back(0.0);
+                                bin_items.push_back(-INFINITY);
+                                bin_items.push_back(0.0);
+                            }
                         }
-                    }
                 cr.info = z.flags | (nb << 8) | ((uint32_t)stride << 20);
             } else {
                 cr.bin_off = z.bin_off = (uint32_t)(bin_ranges.size() / 2);
-                for (uint32_t bb = 0; bb < nb; bb++)
-                    for (int side = 0; side < 2; side++) {
-                        bin_ranges.push_back((uint32_t)(bin_items.size() / 4));
-                        put_slab(bins[bb], side);
-                        bin_ranges.push_back((uint32_t)(bin_items.size() / 4));
-                    }
+                for (int ax = 0; ax < 2; ax++)
+                    for (uint32_t bb = 0; bb < nb; bb++)
+                        for (int side = 0; side < 2; side++) {
+                            bin_ranges.push_back((uint32_t)(bin_items.size() / 4));
+                            put_slab(bins[ax][bb], ax, side);
+                            bin_ranges.push_back((uint32_t)(bin_items.size() / 4));
+                        }
                 cr.info = z.flags | ZC_RANGES | (nb << 8);
             }
             if (bin_items.size() / 4 >= 0xffffffffull) {
@@ -545,21 +567,19 @@ __device__ __forceinline__ ZnD4 zn_ld256(const void *p) {
 //       segment", which is also what the reference's earlier `p == p2` test reports for such an edge
 //   otherwise p can only touch the edge if p2.y == py (then p1.y <= py): at p2, or on a horizontal edge
 //
-// `side` picks the ray direction (1: the slab's mirrored copy, walked with -px; see put_slab).  Both give
-// the same answer for every point, so the choice is free: the caller takes the side of the envelope the
-// point is nearer to, which is the shorter walk on average.
-__device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, uint32_t info, uint32_t bin_off, double y0, double inv,
-                                                 uint32_t side, double px, double py) {
+// The walk runs in the frame of the chosen copy of the ring (see the table builder): `u` is the
+// coordinate along the ray (x, -x, y or -y), `v` the one across it, `slab` the copy's slab number.
+// All four copies give the same answer for every point, so the choice is free.
+__device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, uint32_t info, uint32_t bin_off, uint32_t slab,
+                                                 double px, double py) {
     const ZnD4 *er = (const ZnD4 *)(a.blob + a.h.off_bin_items);  // edge records, 32 B each (one sector)
-    const uint32_t b = 2u * zn_cell(py, y0, inv, (info >> 8) & 0xfffu) + side;
-    if (side) px = -px;
     uint32_t k, k1;
     if (info & ZC_RANGES) {
-        const uint2 br = __ldg((const uint2 *)(a.blob + a.h.off_bin_start) + bin_off + b);
+        const uint2 br = __ldg((const uint2 *)(a.blob + a.h.off_bin_start) + bin_off + slab);
         k = br.x;
         k1 = br.y;
     } else {  // fixed stride; the slab's sentinel ends the loop
-        k = bin_off + b * (info >> 20);
+        k = bin_off + slab * (info >> 20);
         k1 = 0xffffffffu;
     }
     uint32_t crossings = 0;
@@ -613,8 +633,16 @@ __device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, d
                 const ZnD4 ev = zn_ld256((const ZoneTestRec *)(a.blob + h.off_tests) + t);
                 in = px > ev.x && px < ev.y && py > ev.z && py < ev.w;
             } else {
-                in = zn_ring_interior(a, info, (uint32_t)__double2hiint(r.z), miny, (double)zn_lo_f(r.z),
-                                      (px - minx < maxx - px) ? 1u : 0u, px, py);
+                // the ray that leaves the envelope soonest, in slab units (both axes have nb slabs)
+                const uint32_t nb = (info >> 8) & 0xfffu, i16 = (uint32_t)__double2loint(r.z);
+                const double sy = (double)__int_as_float(i16 << 16), sx = (double)__int_as_float(i16 & 0xffff0000u);
+                const double dl = (px - minx) * sx, dr = (maxx - px) * sx, db = (py - miny) * sy, dt = (maxy - py) * sy;
+                const bool alongy = fmin(db, dt) < fmin(dl, dr);
+                const bool neg = alongy ? db < dt : dl < dr;
+                // ray along x: slabs by y (copies 0 .. 2nb-1); along y: slabs by x (copies 2nb .. 4nb-1)
+                const uint32_t sl = alongy ? nb + zn_cell(px, minx, sx, nb) : zn_cell(py, miny, sy, nb);
+                const double u = alongy ? py : px, v = alongy ? px : py;
+                in = zn_ring_interior(a, info, (uint32_t)__double2hiint(r.z), 2u * sl + (neg ? 1u : 0u), neg ? -u : u, v);
             }
             if (in) f(t, info & ZC_OUTSIDE);
         }
@@ -755,7 +783,7 @@ struct ZnWork {
     uint64_t *tile_base;  // [ntiles]
 };
 
-__global__ void __launch_bounds__(ZN_THREADS, 6) zone_count_kernel(ZnArgs a, ZnWork w) {
+__global__ void __launch_bounds__(ZN_THREADS, 5) zone_count_kernel(ZnArgs a, ZnWork w) {
     __shared__ uint32_t s_part[ZN_THREADS / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
