@@ -93,6 +93,7 @@ extern "C" int32_t swgpu_create(int32_t device_ordinal, void *stream, swgpu_ctx 
     }
     swgpu_ctx *ctx = new swgpu_ctx();
     ctx->device = device_ordinal;
+    ctx->sm_count = prop.multiProcessorCount > 0 ? prop.multiProcessorCount : 148;
     if (stream) {
         ctx->stream = (cudaStream_t)stream;
     } else {

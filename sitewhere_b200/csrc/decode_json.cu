@@ -910,23 +910,11 @@ __device__ void json_decode_record(B bytes, uint32_t n, uint32_t rec, JsRow &r) 
     r.status = SWGPU_ST_OK;
 }
 
+// one tile = JS_THREADS records, one per thread.  As in the protobuf decoder: each warp stages and decodes
+// its own 32 records (no block barrier for staging).
 template <bool DENSE>
-__global__ void __launch_bounds__(JS_THREADS) json_decode_kernel(JsArgs a) {
-    // as in the protobuf decoder: the CTA owns a tile of JS_THREADS records in the ordered scan; each warp
-    // stages and decodes its own 32 records (no block barrier for staging)
-    // DENSE = true: optimistic pass, row index = record index, no inter-tile dependency; raises *not_dense
-    // when some record does not decode to exactly one row.  DENSE = false: ordered redo, returns at once
-    // unless *not_dense was raised.  (Same scheme as pb_decode_kernel.)
-    extern __shared__ __align__(16) uint8_t smem[];  // JS_WARPS * (JS_WSTAGE + 32)
-    __shared__ uint64_t s_warp[JS_THREADS / 32 + 2];
-    __shared__ uint32_t s_tile;
+__device__ __forceinline__ void json_decode_tile(const JsArgs &a, const uint32_t tile, uint8_t *smem, uint64_t *s_warp) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (!DENSE) {
-        if (__ldg(a.not_dense) == 0) return;
-        if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
-        __syncthreads();
-    }
-    const uint32_t tile = DENSE ? blockIdx.x : s_tile;
     const uint64_t rec0_64 = (uint64_t)tile * JS_THREADS + warp * 32;
     const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
     const uint32_t nrec = min(32u, a.n - rec0);
@@ -997,6 +985,31 @@ __global__ void __launch_bounds__(JS_THREADS) json_decode_kernel(JsArgs a) {
     }
 }
 
+// DENSE = true: optimistic pass, row index = record index, no inter-tile dependency; raises *not_dense
+// when some record does not decode to exactly one row.  DENSE = false: ordered redo (ticketed tiles and
+// look-back, a few CTAs per SM taking tiles in turn), which returns at once unless *not_dense was raised.
+// (Same scheme as pb_decode_kernel.)
+template <bool DENSE>
+__global__ void __launch_bounds__(JS_THREADS) json_decode_kernel(JsArgs a) {
+    extern __shared__ __align__(16) uint8_t smem[];  // JS_WARPS * (JS_WSTAGE + 32)
+    __shared__ uint64_t s_warp[JS_THREADS / 32 + 2];
+    __shared__ uint32_t s_tile;
+    if (DENSE) {
+        json_decode_tile<true>(a, blockIdx.x, smem, s_warp);
+        return;
+    }
+    if (__ldg(a.not_dense) == 0) return;
+    const uint32_t ntiles = (uint32_t)(((uint64_t)a.n + JS_THREADS - 1) / JS_THREADS);
+    for (;;) {
+        if (threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u);
+        __syncthreads();
+        const uint32_t tile = s_tile;
+        if (tile >= ntiles) return;
+        json_decode_tile<false>(a, tile, smem, s_warp);
+        __syncthreads();  // s_tile, s_warp and the staging buffers are reused
+    }
+}
+
 int sw_stage_decode(swgpu_ctx *ctx, bool json, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
                     uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row,
                     uint32_t *out_rows);
@@ -1044,7 +1057,8 @@ int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *
     SW_CUDA(ctx, cudaFuncSetAttribute(json_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     json_decode_kernel<true><<<ntiles, JS_THREADS, smem, ctx->stream>>>(a);   // optimistic: rows = records
     SW_CUDA(ctx, cudaGetLastError());
-    json_decode_kernel<false><<<ntiles, JS_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
+    const uint32_t nredo = ntiles < (uint32_t)ctx->sm_count * 4u ? ntiles : (uint32_t)ctx->sm_count * 4u;
+    json_decode_kernel<false><<<nredo, JS_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
 }

@@ -8,6 +8,8 @@
 // semantics), and rows are written to the SoA columns at positions given by a single-pass ordered
 // scan (decoupled look-back), so output order is the reference's order with no second pass over
 // the payload.  HBM traffic = payload once + offsets + columns: the kernel is HBM-bound.
+#include <algorithm>
+
 #include "swgpu_common.cuh"
 
 #define PB_THREADS 256
@@ -507,18 +509,10 @@ __device__ __forceinline__ void pb_write_rows(const PbArgs &a, B bytes, const Pb
 //                  *not_dense was raised; then it redoes the batch with exact ordered placement.  In that
 //                  pass every tile waits for the slowest of the few hundred tiles in flight, which is why
 //                  it is ~2.5x slower than the dense pass (measured; DESIGN.md "ordered placement").
+// one tile = PB_THREADS records, one per thread
 template <bool DENSE>
-__global__ void __launch_bounds__(PB_THREADS) pb_decode_kernel(PbArgs a) {
-    extern __shared__ __align__(16) uint8_t smem[];  // PB_WARPS * (PB_WSTAGE + 32)
-    __shared__ uint64_t s_warp[PB_THREADS / 32 + 2];
-    __shared__ uint32_t s_tile;
+__device__ __forceinline__ void pb_decode_tile(const PbArgs &a, const uint32_t tile, uint8_t *smem, uint64_t *s_warp) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (!DENSE) {
-        if (__ldg(a.not_dense) == 0) return;  // the dense pass was exact: nothing to redo
-        if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
-        __syncthreads();
-    }
-    const uint32_t tile = DENSE ? blockIdx.x : s_tile;  // ordered pass: tickets are handed out in start order
     const uint64_t rec0_64 = (uint64_t)tile * PB_THREADS + warp * 32;
     const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
     const uint32_t nrec = min(32u, a.n - rec0);  // 0 for the padding warps of the last CTA
@@ -579,6 +573,30 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_kernel(PbArgs a) {
     }
 }
 
+// DENSE: one CTA per tile.  Ordered pass: a few CTAs per SM take tiles by ticket (tickets are handed out
+// in start order, which is what the look-back needs), so when the dense pass was exact — the usual
+// case — the launch costs a few hundred CTAs that read one flag, not one CTA per tile.
+template <bool DENSE>
+__global__ void __launch_bounds__(PB_THREADS) pb_decode_kernel(PbArgs a) {
+    extern __shared__ __align__(16) uint8_t smem[];  // PB_WARPS * (PB_WSTAGE + 32)
+    __shared__ uint64_t s_warp[PB_THREADS / 32 + 2];
+    __shared__ uint32_t s_tile;
+    if (DENSE) {
+        pb_decode_tile<true>(a, blockIdx.x, smem, s_warp);
+        return;
+    }
+    if (__ldg(a.not_dense) == 0) return;  // the dense pass was exact: nothing to redo
+    const uint32_t ntiles = (uint32_t)(((uint64_t)a.n + PB_THREADS - 1) / PB_THREADS);
+    for (;;) {
+        if (threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u);
+        __syncthreads();
+        const uint32_t tile = s_tile;
+        if (tile >= ntiles) return;
+        pb_decode_tile<false>(a, tile, smem, s_warp);
+        __syncthreads();  // s_tile, s_warp and the staging buffers are reused
+    }
+}
+
 static int check_cols(swgpu_ctx *ctx, const swgpu_decoded_cols *c) {
     if (!c || !c->meta || !c->token_hash || !c->name_hash || !c->event_date || !c->v0 || !c->v1 || !c->v2 ||
         !c->token_span || !c->name_span) {
@@ -627,7 +645,8 @@ int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
     SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     pb_decode_kernel<true><<<ntiles, PB_THREADS, smem, ctx->stream>>>(a);   // optimistic: rows = records
     SW_CUDA(ctx, cudaGetLastError());
-    pb_decode_kernel<false><<<ntiles, PB_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
+    const uint32_t nredo = std::min<uint32_t>(ntiles, (uint32_t)ctx->sm_count * 4u);
+    pb_decode_kernel<false><<<nredo, PB_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
 }

@@ -19,6 +19,7 @@ struct ZoneTableHost;  // zone.cu
 
 struct swgpu_ctx {
     int device = -1;
+    int sm_count = 148;  // multiprocessors of the device (grid sizing of the ticketed kernels)
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     std::string err;

@@ -770,15 +770,14 @@ __global__ void __launch_bounds__(ZN_THREADS) zone_test_kernel(ZnArgs a) {
 }
 
 // ---- three-launch form: count -> scan of tile totals -> emit.  No tile ever waits for another one.
-//   zone_count_kernel  evaluates every location once; parks its alert count (4 B) and, in the common
-//                      case (no Outside-condition tests, at most two alerts), the test ids (8 B); writes
-//                      the tile's total.
+//   zone_count_kernel  evaluates every location once and parks one 8-byte word for it: in the common
+//                      case (no Outside-condition tests, at most two alerts) the count and the test ids,
+//                      otherwise just the count; writes the tile's total.
 //   zone_scan_kernel   one CTA: exclusive scan of the tile totals (a few tens of thousands of words).
 //   zone_emit_kernel   places each location's pairs at tile base + its offset inside the tile; locations
 //                      whose ids were not parked (rare) are evaluated again.
 struct ZnWork {
-    uint32_t *cnt;        // [n]
-    uint64_t *inl;        // [n] two parked test ids
+    uint64_t *park;       // [n] bits 0..1: alerts (3 = "see bits 2.."), then either two 31-bit test ids or the count
     uint64_t *tile_tot;   // [ntiles]
     uint64_t *tile_base;  // [ntiles]
 };
@@ -791,10 +790,11 @@ __global__ void __launch_bounds__(ZN_THREADS, 5) zone_count_kernel(ZnArgs a, ZnW
     ZnLoc L;
     zn_eval(a, i, n_live, L);
     if (i < a.n) {
-        w.cnt[i] = L.count;
-        if (a.h.n_outside == 0 && L.count <= 2) {
+        if (a.h.n_outside == 0 && L.count <= 2) {  // test ids are below 2^31 (one vertex each at least)
             const uint64_t id0 = L.n_in > 0 ? (L.ins[0] >> 1) : 0u, id1 = L.n_in > 1 ? (L.ins[1] >> 1) : 0u;
-            w.inl[i] = id0 | (id1 << 32);
+            w.park[i] = (uint64_t)L.count | (id0 << 2) | (id1 << 33);
+        } else {
+            w.park[i] = 3u | ((uint64_t)L.count << 2);
         }
     }
     uint32_t s = L.count;
@@ -862,7 +862,8 @@ __global__ void __launch_bounds__(ZN_THREADS) zone_emit_kernel(ZnArgs a, ZnWork 
     __shared__ uint32_t s_part[ZN_THREADS / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t i = blockIdx.x * ZN_THREADS + tid;
-    const uint32_t count = i < a.n ? w.cnt[i] : 0;
+    const uint64_t parked = i < a.n ? w.park[i] : 0;
+    const uint32_t count = (parked & 3u) == 3u ? (uint32_t)(parked >> 2) : (uint32_t)(parked & 3u);
     uint32_t inc = count;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -879,9 +880,8 @@ __global__ void __launch_bounds__(ZN_THREADS) zone_emit_kernel(ZnArgs a, ZnWork 
     uint64_t pos = w.tile_base[blockIdx.x] + woff + (inc - count);
     if (a.h.n_outside == 0 && count <= 2) {
         const uint64_t ev = (uint64_t)((a.row_base ? __ldg(a.row_base) : 0u) + i) << 32;
-        const uint64_t ids = w.inl[i];
-        if (pos < a.max_pairs) a.pairs[pos] = ev | (ids & 0xffffffffu);
-        if (count == 2 && pos + 1 < a.max_pairs) a.pairs[pos + 1] = ev | (ids >> 32);
+        if (pos < a.max_pairs) a.pairs[pos] = ev | ((parked >> 2) & 0x7fffffffu);
+        if (count == 2 && pos + 1 < a.max_pairs) a.pairs[pos + 1] = ev | (parked >> 33);
     } else {
         const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
         ZnLoc L;
@@ -908,15 +908,13 @@ int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const u
         return SWGPU_OK;
     }
     const uint32_t ntiles = (n + ZN_THREADS - 1) / ZN_THREADS;
-    // work area: parked counts (4 B) and ids (8 B) per location, totals and bases (8 B each) per tile
-    const size_t off_inl = ((size_t)n * 4 + 255) / 256 * 256;
-    const size_t off_tot = off_inl + (size_t)n * 8;
+    // work area: one parked word (8 B) per location, totals and bases (8 B each) per tile
+    const size_t off_tot = ((size_t)n * 8 + 255) / 256 * 256;
     const size_t off_base = off_tot + (size_t)ntiles * 8;
     const size_t work_bytes = off_base + (size_t)ntiles * 8;
     if (int rc = sw_ensure(ctx, ctx->d_zwork, work_bytes)) return rc;
     ZnWork w;
-    w.cnt = (uint32_t *)ctx->d_zwork.p;
-    w.inl = (uint64_t *)((uint8_t *)ctx->d_zwork.p + off_inl);
+    w.park = (uint64_t *)ctx->d_zwork.p;
     w.tile_tot = (uint64_t *)((uint8_t *)ctx->d_zwork.p + off_tot);
     w.tile_base = (uint64_t *)((uint8_t *)ctx->d_zwork.p + off_base);
     ZnArgs a;
