@@ -858,13 +858,76 @@ __global__ void __launch_bounds__(ZS_THREADS) zone_scan_kernel(const uint64_t *t
     if (tid == 0) *total_out = s_carry;
 }
 
+// Exclusive scan of the tile totals on several CTAs without any wait between them: CTA j scans its own
+// ZS_THREADS totals and simply re-adds all the totals before its range (j coalesced loads per thread, all
+// L2 hits).  Quadratic in the number of CTAs, so sw_zone_launch uses it up to ZS_MC_MAX_TILES tiles
+// (67 M locations) and the sequential kernel above beyond that.
+#define ZS_MC_MAX_TILES 262144u
+__global__ void __launch_bounds__(ZS_THREADS) zone_scan_mc_kernel(const uint64_t *tot, uint64_t *base, uint32_t ntiles,
+                                                                  uint64_t *total_out) {
+    __shared__ uint64_t s_warp[ZS_THREADS / 32], s_acc[ZS_THREADS / 32];
+    __shared__ uint64_t s_pre;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t start = blockIdx.x * ZS_THREADS;
+    uint64_t acc = 0;
+#pragma unroll 8
+    for (uint32_t i = tid; i < start; i += ZS_THREADS) acc += tot[i];
+    const uint32_t i = start + tid;
+    const uint64_t v = i < ntiles ? tot[i] : 0;
+    uint64_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint64_t t = __shfl_up_sync(SW_FULL, inc, o);
+        if (lane >= (uint32_t)o) inc += t;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(SW_FULL, acc, o);
+    if (lane == 31) s_warp[warp] = inc;
+    if (lane == 0) s_acc[warp] = acc;
+    __syncthreads();
+    if (warp == 0) {
+        uint64_t wv = s_warp[lane], winc = wv, av = s_acc[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint64_t t = __shfl_up_sync(SW_FULL, winc, o);
+            if (lane >= (uint32_t)o) winc += t;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) av += __shfl_xor_sync(SW_FULL, av, o);
+        s_warp[lane] = winc - wv;  // exclusive warp offsets
+        if (lane == 0) s_pre = av;
+    }
+    __syncthreads();
+    const uint64_t excl = s_pre + s_warp[warp] + (inc - v);
+    if (i < ntiles) base[i] = excl;
+    if (i == ntiles - 1) *total_out = excl + v;
+}
+
+// Each thread places the pairs of ZE_PER consecutive locations (one 256-bit load of their parked words);
+// a CTA covers ZE_PER tiles, two warps per tile.
+#define ZE_PER 4
 __global__ void __launch_bounds__(ZN_THREADS) zone_emit_kernel(ZnArgs a, ZnWork w) {
     __shared__ uint32_t s_part[ZN_THREADS / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t i = blockIdx.x * ZN_THREADS + tid;
-    const uint64_t parked = i < a.n ? w.park[i] : 0;
-    const uint32_t count = (parked & 3u) == 3u ? (uint32_t)(parked >> 2) : (uint32_t)(parked & 3u);
-    uint32_t inc = count;
+    const uint64_t i0 = ((uint64_t)blockIdx.x * ZN_THREADS + tid) * ZE_PER;
+    uint64_t parked[ZE_PER];
+    if (i0 + ZE_PER <= a.n) {
+        const ZnD4 v = zn_ld256(w.park + i0);
+        parked[0] = (uint64_t)__double_as_longlong(v.x);
+        parked[1] = (uint64_t)__double_as_longlong(v.y);
+        parked[2] = (uint64_t)__double_as_longlong(v.z);
+        parked[3] = (uint64_t)__double_as_longlong(v.w);
+    } else {
+#pragma unroll
+        for (int j = 0; j < ZE_PER; j++) parked[j] = i0 + j < a.n ? w.park[i0 + j] : 0;
+    }
+    uint32_t count[ZE_PER], tsum = 0;
+#pragma unroll
+    for (int j = 0; j < ZE_PER; j++) {
+        count[j] = (parked[j] & 3u) == 3u ? (uint32_t)(parked[j] >> 2) : (uint32_t)(parked[j] & 3u);
+        tsum += count[j];
+    }
+    uint32_t inc = tsum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         uint32_t t = __shfl_up_sync(SW_FULL, inc, o);
@@ -872,21 +935,26 @@ __global__ void __launch_bounds__(ZN_THREADS) zone_emit_kernel(ZnArgs a, ZnWork 
     }
     if (lane == 31) s_part[warp] = inc;
     __syncthreads();
-    uint32_t woff = 0;
+    if (!tsum) return;
+    // a tile is ZN_THREADS locations = 2 warps of this kernel: the odd warp continues after the even one
+    const uint32_t woff = (warp & 1u) ? s_part[warp - 1] : 0u;
+    uint64_t pos = w.tile_base[(uint64_t)blockIdx.x * ZE_PER + (warp >> 1)] + woff + (inc - tsum);
+    const uint32_t row_base = a.row_base ? __ldg(a.row_base) : 0u;
 #pragma unroll
-    for (int k = 0; k < ZN_THREADS / 32; k++)
-        if (k < (int)warp) woff += s_part[k];
-    if (!count) return;
-    uint64_t pos = w.tile_base[blockIdx.x] + woff + (inc - count);
-    if (a.h.n_outside == 0 && count <= 2) {
-        const uint64_t ev = (uint64_t)((a.row_base ? __ldg(a.row_base) : 0u) + i) << 32;
-        if (pos < a.max_pairs) a.pairs[pos] = ev | ((parked >> 2) & 0x7fffffffu);
-        if (count == 2 && pos + 1 < a.max_pairs) a.pairs[pos + 1] = ev | (parked >> 33);
-    } else {
-        const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
-        ZnLoc L;
-        zn_eval(a, i, n_live, L);
-        zn_emit(a, i, L, pos);
+    for (int j = 0; j < ZE_PER; j++) {
+        if (!count[j]) continue;
+        const uint32_t i = (uint32_t)i0 + j;
+        if (a.h.n_outside == 0 && count[j] <= 2) {
+            const uint64_t ev = (uint64_t)(row_base + i) << 32;
+            if (pos < a.max_pairs) a.pairs[pos] = ev | ((parked[j] >> 2) & 0x7fffffffu);
+            if (count[j] == 2 && pos + 1 < a.max_pairs) a.pairs[pos + 1] = ev | (parked[j] >> 33);
+        } else {
+            const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
+            ZnLoc L;
+            zn_eval(a, i, n_live, L);
+            zn_emit(a, i, L, pos);
+        }
+        pos += count[j];
     }
 }
 
@@ -933,9 +1001,15 @@ int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const u
     a.row_base = row_base;
     zone_count_kernel<<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a, w);
     SW_CUDA(ctx, cudaGetLastError());
-    zone_scan_kernel<<<1, ZS_THREADS, 0, ctx->stream>>>(w.tile_tot, w.tile_base, ntiles, n_pairs_dev);
+    // (SWGPU_ZONE_SCAN=seq forces the sequential kernel: lets the tests cover it without a 67 M batch)
+    const char *scan_env = getenv("SWGPU_ZONE_SCAN");
+    if (ntiles <= ZS_MC_MAX_TILES && !(scan_env && scan_env[0] == 's'))
+        zone_scan_mc_kernel<<<(ntiles + ZS_THREADS - 1) / ZS_THREADS, ZS_THREADS, 0, ctx->stream>>>(w.tile_tot, w.tile_base,
+                                                                                                  ntiles, n_pairs_dev);
+    else
+        zone_scan_kernel<<<1, ZS_THREADS, 0, ctx->stream>>>(w.tile_tot, w.tile_base, ntiles, n_pairs_dev);
     SW_CUDA(ctx, cudaGetLastError());
-    zone_emit_kernel<<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a, w);
+    zone_emit_kernel<<<(ntiles + ZE_PER - 1) / ZE_PER, ZN_THREADS, 0, ctx->stream>>>(a, w);
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
 }

@@ -1,6 +1,5 @@
-"""Large batches take the cell-ordered evaluation path of the zone test (counting sort by coarse grid cell,
-evaluation in cell order, results scattered back to arrival order).  Same parity bar as the small-batch
-path: identical, identically ordered alert pairs."""
+"""Larger zone-test batches (many tiles: the count -> scan -> emit split across CTAs, ragged last tile,
+both scan kernels).  Same parity bar as the small batches: identical, identically ordered alert pairs."""
 import numpy as np
 import pytest
 
@@ -58,3 +57,14 @@ def test_sorted_path_rectangles_and_single_cell_grid(ctx):
     one = (np.array([0, 4], np.uint32), np.array([0.0, 1.0, 1.0, 0.2]), np.array([0.0, 0.0, 1.0, 0.9]), np.array([1], np.uint8))
     rng = np.random.default_rng(5)
     run_both(ctx, one, rng.uniform(-0.5, 1.5, 40_000), rng.uniform(-0.5, 1.5, 40_000))
+
+
+def test_sequential_scan_kernel_matches(ctx, monkeypatch):
+    """batches above 67 M locations scan their tile totals with the single-CTA kernel; force it here"""
+    zones = S.star_zones(8, nvert=16, cond_mode="alternate")
+    lon, lat = S.locations_for_zones(70_000, *zones[:3], seed=21, boundary_rate=0.01)
+    ctx.set_zones(*zones)
+    want = ctx.zone_test(lon, lat, max_pairs=70_000 * 40)
+    monkeypatch.setenv("SWGPU_ZONE_SCAN", "seq")
+    got = ctx.zone_test(lon, lat, max_pairs=70_000 * 40)
+    assert np.array_equal(got, want) and len(got) > 70_000
