@@ -539,7 +539,7 @@ __device__ __noinline__ int zn_sign_det_scaled(double x1, double y1, double x2, 
     }
     return sp * cmp;
 }
-__device__ __forceinline__ int zn_sign_det(double x1, double y1, double x2, double y2) {
+__device__ __noinline__ int zn_sign_det(double x1, double y1, double x2, double y2) {
     double p = __dmul_rn(x1, y2), q = __dmul_rn(y1, x2);
     if (p > q) return 1;
     if (p < q) return -1;
@@ -590,12 +590,21 @@ __device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, uint32_t info,
         if (e.x < px && e.z < px) break;  // slab edges are ordered by max x, descending: the rest are left too
         const bool up1 = e.y > py, up2 = e.w > py;
         if (up1 != up2) {
-            double x1 = __dsub_rn(e.x, px), y1 = __dsub_rn(e.y, py);
-            double x2 = __dsub_rn(e.z, px), y2 = __dsub_rn(e.w, py);
-            int s = zn_sign_det(x1, y1, x2, y2);
-            if (s == 0) return false;  // on the boundary
-            if (y2 < y1) s = -s;
-            if (s > 0) crossings++;
+            // sign of x1*y2 - y1*x2 on the translated coordinates, flipped when y2 < y1.  With the ends on
+            // different sides, y2 < y1 is exactly `up1` (a difference of unequal doubles never rounds to 0),
+            // and rounded products that differ already order the exact ones (see zn_sign_det).
+            const double x1 = __dsub_rn(e.x, px), y1 = __dsub_rn(e.y, py);
+            const double x2 = __dsub_rn(e.z, px), y2 = __dsub_rn(e.w, py);
+            const double p = __dmul_rn(x1, y2), q = __dmul_rn(y1, x2);
+            const bool gt = p > q, lt = p < q;
+            if (gt | lt) {
+                crossings += (gt != up1) ? 1u : 0u;
+            } else {  // tie (or not comparable): the exact path
+                int sg = zn_sign_det(x1, y1, x2, y2);
+                if (sg == 0) return false;  // on the boundary
+                if (up1) sg = -sg;
+                if (sg > 0) crossings++;
+            }
         } else if (e.w == py) {
             if (px == e.z) return false;  // p is the vertex p2
             if (e.y == py && px >= fmin(e.x, e.z) && px <= fmax(e.x, e.z)) return false;  // on a horizontal edge
