@@ -45,17 +45,19 @@ static_assert(sizeof(ZoneTestRec) == 64, "ZoneTestRec layout");
 // What one location needs in order to test one zone: 32 bytes = one 256-bit load = one L1 wavefront.
 // The grid holds one of these per cell, so the common case (a cell overlapped by a single zone
 // envelope) costs a single dependent load before the edges.  A cell overlapped by several envelopes
-// holds a list head instead (ZC_LIST: `bin_off` = first entry in the list array, `t` = entries).
-//   minx..maxy  the zone's envelope rounded OUTWARD to float.  Only ever used to reject: a point
-//               between the rounded and the exact border goes on to the ring test, which gives the
-//               same answer Geometry.contains' envelope short-circuit would (outside).
-//   miny, minx, inv16  also the slab functions: y-slab = zn_cell(py, (double)miny, scale_y, nbins) and
-//               x-slab = zn_cell(px, (double)minx, scale_x, nbins).  Any origin/scale works as long as
-//               registration and lookup use the same one, so 16 bits of scale are plenty.
+// holds a list head instead (ZC_LIST: `bin_off` = first entry in the list array, `t` = entries), an
+// empty cell a record with ZC_EMPTY.
+//   minx, miny, inv16  the slab functions: x-slab = zn_cell(px, minx, scale_x, nbins) and
+//               y-slab = zn_cell(py, miny, scale_y, nbins).  Any scale works as long as registration and
+//               lookup use the same one, so 16 bits of it are plenty.  The same two products, in slab
+//               units, also pick the ray direction.
 //   bin_off     first edge record of slab 0 (slabs `stride` records apart, each list ended by a
 //               sentinel edge at -inf), or with ZC_RANGES the first {start,end} slab range.
+// There is no envelope in the record: Geometry.contains' envelope short-circuit only ever answers
+// "outside", and for a point outside the envelope the ring walk says the same (its slab is clamped to the
+// first or last one, where no edge straddles the ray and the point is on no edge) after a single record.
 struct ZnCellRec {
-    float minx, maxx, miny, maxy;
+    double minx, miny;
     uint32_t inv16;  // slab scales as the top 16 bits of a float: low half for y-slabs, high half for x-slabs
     uint32_t bin_off;
     uint32_t t;
@@ -65,21 +67,28 @@ static_assert(sizeof(ZnCellRec) == 32, "ZnCellRec layout");
 #define ZC_OUTSIDE 1u   // alert condition == Outside
 #define ZC_RECT 2u      // JTS isRectangle: RectangleContains on the exact envelope
 #define ZC_RANGES 4u    // uneven slabs: {start,end} ranges instead of a fixed stride
+#define ZC_EMPTY 0x40u  // no zone envelope overlaps the cell
 #define ZC_LIST 0x80u   // list head
 #define ZC_MAX_STRIDE 4095u
 
 // monotone cell function shared by host (registration) and device (lookup); separate IEEE
 // sub and mul (no contraction) so both sides round identically.
-__host__ __device__ __forceinline__ uint32_t zn_cell(double v, double v0, double inv, uint32_t n) {
+__host__ __device__ __forceinline__ double zn_cell_pos(double v, double v0, double inv) {
 #ifdef __CUDA_ARCH__
-    double t = __dmul_rn(__dsub_rn(v, v0), inv);
+    return __dmul_rn(__dsub_rn(v, v0), inv);
 #else
     volatile double d = v - v0;
     volatile double t = d * inv;
+    return t;
 #endif
+}
+__host__ __device__ __forceinline__ uint32_t zn_cell_clamp(double t, uint32_t n) {
     if (!(t >= 0.0)) return 0;
     if (t >= (double)n) return n - 1;
     return (uint32_t)t;
+}
+__host__ __device__ __forceinline__ uint32_t zn_cell(double v, double v0, double inv, uint32_t n) {
+    return zn_cell_clamp(zn_cell_pos(v, v0, inv), n);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -103,12 +112,6 @@ static bool host_is_rectangle(const double *x, const double *y, uint32_t npts, d
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// nearest floats at or below / at or above v (±inf when v is beyond the float range: still a valid bound)
-static float f_down(double v) {
-    float f = (float)v;
-    if ((double)f > v) f = nextafterf(f, -INFINITY);
-    return f;
-}
 // slab scale kept as the top 16 bits of its float value (sign, exponent, 7 mantissa bits)
 static uint32_t inv_bits16(double invd) {
     if (!(invd > 0) || !std::isfinite(invd)) return 0;
@@ -123,11 +126,6 @@ static double inv_from16(uint32_t b16) {
     float f;
     memcpy(&f, &b, 4);
     return (double)f;
-}
-static float f_up(double v) {
-    float f = (float)v;
-    if ((double)f < v) f = nextafterf(f, INFINITY);
-    return f;
 }
 
 static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, const double *lon,
@@ -205,10 +203,8 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
         // the compact record the grid cells carry
         ZnCellRec &cr = crecs[t];
         memset(&cr, 0, sizeof cr);
-        cr.minx = f_down(minx);
-        cr.maxx = f_up(maxx);
-        cr.miny = f_down(miny);
-        cr.maxy = f_up(maxy);
+        cr.minx = minx;
+        cr.miny = miny;
         cr.t = t;
         // slabs over edges i = 1..npts-1 (edge i joins ring[i] and ring[i-1])
         if (rect) {
@@ -228,7 +224,7 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
             // point's slab and is met before the walk stops, whichever way it goes.
             const uint32_t nb = std::max(1u, std::min(64u, (z.npts - 1 + 3) / 4));
             const double *uc[2] = {xs.data(), ys.data()};  // axis 0: ray along x, slabs along y
-            const double v0[2] = {(double)cr.miny, (double)cr.minx};  // slab origins: at or below every vertex
+            const double v0[2] = {miny, minx};  // slab origins
             const double vmax[2] = {maxy, maxx};
             uint32_t inv16[2];
             double inv[2];
@@ -377,8 +373,7 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
         ZnCellRec &e = cell_tab[c];
         memset(&e, 0, sizeof e);
         if (k1 == k0) {
-            e.minx = e.miny = INFINITY;  // rejects every point
-            e.maxx = e.maxy = -INFINITY;
+            e.info = ZC_EMPTY;
         } else if (k1 - k0 == 1) {
             e = crecs[cell_items[k0]];
         } else {
@@ -613,9 +608,6 @@ __device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, uint32_t info,
     return crossings & 1;
 }
 
-__device__ __forceinline__ float zn_lo_f(double v) { return __int_as_float(__double2loint(v)); }
-__device__ __forceinline__ float zn_hi_f(double v) { return __int_as_float(__double2hiint(v)); }
-
 // Visit the tests whose polygon contains (px,py), in ascending test order.
 template <typename F>
 __device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, double py, F f) {
@@ -626,35 +618,33 @@ __device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, d
     ZnD4 r = zn_ld256(ct + (cy * h.grid_nx + cx));
     uint32_t n = 1;
     const ZnD4 *lp = nullptr;
-    if ((uint32_t)__double2hiint(r.w) & ZC_LIST) {
+    if ((uint32_t)__double2hiint(r.w) & (ZC_LIST | ZC_EMPTY)) {
+        if ((uint32_t)__double2hiint(r.w) & ZC_EMPTY) return;
         n = (uint32_t)__double2loint(r.w);
         lp = (const ZnD4 *)(a.blob + h.off_cell_items) + (uint32_t)__double2hiint(r.z);
         r = zn_ld256(lp);
     }
     for (uint32_t k = 0;;) {
-        // conservative (float, rounded outward) envelope: rejects only what Geometry.contains' envelope test rejects
-        const double minx = (double)zn_lo_f(r.x), maxx = (double)zn_hi_f(r.x);
-        const double miny = (double)zn_lo_f(r.y), maxy = (double)zn_hi_f(r.y);
-        if (px >= minx && px <= maxx && py >= miny && py <= maxy) {
-            const uint32_t t = (uint32_t)__double2loint(r.w), info = (uint32_t)__double2hiint(r.w);
-            bool in;
-            if (info & ZC_RECT) {  // RectangleContains: inside the exact envelope and not on its border
-                const ZnD4 ev = zn_ld256((const ZoneTestRec *)(a.blob + h.off_tests) + t);
-                in = px > ev.x && px < ev.y && py > ev.z && py < ev.w;
-            } else {
-                // the ray that leaves the envelope soonest, in slab units (both axes have nb slabs)
-                const uint32_t nb = (info >> 8) & 0xfffu, i16 = (uint32_t)__double2loint(r.z);
-                const double sy = (double)__int_as_float(i16 << 16), sx = (double)__int_as_float(i16 & 0xffff0000u);
-                const double dl = (px - minx) * sx, dr = (maxx - px) * sx, db = (py - miny) * sy, dt = (maxy - py) * sy;
-                const bool alongy = fmin(db, dt) < fmin(dl, dr);
-                const bool neg = alongy ? db < dt : dl < dr;
-                // ray along x: slabs by y (copies 0 .. 2nb-1); along y: slabs by x (copies 2nb .. 4nb-1)
-                const uint32_t sl = alongy ? nb + zn_cell(px, minx, sx, nb) : zn_cell(py, miny, sy, nb);
-                const double u = alongy ? py : px, v = alongy ? px : py;
-                in = zn_ring_interior(a, info, (uint32_t)__double2hiint(r.z), 2u * sl + (neg ? 1u : 0u), neg ? -u : u, v);
-            }
-            if (in) f(t, info & ZC_OUTSIDE);
+        const uint32_t t = (uint32_t)__double2loint(r.w), info = (uint32_t)__double2hiint(r.w);
+        bool in;
+        if (info & ZC_RECT) {  // RectangleContains: inside the exact envelope and not on its border
+            const ZnD4 ev = zn_ld256((const ZoneTestRec *)(a.blob + h.off_tests) + t);
+            in = px > ev.x && px < ev.y && py > ev.z && py < ev.w;
+        } else {
+            // position of the point in slab units from the envelope's low corner (both axes have nb slabs):
+            // gives the slab on either axis and the ray that leaves the envelope soonest
+            const uint32_t nb = (info >> 8) & 0xfffu, i16 = (uint32_t)__double2loint(r.z);
+            const double sy = (double)__int_as_float(i16 << 16), sx = (double)__int_as_float(i16 & 0xffff0000u);
+            const double tl = zn_cell_pos(px, r.x, sx), tb = zn_cell_pos(py, r.y, sy);
+            const double tr = (double)nb - tl, tt = (double)nb - tb;
+            const bool alongy = fmin(tb, tt) < fmin(tl, tr);
+            const bool neg = alongy ? tb < tt : tl < tr;
+            // ray along x: slabs by y (copies 0 .. 2nb-1); along y: slabs by x (copies 2nb .. 4nb-1)
+            const uint32_t sl = alongy ? nb + zn_cell_clamp(tl, nb) : zn_cell_clamp(tb, nb);
+            const double u = alongy ? py : px, v = alongy ? px : py;
+            in = zn_ring_interior(a, info, (uint32_t)__double2hiint(r.z), 2u * sl + (neg ? 1u : 0u), neg ? -u : u, v);
         }
+        if (in) f(t, info & ZC_OUTSIDE);
         if (++k >= n) break;
         r = zn_ld256(lp + k);
     }
@@ -791,22 +781,31 @@ struct ZnWork {
     uint64_t *tile_base;  // [ntiles]
 };
 
-__global__ void __launch_bounds__(ZN_THREADS, 5) zone_count_kernel(ZnArgs a, ZnWork w) {
+__global__ void __launch_bounds__(ZN_THREADS, 6) zone_count_kernel(ZnArgs a, ZnWork w) {
     __shared__ uint32_t s_part[ZN_THREADS / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
     const uint32_t i = blockIdx.x * ZN_THREADS + tid;
-    ZnLoc L;
-    zn_eval(a, i, n_live, L);
-    if (i < a.n) {
-        if (a.h.n_outside == 0 && L.count <= 2) {  // test ids are below 2^31 (one vertex each at least)
-            const uint64_t id0 = L.n_in > 0 ? (L.ins[0] >> 1) : 0u, id1 = L.n_in > 1 ? (L.ins[1] >> 1) : 0u;
-            w.park[i] = (uint64_t)L.count | (id0 << 2) | (id1 << 33);
-        } else {
-            w.park[i] = 3u | ((uint64_t)L.count << 2);
-        }
+    // only the count and the first two containing tests are kept here; a location with more alerts (or
+    // with Outside-condition tests) is evaluated again by the emit kernel
+    uint32_t id0 = 0, id1 = 0, n_in = 0, n_oc = 0, count = 0;
+    if (zn_row_valid(a, i, n_live)) {
+        zn_for_each_inside(a, __ldg(a.lon + i), __ldg(a.lat + i), [&](uint32_t t, uint32_t outside_cond) {
+            if (n_in == 0) id0 = t;
+            if (n_in == 1) id1 = t;
+            n_in++;
+            n_oc += outside_cond;
+        });
+        // alerts: Inside-condition tests that contain the point + Outside-condition tests that do not
+        count = (n_in - n_oc) + (a.h.n_outside - n_oc);
     }
-    uint32_t s = L.count;
+    if (i < a.n) {
+        if (a.h.n_outside == 0 && count <= 2)  // test ids are below 2^31 (one vertex each at least)
+            w.park[i] = (uint64_t)count | ((uint64_t)id0 << 2) | ((uint64_t)id1 << 33);
+        else
+            w.park[i] = 3u | ((uint64_t)count << 2);
+    }
+    uint32_t s = count;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(SW_FULL, s, o);
     if (lane == 0) s_part[warp] = s;
