@@ -165,6 +165,43 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+
+def pcie_probe(torch, dev, nbytes=256 << 20, reps=4):
+    """Host<->device copy rates of this box (pinned memory): each direction alone, then both at once."""
+    hin = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    hout = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    din = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    dout = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+    s1, s2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+
+    def run(up, down):
+        torch.cuda.synchronize()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        if up:
+            ev[0].record(s1)
+        if down:
+            ev[2].record(s2)
+        for _ in range(reps):
+            if up:
+                with torch.cuda.stream(s1):
+                    din.copy_(hin, non_blocking=True)
+            if down:
+                with torch.cuda.stream(s2):
+                    hout.copy_(dout, non_blocking=True)
+        if up:
+            ev[1].record(s1)
+        if down:
+            ev[3].record(s2)
+        torch.cuda.synchronize()
+        gb = nbytes * reps / 1e6
+        return (gb / ev[0].elapsed_time(ev[1]) if up else None, gb / ev[2].elapsed_time(ev[3]) if down else None)
+
+    run(True, True)
+    h, _ = run(True, False)
+    _, d = run(False, True)
+    dh, dd = run(True, True)
+    return {"h2d_GBps": h, "d2h_GBps": d, "duplex_h2d_GBps": dh, "duplex_d2h_GBps": dd}
+
 def run_extras(ctx, sw, torch, stream, dev, peak):
     """Secondary measurements of the other rows of the scope table (not the headline): the JSON decoder on
     the C1 shape and decode + device-state merge on the C3 shape, device-resident, CUDA events."""
@@ -345,7 +382,7 @@ def run_ours(args):
     # locations), status, first_row, and the alert pairs.
     from sitewhere_b200.api import pinned_array, pinned_cols
     e2e_cols = ["meta", "event_date", "v0", "v1", "v2", "token_span"]
-    e2e_value, h2d, d2h, e2e_steps = None, 0, 0, 0
+    e2e_value, h2d, d2h, e2e_steps, pcie = None, 0, 0, 0, None
     if not args.no_e2e:
         p_data = pinned_array((total_bytes,), np.uint8)
         p_data[:] = data
@@ -376,6 +413,14 @@ def run_ours(args):
         e2e_value = n * world * e2e_steps / float(te.item())
         h2d = total_bytes + 8 * (n + 1)
         d2h = len(e2e_cols) * 8 * r_rows + n + 4 * (n + 1) + 8 * r_pairs
+        # the link's own ceiling on this box, for context: pinned copies, each direction alone and both at once
+        pcie = None
+        if rank == 0:
+            try:
+                pcie = pcie_probe(torch, dev)
+                pcie["floor_ms"] = max(h2d / (pcie["duplex_h2d_GBps"] * 1e6), d2h / (pcie["duplex_d2h_GBps"] * 1e6))
+            except Exception as e:  # context only
+                pcie = {"error": repr(e)[:120]}
 
     if rank == 0:
         peak, peak_src = measured_peaks()
@@ -383,13 +428,17 @@ def run_ours(args):
         bytes_zone = 24 * n + 8 * n_pairs
         gbs_dec = bytes_dec / (ms_dec * 1e-3) / 1e9
         gbs_zone = bytes_zone / (ms_zone * 1e-3) / 1e9
-        dom = "pb_decode_kernel" if ms_dec >= ms_zone else "zone_test (zone_count_kernel + zone_scan_kernel + zone_emit_kernel)"
+        # The decode stage is pb_decode_kernel<dense> plus the ordered pass that returns at once (~3 us); the zone
+        # stage is three launches of which zone_count_kernel is the largest (84 % of the stage in the committed
+        # launch list, profiles/r01c_launches.csv).  Dominant kernel = the longer single launch.
+        ZONE_COUNT_SHARE = 0.843
+        dom = "pb_decode_kernel" if ms_dec >= ZONE_COUNT_SHARE * ms_zone else "zone_test (zone_count_kernel + zone_scan_mc_kernel + zone_emit_kernel)"
         ach = gbs_dec if dom == "pb_decode_kernel" else gbs_zone
         # DRAM bytes per launch from the committed `ncu --set full` capture of this very workload
-        # (profiles/r01_ncu_full_summary.md): decode 730.7 + 712.8 MB; zone 247.9 + 96.7 (count) + 119.8 + 11.7 (emit) MB
+        # (profiles/r01c_ncu_full_summary.md): decode 730.7 + 712.3 MB; zone 258.8 + 67.1 (count) + 0.3 (scan) + 80.4 + 7.4 (emit) MB
         traffic = None
         if n == 10_000_000:
-            traffic = 1.4435e9 if dom == "pb_decode_kernel" else 476.1e6
+            traffic = 1.4429e9 if dom == "pb_decode_kernel" else 414.0e6
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_all / args.steps, "higher_is_better": True,
@@ -401,18 +450,20 @@ def run_ours(args):
                              % (total_bytes / 1e6, 72 * n / 1e6),
                        "sharding": "Kafka murmur2(deviceToken) % n_gpus; zone table NCCL-broadcast once"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps},
+                    "steps": e2e_steps, "ms_per_step": (n * world / e2e_value * 1e3) if e2e_value else None,
+                    "pcie": pcie},
             # per step: pb_decode_kernel<dense>, pb_decode_kernel<ordered> (returns at once on a dense batch),
-            # zone_count_kernel, zone_scan_kernel, zone_emit_kernel
+            # zone_count_kernel, zone_scan_mc_kernel, zone_emit_kernel
             "gpu_launches": 5 * args.steps,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
-                         "note": "the zone test is bound by L1 wavefronts / FP64 issue on an L2-resident table, not by HBM; "
-                                 "the HBM-bound kernel of the step is pb_decode_kernel (kernels.pb_decode_kernel.frac_hbm)"},
+                         "note": "pb_decode_kernel<dense> is the longest launch of the step and is HBM-bound; the zone test "
+                                 "(kernels.zone_test_kernel) is bound by instruction issue at ~17 active lanes per "
+                                 "warp instruction on an L2-resident table, not by HBM"},
             "kernels": {"pb_decode_kernel": {"ms": ms_dec, "algorithmic_bytes": bytes_dec, "GBps": gbs_dec,
                                              "frac_hbm": gbs_dec / peak, "events_per_s": n / (ms_dec * 1e-3)},
                         "zone_test_kernel": {"ms": ms_zone, "algorithmic_bytes": bytes_zone, "GBps": gbs_zone,
-                                             "frac_hbm": gbs_zone / peak, "bound": "fp64/latency (zone table in L2)",
+                                             "frac_hbm": gbs_zone / peak, "bound": "instruction issue / divergence (zone table in L2)",
                                              "locations_per_s": n / (ms_zone * 1e-3)}},
             "clocks": clocks,
         }

@@ -203,7 +203,7 @@ int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const double *lat
  * micro-batcher issues per batch.  Replaces IDeviceEventDecoder.decode per payload
  * (ES/spi/IDeviceEventDecoder.java:39) followed by ZoneTestRuleProcessor.onLocation per decoded location
  * (RP/processors/geospatial/ZoneTestRuleProcessor.java:47-63).  The batch is processed in chunks of
- * `chunk_records` records (0 = default 262,144) through a three-slot device ring so that the copy-in of
+ * `chunk_records` records (0 = about a dozen chunks per call, between 131,072 and 1,048,576 records each) through a three-slot device ring so that the copy-in of
  * the next chunk, the kernels of the current one and the copy-out of the previous one overlap; for
  * that the caller's buffers should come from swgpu_alloc_pinned (pageable memory works, slower).
  * Outputs are exactly those of swgpu_decode_{pb,json} followed by swgpu_zone_test on the decoded

@@ -641,8 +641,18 @@ int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
     a.row_next = row_next;
     a.not_dense = (uint32_t *)ctx->scratch + 1;
     const int smem = PB_WARPS * (PB_WSTAGE + 32);
-    SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    {
+        // per device, once: the attribute is a property of the loaded function
+        static std::mutex mu;
+        static bool done[64] = {false};
+        std::lock_guard<std::mutex> lk(mu);
+        const int d = ctx->device & 63;
+        if (!done[d]) {
+            SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            done[d] = true;
+        }
+    }
     pb_decode_kernel<true><<<ntiles, PB_THREADS, smem, ctx->stream>>>(a);   // optimistic: rows = records
     SW_CUDA(ctx, cudaGetLastError());
     const uint32_t nredo = std::min<uint32_t>(ntiles, (uint32_t)ctx->sm_count * 4u);
