@@ -4,16 +4,20 @@
 //  containment = JTS 1.13 Polygon.contains(Point): envelope short-circuit, isRectangle ->
 //  RectangleContains, else RayCrossingCounter with RobustDeterminant.signOfDet2x2).
 //
-// Results are bit-identical to the index-free reference loop; two exact accelerations remove work
+// Results are bit-identical to the index-free reference loop; three exact accelerations remove work
 // that cannot change the answer:
 //   * a uniform grid over zone envelopes: Geometry.contains starts with an envelope test, so a
 //     test whose envelope misses the point's grid cell is Outside.  Cell ids come from the same
 //     monotone expression on host (registration) and device (lookup), so a point inside an
 //     envelope always finds that zone in its cell.
-//   * per-zone y-slabs over ring edges: an edge whose y-range misses the point's slab is strictly
-//     above or below the ray; RayCrossingCounter.countSegment neither counts it nor flags a boundary.
+//   * per-zone slabs across the ray: an edge whose range misses the point's slab is strictly on one
+//     side of the ray; RayCrossingCounter.countSegment neither counts it nor flags a boundary.
+//   * a choice of ray: every ring is stored for the four axis-parallel ray directions and the walk
+//     takes the one that leaves the envelope soonest; the crossing parity and the on-boundary
+//     verdict do not depend on the direction (see build_zone_blob).
 // Crossing side = exact sign of x1*y2 - y1*x2 on the translated coordinates via error-free products
-// (fma), the value RobustDeterminant returns.  FP64 pipe bound; the zone table lives in L2.
+// (fma), the value RobustDeterminant returns.  Bound by instruction issue (walk lengths differ per
+// lane); the zone table lives in L2.
 #include <math.h>
 
 #include <algorithm>
