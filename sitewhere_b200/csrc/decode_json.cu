@@ -73,6 +73,23 @@ struct JsonScan {
         const uint32_t start = pos;
         info = 0;
         for (;;) {
+            // eight bytes at a time while they are plain string content: stop at the first byte that is a
+            // quote, a backslash, a control character or non-ASCII (exact per byte: the low seven bits are
+            // tested with carry-free adds, the high bit separately), and let the byte-wise rules below take it
+            while (pos + 8 <= n) {
+                const uint64_t w = b.le64(pos);
+                const uint64_t l = w & 0x7f7f7f7f7f7f7f7full;
+                const uint64_t q = l ^ 0x2222222222222222ull, bs = l ^ 0x5c5c5c5c5c5c5c5cull;
+                const uint64_t m = (w | ~(l + 0x6060606060606060ull) | ~(q + 0x7f7f7f7f7f7f7f7full) |
+                                    ~(bs + 0x7f7f7f7f7f7f7f7full)) &
+                                   0x8080808080808080ull;
+                if (m == 0) {
+                    pos += 8;
+                    continue;
+                }
+                pos += (uint32_t)(__ffsll((long long)m) - 1) >> 3;
+                break;
+            }
             if (pos >= n) return false;
             uint32_t c = b.byte(pos);
             if (c == '"') break;
@@ -164,7 +181,25 @@ struct JsonScan {
         }
         return true;
     }
-    __device__ bool key_is(uint32_t off, const char *lit, uint32_t l) const {
+    // bytes [off, off+l) == lit (l <= 16; the caller has scanned the key, so off + l <= n).  One or two
+    // 8-byte reads against constants instead of a byte loop; byte-wise only for a short key in the last
+    // bytes of the record.
+    static __device__ __forceinline__ uint64_t lit64(const char *lit, uint32_t l) {
+        uint64_t v = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < 8; k++)
+            if (k < l) v |= (uint64_t)(uint8_t)lit[k] << (8 * k);
+        return v;
+    }
+    __device__ __forceinline__ bool key_is(uint32_t off, const char *lit, uint32_t l) const {
+        if (l <= 8) {
+            if (off + 8 <= n) {
+                const uint64_t mask = l == 8 ? ~0ull : ((1ull << (8 * (l & 7))) - 1ull);
+                return (b.le64(off) & mask) == lit64(lit, l);
+            }
+        } else {
+            return b.le64(off) == lit64(lit, 8) && b.le64(off + l - 8) == lit64(lit + (l - 8), 8);
+        }
         for (uint32_t k = 0; k < l; k++)
             if (b.byte(off + k) != (uint32_t)(uint8_t)lit[k]) return false;
         return true;
