@@ -17,7 +17,7 @@
 
 #define JS_THREADS 128
 #define JS_WARPS (JS_THREADS / 32)
-#define JS_WSTAGE (12 * 1024)  // bytes staged per warp tile: 32 records of up to 384 B on average
+#define JS_WSTAGE (8 * 1024)  // bytes staged per warp tile: 32 records of up to 256 B on average (more CTAs per SM than 12 KiB)
 #define JS_MAX_DEPTH 256
 
 struct JsArgs {
