@@ -21,8 +21,14 @@ for l in sass:
     m = re.match(r"\s+/\*([0-9a-f]{4,})\*/", l)
     if m:
         line_of[int(m.group(1), 16)] = cur
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+import os
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + os.environ.get("NCU_ARGS", "").split(), capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
+# a report with several kernels prints one section per kernel: keep the first
+for j in range(2, len(rows)):
+    if rows[j] and rows[j][0] == "Kernel Name":
+        rows = rows[:j]
+        break
 hdr = rows[1]
 ia, iw, it, iss = hdr.index("Address"), hdr.index("Instructions Executed"), hdr.index("Thread Instructions Executed"), hdr.index("Warp Stall Sampling (All Samples)")
 data = rows[2:]
