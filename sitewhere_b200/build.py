@@ -57,7 +57,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         f.write("\n".join(log))
     if verbose:
         print("\n".join(log))
-    cmd = [nvcc(), "-shared", "-o", OUT, *objs, "-cudart", "static",
+    # the arch is given to the link step too: without it nvcc adds a device-link stub for its default (sm_52)
+    cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", OUT, *objs, "-cudart", "static",
            "-Xlinker", "--exclude-libs,ALL"]
     subprocess.check_call(cmd)
     return OUT
