@@ -39,6 +39,8 @@ def main():
             continue
         j = hdr.index(m)
         print("| %s | %s | %s |" % (m, units[j], " | ".join(r[j] for r in data)))
+    if launches == "-":
+        return
     print("\n## Launch list of the timed steps (`ncu --metrics gpu__time_duration.sum`), microseconds\n")
     rows = list(csv.reader(open(launches)))
     for i, r in enumerate(rows):
