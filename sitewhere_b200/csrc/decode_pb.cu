@@ -573,9 +573,10 @@ __device__ __forceinline__ void pb_decode_tile(const PbArgs &a, const uint32_t t
     }
 }
 
-// DENSE: one CTA per tile.  Ordered pass: a few CTAs per SM take tiles by ticket (tickets are handed out
-// in start order, which is what the look-back needs), so when the dense pass was exact — the usual
-// case — the launch costs a few hundred CTAs that read one flag, not one CTA per tile.
+// DENSE: one CTA per tile (kept for reference and for the JSON decoder's twin; the protobuf dense pass
+// now runs pb_decode_dense_kernel below).  Ordered pass: a few CTAs per SM take tiles by ticket (tickets
+// are handed out in start order, which is what the look-back needs), so when the dense pass was exact —
+// the usual case — the launch costs a few hundred CTAs that read one flag, not one CTA per tile.
 template <bool DENSE>
 __global__ void __launch_bounds__(PB_THREADS) pb_decode_kernel(PbArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];  // PB_WARPS * (PB_WSTAGE + 32)
@@ -595,6 +596,127 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_kernel(PbArgs a) {
         pb_decode_tile<false>(a, tile, smem, s_warp);
         __syncthreads();  // s_tile, s_warp and the staging buffers are reused
     }
+}
+
+// ---- dense pass, pipelined.  Same work per warp-tile (32 records) as pb_decode_tile<true>, but a warp goes
+// through PD_TILES consecutive tiles with the NEXT tile's payload already on its way into the other half
+// of its shared-memory slice (cp.async, 16 bytes per lane per step) and the offsets of the tile after that
+// already requested, so the two serial round trips at the head of a tile (offsets, then payload: half of
+// the stall samples of the one-tile-per-warp kernel) are paid once per warp instead of once per tile.
+#define PD_TILES 4
+#define PD_STAGE 3072  // bytes staged per warp tile (32 records of up to 96 B on average); larger tiles read global memory
+
+__device__ __forceinline__ void pd_cp_async16(uint8_t *dst_smem, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void pd_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void pd_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// A tile in flight is just this lane's record offsets; everything else (record count, first byte, alignment
+// lead, whether it fits the stage) is recomputed from them when needed — a few shuffles and integer ops
+// instead of a dozen live registers per tile.
+struct PdTile {
+    uint64_t r0, r1;  // this lane's record: [r0, r1) in the payload
+};
+struct PdGeom {
+    uint64_t b0;  // first byte of the warp tile
+    uint32_t rec0, nrec, lead;
+    bool staged;
+};
+__device__ __forceinline__ uint32_t pd_nrec(const PbArgs &a, uint32_t wt, uint32_t nwt) {
+    return wt < nwt ? min(32u, a.n - wt * 32u) : 0u;
+}
+__device__ __forceinline__ void pd_load_offsets(const PbArgs &a, uint32_t wt, uint32_t nwt, uint32_t lane, PdTile &t) {
+    t.r0 = t.r1 = 0;
+    if (lane < pd_nrec(a, wt, nwt)) {
+        t.r0 = __ldg(a.rec_off + wt * 32u + lane);
+        t.r1 = __ldg(a.rec_off + wt * 32u + lane + 1);
+    }
+}
+__device__ __forceinline__ PdGeom pd_geom(const PbArgs &a, uint32_t wt, uint32_t nwt, const PdTile &t, uint64_t &span) {
+    PdGeom g;
+    g.nrec = pd_nrec(a, wt, nwt);
+    g.rec0 = wt < nwt ? wt * 32u : a.n;
+    g.b0 = __shfl_sync(SW_FULL, t.r0, 0);
+    const uint64_t b1 = __shfl_sync(SW_FULL, t.r1, g.nrec ? g.nrec - 1 : 0);
+    g.lead = (uint32_t)((uintptr_t)(a.bytes + g.b0) & 15);
+    span = (uint64_t)g.lead + (b1 - g.b0);
+    g.staged = span <= PD_STAGE;
+    return g;
+}
+// request the tile's bytes (needs the offsets): one commit group per tile, possibly empty
+__device__ __forceinline__ void pd_issue(const PbArgs &a, uint32_t wt, uint32_t nwt, uint32_t lane, const PdTile &t,
+                                         uint8_t *buf) {
+    uint64_t span;
+    const PdGeom g = pd_geom(a, wt, nwt, t, span);
+    if (g.staged && g.nrec) {
+        const uint8_t *src = a.bytes + g.b0 - g.lead;
+        const uint32_t nvec = (uint32_t)((span + 15) >> 4);
+        for (uint32_t i = lane; i < nvec; i += 32) pd_cp_async16(buf + 16 * i, src + 16 * i);
+    }
+    pd_commit();
+}
+
+__global__ void __launch_bounds__(PB_THREADS) pb_decode_dense_kernel(PbArgs a) {
+    extern __shared__ __align__(16) uint8_t smem[];  // PB_WARPS * 2 * (PD_STAGE + 32)
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t nwt = (a.n + 31u) / 32u;  // warp tiles in the batch
+    const uint32_t first = (blockIdx.x * PB_WARPS + warp) * PD_TILES;
+    if (first >= nwt) return;
+    uint8_t *const slice = smem + (size_t)(warp * 2) * (PD_STAGE + 32);
+    const uint64_t row_base = a.row_base ? (uint64_t)__ldg(a.row_base) : 0ull;  // rows of earlier chunks
+    PdTile cur, nxt, nn;
+    pd_load_offsets(a, first, nwt, lane, cur);
+    pd_load_offsets(a, first + 1, nwt, lane, nxt);
+    pd_issue(a, first, nwt, lane, cur, slice);
+#pragma unroll 1
+    for (uint32_t k = 0; k < PD_TILES; k++) {
+        const uint32_t wt = first + k;
+        if (wt >= nwt) break;  // past the end of the batch
+        // tile k+1: bytes on their way; tile k+2: offsets requested
+        pd_issue(a, wt + 1, nwt, lane, nxt, slice + ((k + 1) & 1) * (PD_STAGE + 32));
+        pd_load_offsets(a, k + 2 < PD_TILES ? wt + 2 : nwt, nwt, lane, nn);
+        pd_wait<1>();  // everything but the newest group, i.e. tile k, has landed
+        __syncwarp();
+        uint64_t span;
+        const PdGeom g = pd_geom(a, wt, nwt, cur, span);
+        const uint8_t *ws = slice + (k & 1) * (PD_STAGE + 32);
+        if (lane < g.nrec) {
+            PbOut o;
+            o.count = 0;
+            o.status = 0;
+            const uint64_t l64 = cur.r1 - cur.r0;
+            const uint32_t len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
+            if (g.staged)
+                pb_parse_record(SmemBytes{ws + g.lead + (uint32_t)(cur.r0 - g.b0)}, len, o);
+            else
+                pb_parse_record(GmemBytes{a.bytes + cur.r0}, len, o);
+            const uint32_t rec = g.rec0 + lane;
+            const uint64_t row0 = rec;  // row index = record index
+            if (o.count != 1) atomicOr(a.not_dense, 1u);
+            a.status[rec] = (uint8_t)o.status;
+            a.first_row[rec] = (uint32_t)(row_base + row0);
+            if (o.count == 1) {
+                if (g.staged)
+                    pb_write_rows(a, SmemBytes{ws + g.lead + (uint32_t)(cur.r0 - g.b0)}, o, rec, row0);
+                else
+                    pb_write_rows(a, GmemBytes{a.bytes + cur.r0}, o, rec, row0);
+            }
+            if (rec == a.n - 1) {  // the last record of the batch
+                a.first_row[a.n] = (uint32_t)(row_base + a.n);
+                *a.out_rows = a.n;
+                if (a.row_next) *a.row_next = (uint32_t)(row_base + a.n);
+            }
+        }
+        __syncwarp();  // the buffer is refilled two tiles from now
+        cur = nxt;
+        nxt = nn;
+    }
+    pd_wait<0>();
 }
 
 static int check_cols(swgpu_ctx *ctx, const swgpu_decoded_cols *c) {
@@ -648,12 +770,19 @@ int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
         std::lock_guard<std::mutex> lk(mu);
         const int d = ctx->device & 63;
         if (!done[d]) {
-            SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
             SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              PB_WARPS * 2 * (PD_STAGE + 32)));
             done[d] = true;
         }
     }
-    pb_decode_kernel<true><<<ntiles, PB_THREADS, smem, ctx->stream>>>(a);   // optimistic: rows = records
+    {
+        // optimistic: rows = records.  Pipelined kernel: PD_TILES warp tiles per warp.
+        const int dsmem = PB_WARPS * 2 * (PD_STAGE + 32);
+        const uint32_t nwt = (n + 31u) / 32u;
+        const uint32_t per_cta = PB_WARPS * PD_TILES;
+        pb_decode_dense_kernel<<<(nwt + per_cta - 1) / per_cta, PB_THREADS, dsmem, ctx->stream>>>(a);
+    }
     SW_CUDA(ctx, cudaGetLastError());
     const uint32_t nredo = std::min<uint32_t>(ntiles, (uint32_t)ctx->sm_count * 4u);
     pb_decode_kernel<false><<<nredo, PB_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
