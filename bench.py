@@ -38,6 +38,8 @@ ZONE_GRID = 32          # 32 x 32 = 1,024 zones
 ZONE_VERTS = 64
 
 
+WORKLOAD = "C2: 10M protobuf DeviceLocation decode + zone test vs 1,024 concave 64-vertex zones"
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -156,8 +158,8 @@ def run_reference(args):
             "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8/f64", "data": "synthetic",
             "impl": "reference",
-            "config": {"workload": "C2: protobuf DeviceLocation decode + zone test, 1,024 concave 64-vertex zones",
-                       "events_per_step": sample, "zones": ZONE_GRID * ZONE_GRID, "vertices": ZONE_VERTS},
+            "config": {"workload": WORKLOAD, "sample_events_per_step": sample, "zones": ZONE_GRID * ZONE_GRID,
+                       "vertices": ZONE_VERTS, "devices": N_DEVICES},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{sample} events of the C2 workload per step (JVM path unavailable: no JDK on this box)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -443,7 +445,7 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_all / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8/f64", "data": "synthetic",
-            "config": {"workload": "C2: 10M protobuf DeviceLocation decode + zone test vs 1,024 concave 64-vertex zones",
+            "config": {"workload": WORKLOAD,
                        "events_per_gpu_per_step": n, "zones": ZONE_GRID * ZONE_GRID, "vertices": ZONE_VERTS,
                        "devices": N_DEVICES, "alerts_per_step": n_pairs,
                        "l2": "inputs (%.0f MB payload + %.0f MB columns) exceed the 126 MB L2; no flush needed"
