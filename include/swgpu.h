@@ -204,7 +204,9 @@ int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const double *lat
  * (ES/spi/IDeviceEventDecoder.java:39) followed by ZoneTestRuleProcessor.onLocation per decoded location
  * (RP/processors/geospatial/ZoneTestRuleProcessor.java:47-63).  The batch is processed in chunks of
  * `chunk_records` records (0 = about a dozen chunks per call, between 131,072 and 1,048,576 records each) through a three-slot device ring so that the copy-in of
- * the next chunk, the kernels of the current one and the copy-out of the previous one overlap; for
+ * the next chunk, the kernels of the current one and the copy-out of the previous one overlap (a batch of at
+ * most 16,384 records with chunk_records = 0 instead takes one staging block each way: one upload, the
+ * kernels, one download — a 64 KB poll completes in ~75 us on the calling thread); for
  * that the caller's buffers should come from swgpu_alloc_pinned (pageable memory works, slower).
  * Outputs are exactly those of swgpu_decode_{pb,json} followed by swgpu_zone_test on the decoded
  * lon/lat/meta columns: rows in reference order, `first_row` / `status` per record, alert pairs

@@ -656,6 +656,15 @@ __device__ __forceinline__ void pd_issue(const PbArgs &a, uint32_t wt, uint32_t 
     if (g.staged && g.nrec) {
         const uint8_t *src = a.bytes + g.b0 - g.lead;
         const uint32_t nvec = (uint32_t)((span + 15) >> 4);
+#ifdef SWGPU_DEBUG_BOUNDS
+        {
+            const uint8_t *lo = a.bytes + __ldg(a.rec_off) - 16, *hi = a.bytes + __ldg(a.rec_off + a.n) + 64;
+            if (lane == 0 && (src < lo || src + 16 * (size_t)nvec > hi || nvec > (PD_STAGE + 16) / 16))
+                printf("pd_issue OOB: wt %u nrec %u b0 %llu span %llu lead %u nvec %u src-lo %lld hi-end %lld\n", wt, g.nrec,
+                       (unsigned long long)g.b0, (unsigned long long)span, g.lead, nvec, (long long)(src - lo),
+                       (long long)(hi - (src + 16 * (size_t)nvec)));
+        }
+#endif
         for (uint32_t i = lane; i < nvec; i += 32) pd_cp_async16(buf + 16 * i, src + 16 * i);
     }
     pd_commit();
@@ -678,7 +687,8 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_dense_kernel(PbArgs a) {
         const uint32_t wt = first + k;
         if (wt >= nwt) break;  // past the end of the batch
         // tile k+1: bytes on their way; tile k+2: offsets requested
-        pd_issue(a, wt + 1, nwt, lane, nxt, slice + ((k + 1) & 1) * (PD_STAGE + 32));
+        // (the warp's last tile has no successor of its own: an empty group keeps the wait below uniform)
+        pd_issue(a, k + 1 < PD_TILES ? wt + 1 : nwt, nwt, lane, nxt, slice + ((k + 1) & 1) * (PD_STAGE + 32));
         pd_load_offsets(a, k + 2 < PD_TILES ? wt + 2 : nwt, nwt, lane, nn);
         pd_wait<1>();  // everything but the newest group, i.e. tile k, has landed
         __syncwarp();

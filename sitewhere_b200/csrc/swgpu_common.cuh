@@ -136,31 +136,13 @@ __device__ __forceinline__ uint64_t sw_lookback(uint64_t *tile_state, uint32_t t
     return excl;
 }
 
-// Warp-granular form: a tile is the 32 lanes of one warp.  No block barrier is involved, so warps
-// of a CTA proceed independently (a slow record or a long look-back stalls one warp, not eight).
-// Returns this lane's global exclusive offset; *tile_total_out = the warp's total.
-__device__ __forceinline__ uint64_t sw_warp_ordered_offset(uint32_t count, uint64_t *tile_state, uint32_t wtile,
-                                                           uint64_t *tile_total_out) {
-    const uint32_t lane = threadIdx.x & 31;
-    uint32_t inc = count;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t t = __shfl_up_sync(SW_FULL, inc, o);
-        if (lane >= (uint32_t)o) inc += t;
-    }
-    const uint64_t total = __shfl_sync(SW_FULL, inc, 31);
-    const uint64_t base = sw_lookback(tile_state, wtile, total);
-    *tile_total_out = total;
-    return base + (uint64_t)(inc - count);
-}
-
 // Block-wide exclusive scan of one uint32 per thread + ordered global base through look-back.
 // Returns (global exclusive prefix for this thread); *block_total_out gets the tile total.
 // smem: needs THREADS/32 + 2 uint64 words.
 template <int THREADS>
 __device__ __forceinline__ uint64_t sw_block_ordered_offset(uint32_t count, uint64_t *tile_state,
                                                             uint32_t tile, uint64_t *s_warp /*[THREADS/32+2]*/,
-                                                            uint64_t *tile_total_out, bool dbg_skip = false) {
+                                                            uint64_t *tile_total_out) {
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t inc = count;
 #pragma unroll
@@ -180,7 +162,7 @@ __device__ __forceinline__ uint64_t sw_block_ordered_offset(uint32_t count, uint
             if (lane >= (uint32_t)o) winc += t;
         }
         uint64_t total = __shfl_sync(SW_FULL, winc, NW - 1);
-        uint64_t base = dbg_skip ? (uint64_t)tile * THREADS : sw_lookback(tile_state, tile, total);
+        uint64_t base = sw_lookback(tile_state, tile, total);
         if (lane < NW) s_warp[lane] = winc - w;  // exclusive warp offsets
         if (lane == 0) {
             s_warp[NW] = base;

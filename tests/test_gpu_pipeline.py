@@ -95,3 +95,38 @@ def test_empty_batch(ctx):
     ctx.set_zones(*S.rect_zones(2))
     cols, status, first_row, n_rows, pairs = ctx.decode_zone_test("pb", np.zeros(0, np.uint8), np.zeros(1, np.uint64))
     assert n_rows == 0 and pairs.shape[0] == 0 and first_row.tolist() == [0]
+
+
+def test_small_batch_path(ctx):
+    """batches of up to 16,384 records with the chunk size left to the library go through one staging block each
+    way: same results as the ring, for both formats, with failed records, a subset of columns, a batch whose
+    fan-out does not fit the block (falls back to the ring) and one whose alerts exceed the caller's buffer"""
+    zones = S.star_zones(8, cond_mode="alternate")
+    good, goff, _ = S.pb_mixed(3000, 200, seed=31, zones=zones)
+    raw = good.tobytes()
+    recs = [raw[int(goff[i]): int(goff[i + 1])] for i in range(3000)]
+    rng = np.random.default_rng(7)
+    for k, c in enumerate(pb_cases.cases()):
+        recs.insert(int(rng.integers(0, len(recs))), c[1])
+    data, rec_off = S.pack_records(recs)
+    check(ctx, "pb", data, rec_off, zones, chunk=0)                     # small block (alerts retried with a larger buffer)
+    check(ctx, "pb", data, rec_off, zones, chunk=1000)                  # ring, for comparison
+    recs.insert(500, S.pb_measurements_record("fan", [("m%03d" % k, float(k)) for k in range(5000)], date=5))
+    data, rec_off = S.pack_records(recs)
+    check(ctx, "pb", data, rec_off, zones, chunk=0)                     # 5,000 rows from one record: does not fit the block
+    jrecs = [c[1] for c in json_cases.cases()]
+    lon, lat = S.locations_for_zones(800, *zones[:3], seed=15, boundary_rate=0.05)
+    for i in range(800):
+        jrecs.insert(int(rng.integers(0, len(jrecs))),
+                     S.json_location(S.token_str(i % 50), repr(float(lat[i])), repr(float(lon[i])), "1.0", S.EVENT_DATE_BASE + i))
+    data, rec_off = S.pack_records(jrecs)
+    check(ctx, "json", data, rec_off, zones, chunk=0)
+    # column subset + no status / first_row
+    ctx.set_zones(*zones)
+    names = ["meta", "v1"]
+    p_cols = pinned_cols(len(jrecs), names)
+    cols, status, first_row, n_rows, pairs = ctx.decode_zone_test("json", data, rec_off, p_cols, None, None, None)
+    ocols, _, _, ototal = oracle.decode_json(data, rec_off)
+    assert n_rows == ototal
+    for nm in names:
+        assert np.array_equal(getattr(cols, nm)[:ototal].view(np.uint64), getattr(ocols, nm)[:ototal].view(np.uint64)), nm
