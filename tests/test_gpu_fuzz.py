@@ -110,3 +110,46 @@ def test_zone_lattice_polygons(ctx):
         got = ctx.zone_test(lon, lat, max_pairs=n * (T + 1))
         want, total = oracle.zone_test(*zones, lon, lat)
         assert got.shape[0] == total and np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("fmt", ["pb", "json"])
+def test_every_base_alignment_and_offset_origin(ctx, fmt):
+    """device-resident decode with the payload pointer at every alignment mod 16, record offsets that do not
+    start at zero, and a batch size that leaves a ragged last warp tile: the staging copies work on
+    16-byte-aligned windows around the records and must neither miss bytes nor leave their buffer"""
+    import torch
+    import oracle
+    import sitewhere_b200 as sw
+    dev = torch.device("cuda", 0)
+    if fmt == "pb":
+        data, rec_off, _ = S.pb_mixed(4999, 300, seed=55)
+        recs = _records(data, rec_off) + [bytes(c[1]) for c in pb_cases.cases()]
+    else:
+        d1, o1, _ = S.json_measurements(2999, 100, seed=56)
+        recs = _records(d1, o1) + [bytes(c[1]) for c in json_cases.cases()]
+    data, rec_off = S.pack_records(recs)
+    n = len(recs)
+    ocols, ostatus, ofirst, ototal = getattr(oracle, "decode_" + fmt)(data, rec_off)
+    st = torch.cuda.ExternalStream(ctx.stream)
+    for shift in range(0, 16):
+        origin = 1000 + 7 * shift                       # rec_off[0]: the batch is a window of a larger buffer
+        with torch.cuda.stream(st):
+            buf = torch.zeros(origin + shift + data.shape[0] + 256, dtype=torch.uint8, device=dev)
+            buf[origin + shift: origin + shift + data.shape[0]].copy_(torch.from_numpy(data))
+            d_off = torch.from_numpy((rec_off + np.uint64(origin)).view(np.int64)).to(dev)
+            cols = sw.DeviceCols(ototal + 8, dev, optional=True)
+            d_status = torch.empty(n, dtype=torch.uint8, device=dev)
+            d_first = torch.empty(n + 1, dtype=torch.int32, device=dev)
+            d_nrows = torch.zeros(1, dtype=torch.int32, device=dev)
+            getattr(ctx, "decode_%s_dev" % fmt)(buf[shift:], d_off, n, cols, d_status, d_first, d_nrows)
+        ctx.sync()
+        assert int(d_nrows.item()) == ototal
+        assert np.array_equal(d_status.cpu().numpy(), ostatus[:n])
+        assert np.array_equal(d_first.cpu().numpy().view(np.uint32), ofirst)
+        for name in ("meta", "token_hash", "name_hash", "event_date", "v0", "v1", "v2"):
+            g = getattr(cols, name)[:ototal].cpu().numpy().view(np.uint64)
+            assert np.array_equal(g, getattr(ocols, name)[:ototal].view(np.uint64)), (shift, name)
+        # spans are offsets into the record: the same whatever the window
+        for name in ("token_span", "name_span"):
+            g = getattr(cols, name)[:ototal].cpu().numpy().view(np.uint64)
+            assert np.array_equal(g, getattr(ocols, name)[:ototal].view(np.uint64)), (shift, name)
