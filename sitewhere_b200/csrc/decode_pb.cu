@@ -600,20 +600,35 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_kernel(PbArgs a) {
 
 // ---- dense pass, pipelined.  Same work per warp-tile (32 records) as pb_decode_tile<true>, but a warp goes
 // through PD_TILES consecutive tiles with the NEXT tile's payload already on its way into the other half
-// of its shared-memory slice (cp.async, 16 bytes per lane per step) and the offsets of the tile after that
+// of its shared-memory slice (one TMA bulk copy per tile, completion on an mbarrier) and the offsets of the tile after that
 // already requested, so the two serial round trips at the head of a tile (offsets, then payload: half of
 // the stall samples of the one-tile-per-warp kernel) are paid once per warp instead of once per tile.
 #define PD_TILES 4
 #define PD_STAGE 3072  // bytes staged per warp tile (32 records of up to 96 B on average); larger tiles read global memory
 
-__device__ __forceinline__ void pd_cp_async16(uint8_t *dst_smem, const void *src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src)
+// One bulk copy (TMA unit, `cp.async.bulk`: SASS UBLKCP) per tile, issued by one lane, completion counted
+// in bytes on an mbarrier in shared memory: no per-lane copy loop, no registers or LSU slots spent on staging.
+__device__ __forceinline__ uint32_t pd_saddr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void pd_bar_init(uint64_t *bar) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(pd_saddr(bar)) : "memory");
+}
+__device__ __forceinline__ void pd_bulk_load(uint8_t *dst_smem, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pd_saddr(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     pd_saddr(dst_smem)),
+                 "l"(src), "r"(bytes), "r"(pd_saddr(bar))
                  : "memory");
 }
-__device__ __forceinline__ void pd_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void pd_wait() {
-    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+__device__ __forceinline__ void pd_bar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; spin++) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(pd_saddr(bar)), "r"(parity)
+            : "memory");
+        if (spin > (1u << 26)) __trap();  // a copy that never lands is a bug: fail loudly instead of hanging
+    }
 }
 
 // A tile in flight is just this lane's record offsets; everything else (record count, first byte, alignment
@@ -648,53 +663,56 @@ __device__ __forceinline__ PdGeom pd_geom(const PbArgs &a, uint32_t wt, uint32_t
     g.staged = span <= PD_STAGE;
     return g;
 }
-// request the tile's bytes (needs the offsets): one commit group per tile, possibly empty
-__device__ __forceinline__ void pd_issue(const PbArgs &a, uint32_t wt, uint32_t nwt, uint32_t lane, const PdTile &t,
-                                         uint8_t *buf) {
+// request the tile's bytes (needs the offsets); true if a copy is now in flight on `bar`
+__device__ __forceinline__ bool pd_issue(const PbArgs &a, uint32_t wt, uint32_t nwt, uint32_t lane, const PdTile &t,
+                                         uint8_t *buf, uint64_t *bar) {
     uint64_t span;
     const PdGeom g = pd_geom(a, wt, nwt, t, span);
-    if (g.staged && g.nrec) {
+    const bool go = g.staged && g.nrec;
+    if (go && lane == 0) {
         const uint8_t *src = a.bytes + g.b0 - g.lead;
-        const uint32_t nvec = (uint32_t)((span + 15) >> 4);
-#ifdef SWGPU_DEBUG_BOUNDS
-        {
-            const uint8_t *lo = a.bytes + __ldg(a.rec_off) - 16, *hi = a.bytes + __ldg(a.rec_off + a.n) + 64;
-            if (lane == 0 && (src < lo || src + 16 * (size_t)nvec > hi || nvec > (PD_STAGE + 16) / 16))
-                printf("pd_issue OOB: wt %u nrec %u b0 %llu span %llu lead %u nvec %u src-lo %lld hi-end %lld\n", wt, g.nrec,
-                       (unsigned long long)g.b0, (unsigned long long)span, g.lead, nvec, (long long)(src - lo),
-                       (long long)(hi - (src + 16 * (size_t)nvec)));
-        }
-#endif
-        for (uint32_t i = lane; i < nvec; i += 32) pd_cp_async16(buf + 16 * i, src + 16 * i);
+        pd_bulk_load(buf, src, (uint32_t)((span + 15) >> 4) << 4, bar);
     }
-    pd_commit();
+    return go;
 }
 
 __global__ void __launch_bounds__(PB_THREADS) pb_decode_dense_kernel(PbArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];  // PB_WARPS * 2 * (PD_STAGE + 32)
+    __shared__ __align__(8) uint64_t s_bar[PB_WARPS][2];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t nwt = (a.n + 31u) / 32u;  // warp tiles in the batch
     const uint32_t first = (blockIdx.x * PB_WARPS + warp) * PD_TILES;
     if (first >= nwt) return;
     uint8_t *const slice = smem + (size_t)(warp * 2) * (PD_STAGE + 32);
+    uint64_t *const bar = s_bar[warp];
+    if (lane == 0) {
+        pd_bar_init(&bar[0]);
+        pd_bar_init(&bar[1]);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
     const uint64_t row_base = a.row_base ? (uint64_t)__ldg(a.row_base) : 0ull;  // rows of earlier chunks
     PdTile cur, nxt, nn;
     pd_load_offsets(a, first, nwt, lane, cur);
     pd_load_offsets(a, first + 1, nwt, lane, nxt);
-    pd_issue(a, first, nwt, lane, cur, slice);
+    uint32_t parity = 0;                                           // bit b: phase of buffer b's barrier
+    bool cur_copy = pd_issue(a, first, nwt, lane, cur, slice, &bar[0]);
 #pragma unroll 1
     for (uint32_t k = 0; k < PD_TILES; k++) {
         const uint32_t wt = first + k;
         if (wt >= nwt) break;  // past the end of the batch
-        // tile k+1: bytes on their way; tile k+2: offsets requested
-        // (the warp's last tile has no successor of its own: an empty group keeps the wait below uniform)
-        pd_issue(a, k + 1 < PD_TILES ? wt + 1 : nwt, nwt, lane, nxt, slice + ((k + 1) & 1) * (PD_STAGE + 32));
+        // tile k+1: bytes on their way (the warp's last tile has no successor of its own); tile k+2: offsets requested
+        const uint32_t b = k & 1;
+        const bool nxt_copy = pd_issue(a, k + 1 < PD_TILES ? wt + 1 : nwt, nwt, lane, nxt,
+                                       slice + (b ^ 1) * (PD_STAGE + 32), &bar[b ^ 1]);
         pd_load_offsets(a, k + 2 < PD_TILES ? wt + 2 : nwt, nwt, lane, nn);
-        pd_wait<1>();  // everything but the newest group, i.e. tile k, has landed
-        __syncwarp();
+        if (cur_copy) {
+            pd_bar_wait(&bar[b], (parity >> b) & 1u);
+            parity ^= 1u << b;
+        }
         uint64_t span;
         const PdGeom g = pd_geom(a, wt, nwt, cur, span);
-        const uint8_t *ws = slice + (k & 1) * (PD_STAGE + 32);
+        const uint8_t *ws = slice + b * (PD_STAGE + 32);
         if (lane < g.nrec) {
             PbOut o;
             o.count = 0;
@@ -722,11 +740,11 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_dense_kernel(PbArgs a) {
                 if (a.row_next) *a.row_next = (uint32_t)(row_base + a.n);
             }
         }
-        __syncwarp();  // the buffer is refilled two tiles from now
+        __syncwarp();  // every lane is done reading this buffer: it is refilled two tiles from now
         cur = nxt;
         nxt = nn;
+        cur_copy = nxt_copy;
     }
-    pd_wait<0>();
 }
 
 static int check_cols(swgpu_ctx *ctx, const swgpu_decoded_cols *c) {
