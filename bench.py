@@ -430,17 +430,17 @@ def run_ours(args):
         bytes_zone = 24 * n + 8 * n_pairs
         gbs_dec = bytes_dec / (ms_dec * 1e-3) / 1e9
         gbs_zone = bytes_zone / (ms_zone * 1e-3) / 1e9
-        # The decode stage is pb_decode_kernel<dense> plus the ordered pass that returns at once (~3 us); the zone
+        # The decode stage is pb_decode_dense_kernel plus the ordered pass that returns at once (~3 us); the zone
         # stage is three launches of which zone_count_kernel is the largest (84 % of the stage in the committed
-        # launch list, profiles/r01c_launches.csv).  Dominant kernel = the longer single launch.
+        # launch list, profiles/r01d_launches.csv).  Dominant kernel = the longer single launch.
         ZONE_COUNT_SHARE = 0.843
         dom = "pb_decode_kernel" if ms_dec >= ZONE_COUNT_SHARE * ms_zone else "zone_test (zone_count_kernel + zone_scan_mc_kernel + zone_emit_kernel)"
         ach = gbs_dec if dom == "pb_decode_kernel" else gbs_zone
         # DRAM bytes per launch from the committed `ncu --set full` capture of this very workload
-        # (profiles/r01c_ncu_full_summary.md): decode 730.7 + 712.3 MB; zone 258.8 + 67.1 (count) + 0.3 (scan) + 80.4 + 7.4 (emit) MB
+        # (profiles/r01d_ncu_full_summary.md): decode 710.3 + 733.3 MB; zone 258.6 + 67.1 (count) + 0.3 (scan) + 80.4 + 7.4 (emit) MB
         traffic = None
         if n == 10_000_000:
-            traffic = 1.4429e9 if dom == "pb_decode_kernel" else 414.0e6
+            traffic = 1.4435e9 if dom == "pb_decode_kernel" else 413.8e6
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_all / args.steps, "higher_is_better": True,
@@ -459,7 +459,7 @@ def run_ours(args):
             "gpu_launches": 5 * args.steps,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
-                         "note": "pb_decode_kernel<dense> is the longest launch of the step and is HBM-bound; the zone test "
+                         "note": "pb_decode_dense_kernel is the longest launch of the step and is HBM-bound; the zone test "
                                  "(kernels.zone_test_kernel) is bound by instruction issue at ~17 active lanes per "
                                  "warp instruction on an L2-resident table, not by HBM"},
             "kernels": {"pb_decode_kernel": {"ms": ms_dec, "algorithmic_bytes": bytes_dec, "GBps": gbs_dec,
