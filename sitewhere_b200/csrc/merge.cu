@@ -5,10 +5,14 @@
 //  lastAlertEventIds[type] := id).
 //
 // Sort-free: the sequential "later event overwrites" is, per key, an argmax over the arrival
-// sequence number.  Pass 1 finds/claims the key's slot in an open-addressing table (hash picks the
-// bucket, the key BYTES decide equality) and does atomicMax(slot.best, seq+1); pass 2 lets exactly
-// the winner of each key write its payload (event id, date, value).  HBM-bound: one 64-byte slot and
-// one arena key per event, random access.
+// sequence number.  A row finds/claims its key's slot in an open-addressing table (hash picks the
+// bucket, the key BYTES decide equality), does atomicMax(slot.best, seq+1) and, if it raised the
+// maximum, writes its payload (event id, date, value) at once; the rare rows that raised a maximum set
+// by an older row of the same launch go on a fix-up list that a second, tiny kernel replays.  Rows
+// are taken newest first, so most older rows of a key lose their atomicMax and leave.  HBM-bound: one
+// 64-byte slot and one arena key per event, random access.
+#include <algorithm>
+
 #include "swgpu_common.cuh"
 
 #define MG_THREADS 256
@@ -27,6 +31,7 @@ static_assert(sizeof(MgSlot) == 64, "MgSlot layout");
 
 struct MgCounters {  // device
     unsigned long long n_keys, arena_top, table_full, arena_full, key_too_long;
+    unsigned long long n_fix;  // rows on this launch's fix-up list (reset by the launcher)
 };
 
 struct MgState {
@@ -37,7 +42,7 @@ struct MgState {
     MgCounters *ctr = nullptr;
     uint64_t keys_upper = 0;   // host upper bound on live keys
     uint64_t arena_upper = 0;  // host upper bound on arena bytes
-    swgpu_ctx::Buf slot_idx;   // per-row slot index between pass 1 and 2
+    swgpu_ctx::Buf fix;        // fix-up list of the current launch (row + slot per entry)
 };
 
 __host__ __device__ __forceinline__ uint64_t mg_mix(uint64_t th, uint64_t nh, uint32_t kindbyte) {
@@ -65,10 +70,10 @@ struct MgArgs {
     const uint32_t *n_rows_dev;
     uint64_t seq_base;
     const uint64_t *id_hi, *id_lo;
-    uint64_t *slot_idx;
+    uint32_t *fix_row;   // fix-up list: row ...
+    uint64_t *fix_slot;  // ... and its slot
 };
 
-#define MG_NOSLOT 0xffffffffffffffffull
 
 // Keys live in the arena as 8-byte words so that equality is a handful of 64-bit compares:
 //   word 0            token length | name length << 16 | kind byte << 32
@@ -118,7 +123,6 @@ __global__ void __launch_bounds__(MG_THREADS) merge_upsert_kernel(MgArgs a) {
     // newest rows first: CTAs start roughly in index order, so for a key with several rows in the batch the
     // winner tends to arrive first and the older rows lose their atomicMax at once (no publish work for them)
     const uint32_t r = n_live - 1 - ridx;
-    a.slot_idx[r] = MG_NOSLOT;
     const uint64_t m = __ldg(a.meta + r);
     const uint32_t kind = SWGPU_META_KIND(m), fl = SWGPU_META_FLAGS(m);
     if (kind > SWGPU_KIND_ALERT || (fl & SWGPU_F_NULL_TOKEN)) return;
@@ -149,6 +153,10 @@ __global__ void __launch_bounds__(MG_THREADS) merge_upsert_kernel(MgArgs a) {
 #pragma unroll
         for (uint32_t i = 0; i < 2; i++) kw[5 + i] = i < nw ? mg_payload_word(name + 8 * i, min(8u, nl - 8 * i)) : 0ull;
     }
+    // the payload this row would store (most rows do: one row per key per batch is the common case)
+    const uint64_t v_hi = __ldg(a.id_hi + r), v_lo = __ldg(a.id_lo + r);
+    const int64_t v_date = __ldg(a.event_date + r);
+    const double v_val = __ldg(a.v0 + r);
     for (uint64_t probes = 0; probes <= a.mask; probes++, s = (s + 1) & a.mask) {
         MgSlot *sl = a.slots + s;
         uint64_t tag = mg_ld_acquire_u64(&sl->tag);  // acquire: a published tag makes the key words visible
@@ -209,24 +217,41 @@ __global__ void __launch_bounds__(MG_THREADS) merge_upsert_kernel(MgArgs a) {
             return;
         }
     }
+    // ---- last writer wins.  `best` = seq + 1 of the newest event seen for the key; the row that raises it owns
+    // the slot's payload at that moment and writes it here, in the same pass.  Two rows of one launch can both
+    // raise it (an older row got there first, then a newer one): their payload stores may land in either order,
+    // so the newer row — which sees a previous value from this same launch — also puts itself on a fix-up
+    // list, and a second, tiny kernel lets the final winner of each such key write once more after every store
+    // of this kernel has landed.  With the newest rows first this is rare (same-key rows must be in flight
+    // together): the list is a few percent of the rows at most, against a second pass over all of them.
     const unsigned long long mine = (unsigned long long)(a.seq_base + r + 1);
     const unsigned long long old = atomicMax((unsigned long long *)&a.slots[s].best, mine);
-    // a row that did not raise the maximum can never be the final winner: it needs no publish step
-    a.slot_idx[r] = old < mine ? s : MG_NOSLOT;
+    if (old >= mine) return;  // an event at least as new is already there (also: replay of the same batch)
+    MgSlot *sl = a.slots + s;
+    sl->id_hi = v_hi;
+    sl->id_lo = v_lo;
+    sl->date = v_date;
+    sl->value = v_val;
+    if (old > a.seq_base) {  // the previous value was set by an older row of this launch
+        const unsigned long long k = atomicAdd(&a.ctr->n_fix, 1ull);
+        a.fix_row[k] = r;
+        a.fix_slot[k] = s;
+    }
 }
 
-__global__ void __launch_bounds__(MG_THREADS) merge_publish_kernel(MgArgs a) {
-    const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n_rows) : a.n_rows;
-    const uint32_t r = blockIdx.x * MG_THREADS + threadIdx.x;
-    if (r >= n_live) return;
-    const uint64_t s = a.slot_idx[r];
-    if (s == MG_NOSLOT) return;
-    MgSlot *sl = a.slots + s;
-    if (sl->best != a.seq_base + r + 1) return;  // a later event of this key won
-    sl->id_hi = __ldg(a.id_hi + r);
-    sl->id_lo = __ldg(a.id_lo + r);
-    sl->date = __ldg(a.event_date + r);
-    sl->value = __ldg(a.v0 + r);
+// second pass, over the fix-up list only
+__global__ void __launch_bounds__(MG_THREADS) merge_fixup_kernel(MgArgs a) {
+    const unsigned long long n = a.ctr->n_fix;
+    for (unsigned long long k = (unsigned long long)blockIdx.x * MG_THREADS + threadIdx.x; k < n;
+         k += (unsigned long long)gridDim.x * MG_THREADS) {
+        const uint32_t r = a.fix_row[k];
+        MgSlot *sl = a.slots + a.fix_slot[k];
+        if (sl->best != a.seq_base + r + 1) continue;  // a later event of this key won
+        sl->id_hi = __ldg(a.id_hi + r);
+        sl->id_lo = __ldg(a.id_lo + r);
+        sl->date = __ldg(a.event_date + r);
+        sl->value = __ldg(a.v0 + r);
+    }
 }
 
 // re-insert live slots into a larger table (keys are distinct: no byte compare needed)
@@ -257,7 +282,7 @@ void sw_state_free(swgpu_ctx *ctx) {
     if (st->slots) cudaFree(st->slots);
     if (st->arena) cudaFree(st->arena);
     if (st->ctr) cudaFree(st->ctr);
-    if (st->slot_idx.p) cudaFree(st->slot_idx.p);
+    if (st->fix.p) cudaFree(st->fix.p);
     delete st;
     ctx->state = nullptr;
 }
@@ -369,7 +394,7 @@ extern "C" int32_t swgpu_merge_dev(swgpu_ctx *ctx, const uint8_t *bytes, const u
         st->keys_upper = ku;
         st->arena_upper = au;
     }
-    if (int rc = sw_ensure(ctx, st->slot_idx, (size_t)n_rows * 8)) return rc;
+    if (int rc = sw_ensure(ctx, st->fix, (size_t)n_rows * 12 + 64)) return rc;
     MgArgs a;
     a.slots = st->slots;
     a.mask = st->cap - 1;
@@ -390,11 +415,13 @@ extern "C" int32_t swgpu_merge_dev(swgpu_ctx *ctx, const uint8_t *bytes, const u
     a.seq_base = seq_base;
     a.id_hi = id_hi;
     a.id_lo = id_lo;
-    a.slot_idx = (uint64_t *)st->slot_idx.p;
+    a.fix_slot = (uint64_t *)st->fix.p;
+    a.fix_row = (uint32_t *)((uint8_t *)st->fix.p + (((size_t)n_rows * 8 + 63) & ~(size_t)63));
     const unsigned nb = (n_rows + MG_THREADS - 1) / MG_THREADS;
+    SW_CUDA(ctx, cudaMemsetAsync(&st->ctr->n_fix, 0, sizeof(unsigned long long), ctx->stream));
     merge_upsert_kernel<<<nb, MG_THREADS, 0, ctx->stream>>>(a);
     SW_CUDA(ctx, cudaGetLastError());
-    merge_publish_kernel<<<nb, MG_THREADS, 0, ctx->stream>>>(a);
+    merge_fixup_kernel<<<std::min<unsigned>(nb, (unsigned)ctx->sm_count * 4u), MG_THREADS, 0, ctx->stream>>>(a);
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
 }
