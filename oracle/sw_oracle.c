@@ -75,14 +75,20 @@ uint32_t orc_murmur2(const uint8_t *data, uint32_t len) {
 uint32_t orc_partition(const uint8_t *key, uint32_t len, uint32_t n_partitions) {
     return (orc_murmur2(key, len) & 0x7fffffffu) % n_partitions;
 }
-/* 64-bit row hash: low half is the Kafka hash (so a row's shard is derivable from it), high half
- * an independent FNV-1a/fmix32.  Not part of the reference; a new column of the columnar form. */
+/* 64-bit row hash: low half is the Kafka hash (so a row's shard is derivable from it); high half an
+ * independent hash over the same little-endian 4-byte words (xor, multiply, rotate per word; tail bytes and
+ * length folded in last; fmix32 finish).  Not part of the reference; a new column of the columnar form. */
+static uint32_t hash_hi_step(uint32_t f, uint32_t word) {
+    f = (f ^ word) * 0x9E3779B1u;
+    return (f << 15) | (f >> 17);
+}
 uint64_t orc_hash64(const uint8_t *data, uint32_t len) {
-    uint32_t h = 0x811c9dc5u;
-    for (uint32_t i = 0; i < len; i++) {
-        h ^= data[i];
-        h *= 0x01000193u;
-    }
+    uint32_t h = 0x811c9dc5u, i = 0, tail = 0;
+    for (; i + 4 <= len; i += 4)
+        h = hash_hi_step(h, (uint32_t)data[i] | ((uint32_t)data[i + 1] << 8) | ((uint32_t)data[i + 2] << 16) |
+                                ((uint32_t)data[i + 3] << 24));
+    for (uint32_t k = 0; i + k < len; k++) tail |= (uint32_t)data[i + k] << (8 * k);
+    h = hash_hi_step(h, tail ^ (len << 24));
     h ^= h >> 16;
     h *= 0x85ebca6bu;
     h ^= h >> 13;

@@ -567,15 +567,12 @@ extern "C" int32_t swgpu_state_snapshot(swgpu_ctx *ctx, uint64_t max_keys, uint6
     return SWGPU_OK;
 }
 
-static uint64_t host_hash64(const uint8_t *d, uint32_t len) {
-    uint32_t f = 0x811c9dc5u;
-    for (uint32_t i = 0; i < len; i++) f = (f ^ d[i]) * 0x01000193u;
-    f ^= f >> 16;
-    f *= 0x85ebca6bu;
-    f ^= f >> 13;
-    f *= 0xc2b2ae35u;
-    f ^= f >> 16;
-    return ((uint64_t)f << 32) | swgpu_murmur2(d, len);
+static uint64_t host_hash64(const uint8_t *d, uint32_t len) {  // sw_hash64 on the host
+    uint32_t f = 0x811c9dc5u, i = 0, tail = 0;
+    for (; i + 4 <= len; i += 4)
+        f = sw_hash_hi_step(f, (uint32_t)d[i] | ((uint32_t)d[i + 1] << 8) | ((uint32_t)d[i + 2] << 16) | ((uint32_t)d[i + 3] << 24));
+    for (uint32_t k = 0; i + k < len; k++) tail |= (uint32_t)d[i + k] << (8 * k);
+    return ((uint64_t)sw_hash_hi_final(f, tail, len) << 32) | swgpu_murmur2(d, len);
 }
 
 extern "C" int32_t swgpu_state_restore(swgpu_ctx *ctx, const swgpu_state_rows *in, uint64_t n_keys) {

@@ -175,7 +175,24 @@ __device__ __forceinline__ uint64_t sw_block_ordered_offset(uint32_t count, uint
     return r;
 }
 
-// ---- hashes (bit-identical to Kafka Utils.murmur2 in the low half) ---------------------------------
+// ---- hashes ------------------------------------------------------------------------------------------
+// 64-bit row hash.  Low half: Kafka Utils.murmur2 (bit-identical: a row's shard is derivable from it).
+// High half: an independent hash over the same little-endian 4-byte words murmur2 consumes (xor, multiply,
+// rotate per word; the 1-3 tail bytes and the length folded in last), finished with fmix32.  One pass over
+// the bytes feeds both; the high half is this repository's own definition (oracle: orc_hash64).
+__host__ __device__ __forceinline__ uint32_t sw_hash_hi_step(uint32_t f, uint32_t word) {
+    f = (f ^ word) * 0x9E3779B1u;
+    return (f << 15) | (f >> 17);
+}
+__host__ __device__ __forceinline__ uint32_t sw_hash_hi_final(uint32_t f, uint32_t tail, uint32_t len) {
+    f = sw_hash_hi_step(f, tail ^ (len << 24));
+    f ^= f >> 16;
+    f *= 0x85ebca6bu;
+    f ^= f >> 13;
+    f *= 0xc2b2ae35u;
+    f ^= f >> 16;
+    return f;
+}
 template <typename Rd>
 __device__ __forceinline__ uint64_t sw_hash64(const Rd &rd, uint32_t off, uint32_t len) {
     const uint32_t m = 0x5bd1e995u;
@@ -188,10 +205,7 @@ __device__ __forceinline__ uint64_t sw_hash64(const Rd &rd, uint32_t off, uint32
 #pragma unroll
         for (int half = 0; half < 2; half++) {
             uint32_t k = (uint32_t)(v >> (32 * half));
-            f = (f ^ (k & 0xff)) * 0x01000193u;
-            f = (f ^ ((k >> 8) & 0xff)) * 0x01000193u;
-            f = (f ^ ((k >> 16) & 0xff)) * 0x01000193u;
-            f = (f ^ (k >> 24)) * 0x01000193u;
+            f = sw_hash_hi_step(f, k);
             k *= m;
             k ^= k >> 24;
             k *= m;
@@ -202,37 +216,27 @@ __device__ __forceinline__ uint64_t sw_hash64(const Rd &rd, uint32_t off, uint32
     for (; i + 4 <= len; i += 4) {
         uint32_t b0 = rd.byte(off + i), b1 = rd.byte(off + i + 1), b2 = rd.byte(off + i + 2),
                  b3 = rd.byte(off + i + 3);
-        f = (f ^ b0) * 0x01000193u;
-        f = (f ^ b1) * 0x01000193u;
-        f = (f ^ b2) * 0x01000193u;
-        f = (f ^ b3) * 0x01000193u;
         uint32_t k = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+        f = sw_hash_hi_step(f, k);
         k *= m;
         k ^= k >> 24;
         k *= m;
         h *= m;
         h ^= k;
     }
-    uint32_t rem = len - i;
+    uint32_t rem = len - i, tail = 0;
     if (rem) {
         uint32_t b0 = rd.byte(off + i);
         uint32_t b1 = rem > 1 ? rd.byte(off + i + 1) : 0;
         uint32_t b2 = rem > 2 ? rd.byte(off + i + 2) : 0;
-        f = (f ^ b0) * 0x01000193u;
-        if (rem > 1) f = (f ^ b1) * 0x01000193u;
-        if (rem > 2) f = (f ^ b2) * 0x01000193u;
-        h ^= (b2 << 16) | (b1 << 8) | b0;
+        tail = (b2 << 16) | (b1 << 8) | b0;
+        h ^= tail;
         h *= m;
     }
     h ^= h >> 13;
     h *= m;
     h ^= h >> 15;
-    f ^= f >> 16;
-    f *= 0x85ebca6bu;
-    f ^= f >> 13;
-    f *= 0xc2b2ae35u;
-    f ^= f >> 16;
-    return ((uint64_t)f << 32) | h;
+    return ((uint64_t)sw_hash_hi_final(f, tail, len) << 32) | h;
 }
 
 // ---- byte readers: the same parser runs over a shared-memory staged record or over global memory ----
