@@ -466,6 +466,9 @@ def run_ours(args):
                                              "frac_hbm": gbs_dec / peak, "events_per_s": n / (ms_dec * 1e-3)},
                         "zone_test_kernel": {"ms": ms_zone, "algorithmic_bytes": bytes_zone, "GBps": gbs_zone,
                                              "frac_hbm": gbs_zone / peak, "bound": "instruction issue / divergence (zone table in L2)",
+                                             # from the committed ncu capture of this workload (profiles/r01d_ncu_full_summary.md)
+                                             "ncu": {"zone_count_kernel": {"fp64_pipe_pct": 23.6, "issue_active_pct": 56.0,
+                                                                           "active_lanes_per_inst": 17.3}},
                                              "locations_per_s": n / (ms_zone * 1e-3)}},
             "clocks": clocks,
         }
