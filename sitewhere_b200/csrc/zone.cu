@@ -915,58 +915,59 @@ __global__ void __launch_bounds__(ZS_THREADS) zone_scan_mc_kernel(const uint64_t
     if (i == ntiles - 1) *total_out = excl + v;
 }
 
-// Each thread places the pairs of ZE_PER consecutive locations (one 256-bit load of their parked words);
-// a CTA covers ZE_PER tiles, two warps per tile.
-#define ZE_PER 4
+// Each thread places the pairs of ZE_PER = 8 consecutive locations (two 256-bit loads of their parked words,
+// both in flight together); a warp therefore covers exactly one 256-location tile: its offsets come from one
+// warp scan, with no shared memory and no CTA barrier.
+#define ZE_PER 8
+static_assert(ZE_PER * 32 == ZN_THREADS, "one warp of the emit kernel = one tile");
 __global__ void __launch_bounds__(ZN_THREADS) zone_emit_kernel(ZnArgs a, ZnWork w) {
-    __shared__ uint32_t s_part[ZN_THREADS / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint64_t i0 = ((uint64_t)blockIdx.x * ZN_THREADS + tid) * ZE_PER;
+    const uint64_t tile = (uint64_t)blockIdx.x * (ZN_THREADS / 32) + warp;
+    const uint64_t i0 = (tile * 32 + lane) * ZE_PER;
+    if (tile * ZN_THREADS >= a.n) return;  // whole warp
     uint64_t parked[ZE_PER];
     if (i0 + ZE_PER <= a.n) {
-        const ZnD4 v = zn_ld256(w.park + i0);
-        parked[0] = (uint64_t)__double_as_longlong(v.x);
-        parked[1] = (uint64_t)__double_as_longlong(v.y);
-        parked[2] = (uint64_t)__double_as_longlong(v.z);
-        parked[3] = (uint64_t)__double_as_longlong(v.w);
+        const ZnD4 v0 = zn_ld256(w.park + i0), v1 = zn_ld256(w.park + i0 + 4);
+        parked[0] = (uint64_t)__double_as_longlong(v0.x);
+        parked[1] = (uint64_t)__double_as_longlong(v0.y);
+        parked[2] = (uint64_t)__double_as_longlong(v0.z);
+        parked[3] = (uint64_t)__double_as_longlong(v0.w);
+        parked[4] = (uint64_t)__double_as_longlong(v1.x);
+        parked[5] = (uint64_t)__double_as_longlong(v1.y);
+        parked[6] = (uint64_t)__double_as_longlong(v1.z);
+        parked[7] = (uint64_t)__double_as_longlong(v1.w);
     } else {
 #pragma unroll
         for (int j = 0; j < ZE_PER; j++) parked[j] = i0 + j < a.n ? w.park[i0 + j] : 0;
     }
-    uint32_t count[ZE_PER], tsum = 0;
+    uint32_t tsum = 0;
 #pragma unroll
-    for (int j = 0; j < ZE_PER; j++) {
-        count[j] = (parked[j] & 3u) == 3u ? (uint32_t)(parked[j] >> 2) : (uint32_t)(parked[j] & 3u);
-        tsum += count[j];
-    }
+    for (int j = 0; j < ZE_PER; j++) tsum += (parked[j] & 3u) == 3u ? (uint32_t)(parked[j] >> 2) : (uint32_t)(parked[j] & 3u);
     uint32_t inc = tsum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         uint32_t t = __shfl_up_sync(SW_FULL, inc, o);
         if (lane >= (uint32_t)o) inc += t;
     }
-    if (lane == 31) s_part[warp] = inc;
-    __syncthreads();
     if (!tsum) return;
-    // a tile is ZN_THREADS locations = 2 warps of this kernel: the odd warp continues after the even one
-    const uint32_t woff = (warp & 1u) ? s_part[warp - 1] : 0u;
-    uint64_t pos = w.tile_base[(uint64_t)blockIdx.x * ZE_PER + (warp >> 1)] + woff + (inc - tsum);
+    uint64_t pos = w.tile_base[tile] + (inc - tsum);
     const uint32_t row_base = a.row_base ? __ldg(a.row_base) : 0u;
 #pragma unroll
     for (int j = 0; j < ZE_PER; j++) {
-        if (!count[j]) continue;
+        const uint32_t count = (parked[j] & 3u) == 3u ? (uint32_t)(parked[j] >> 2) : (uint32_t)(parked[j] & 3u);
+        if (!count) continue;
         const uint32_t i = (uint32_t)i0 + j;
-        if (a.h.n_outside == 0 && count[j] <= 2) {
+        if (a.h.n_outside == 0 && count <= 2) {
             const uint64_t ev = (uint64_t)(row_base + i) << 32;
             if (pos < a.max_pairs) a.pairs[pos] = ev | ((parked[j] >> 2) & 0x7fffffffu);
-            if (count[j] == 2 && pos + 1 < a.max_pairs) a.pairs[pos + 1] = ev | (parked[j] >> 33);
+            if (count == 2 && pos + 1 < a.max_pairs) a.pairs[pos + 1] = ev | (parked[j] >> 33);
         } else {
             const uint32_t n_live = a.n_rows_dev ? min(__ldg(a.n_rows_dev), a.n) : a.n;
             ZnLoc L;
             zn_eval(a, i, n_live, L);
             zn_emit(a, i, L, pos);
         }
-        pos += count[j];
+        pos += count;
     }
 }
 
@@ -1021,7 +1022,7 @@ int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const u
     else
         zone_scan_kernel<<<1, ZS_THREADS, 0, ctx->stream>>>(w.tile_tot, w.tile_base, ntiles, n_pairs_dev);
     SW_CUDA(ctx, cudaGetLastError());
-    zone_emit_kernel<<<(ntiles + ZE_PER - 1) / ZE_PER, ZN_THREADS, 0, ctx->stream>>>(a, w);
+    zone_emit_kernel<<<(ntiles + ZN_THREADS / 32 - 1) / (ZN_THREADS / 32), ZN_THREADS, 0, ctx->stream>>>(a, w);
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
 }
