@@ -172,7 +172,9 @@ int32_t swgpu_decode_pb(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
 int32_t swgpu_decode_json(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
                           uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
                           uint32_t *first_row, uint32_t *out_rows);
-/* Device-resident variants.  `bytes` must be readable up to rec_off[n] rounded up to 16.
+/* Device-resident variants.  The payload is staged in 16-byte-aligned windows: the 16-byte block that holds
+ * byte rec_off[0] and the one that holds byte rec_off[n]-1 must be readable in full (true for any buffer
+ * from cudaMalloc; give a sub-buffer 16 bytes of slack after the last record).
  * out_rows_dev: one uint32 on the device.                                                       */
 int32_t swgpu_decode_pb_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
                             uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
