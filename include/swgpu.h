@@ -264,6 +264,15 @@ int32_t swgpu_merge_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
                         const uint32_t *n_rows_dev, uint64_t seq_base, const uint64_t *id_hi,
                         const uint64_t *id_lo);
 /* Number of live keys and bytes in the key arena.                                             */
+/* Fused host-buffer call of the device-state consumer: decode the batch and fold every decoded row into the
+ * state, rows staying on the GPU.  Replaces, for one poll() batch, DeviceStateProcessingLogic.process
+ * (DS/processing/DeviceStateProcessingLogic.java:65-67: unmarshal each record, then processDeviceStateEvent
+ * :116-160) — the same result as swgpu_decode_{pb,json} followed by swgpu_merge with seq = seq_base + row.
+ * id_hi/id_lo[n]: the persisted event id of each RECORD; a record that decodes to several rows gives all of
+ * them its id.  status[n] (may be NULL) as in swgpu_decode_*; *out_rows = rows merged (advance seq_base by it). */
+int32_t swgpu_decode_merge(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
+                           uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo, uint8_t *status,
+                           uint32_t *out_rows);
 int32_t swgpu_state_size(swgpu_ctx *ctx, uint64_t *n_keys, uint64_t *key_bytes);
 /* Snapshot (host pointers): one row per live key, in unspecified order.  key_off has n_keys+1
  * entries into key_bytes; a key is  token length (2 bytes LE) | kind byte | token bytes | name bytes.               */

@@ -6,7 +6,7 @@
  * The reference handles the batch record by record: unmarshal the enriched event, read the device's state document,
  * overwrite lastLocationEventId / lastMeasurementEventIds[name] / lastAlertEventIds[type] (+ lastInteractionDate) and
  * write the document back — one read-modify-write of the store per EVENT.  Here the whole poll() batch is folded on
- * the GPU first (swgpu_merge: per (device, kind, name) the newest event wins, exactly what the sequential loop leaves
+ * the GPU first (swgpu_decode_merge: per (device, kind, name) the newest event wins, exactly what the sequential loop leaves
  * behind), and only the winners are written: one store update per touched DEVICE per flush.
  * NOT COMPILED in this repository (no JDK in the build container).
  */
@@ -76,15 +76,11 @@ public class GpuDeviceStateProcessingLogic extends TenantEngineLifecycleComponen
 		idLo.setAtIndex(JAVA_LONG, i, id.getLeastSignificantBits());
 	    }
 	    recOff.setAtIndex(JAVA_LONG, n, off);
-	    // decode into device-resident columns, then fold: both calls are in include/swgpu.h
-	    MemorySegment cols = a.allocate(SwGpu.COLS_BYTES);
-	    MemorySegment status = a.allocate(n), firstRow = a.allocate(4L * (n + 1)), outRows = a.allocate(4);
-	    SwGpu.HostCols host = SwGpu.HostCols.allocate(a, n, cols);
-	    ctx.check((int) SwGpu.DECODE_PB.invokeExact(ctx.handle, bytes, recOff, n, n, cols, status, firstRow, outRows));
-	    int rows = outRows.get(java.lang.foreign.ValueLayout.JAVA_INT, 0);
-	    ctx.check((int) SwGpu.MERGE.invokeExact(ctx.handle, bytes, recOff, n, cols, rows, sequence, idHi, idLo));
-	    sequence += rows;
-	    host.close();
+	    // one native call: decode on the GPU and fold into the state, rows never leave the device
+	    MemorySegment status = a.allocate(n), outRows = a.allocate(4);
+	    ctx.check((int) SwGpu.DECODE_MERGE.invokeExact(ctx.handle, SwGpu.FMT_PROTOBUF, bytes, recOff, n, sequence, idHi, idLo,
+		    status, outRows));
+	    sequence += outRows.get(java.lang.foreign.ValueLayout.JAVA_INT, 0);
 	} catch (SiteWhereException e) {
 	    throw e;
 	} catch (Throwable t) {

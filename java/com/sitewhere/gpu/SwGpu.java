@@ -51,6 +51,8 @@ public final class SwGpu {
 		    ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, JAVA_INT));
     static final MethodHandle MERGE = h("swgpu_merge", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
 	    JAVA_INT, ADDRESS, JAVA_INT, JAVA_LONG, ADDRESS, ADDRESS));
+    static final MethodHandle DECODE_MERGE = h("swgpu_decode_merge", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
+	    ADDRESS, ADDRESS, JAVA_INT, JAVA_LONG, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
     static final MethodHandle STATE_SIZE = h("swgpu_state_size", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
     static final MethodHandle STATE_SNAPSHOT = h("swgpu_state_snapshot",
 	    FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG, JAVA_LONG, ADDRESS, ADDRESS));

@@ -75,6 +75,7 @@ SIGNATURES = {
     "swgpu_zone_test_noalloc_dev": (_I32, [_P, _P, _P, _P, _U32, _P, _U64, _P, _P]),
     "swgpu_state_reserve": (_I32, [_P, _U64, _U64]),
     "swgpu_merge": (_I32, [_P, _P, _P, _U32, _COLS, _U32, _U64, _P, _P]),
+    "swgpu_decode_merge": (_I32, [_P, _I32, _P, _P, _U32, _U64, _P, _P, _P, C.POINTER(_U32)]),
     "swgpu_merge_dev": (_I32, [_P, _P, _P, _U32, _COLS, _U32, _P, _U64, _P, _P]),
     "swgpu_state_size": (_I32, [_P, C.POINTER(_U64), C.POINTER(_U64)]),
     "swgpu_state_snapshot": (_I32, [_P, _U64, _U64, _ROWS, C.POINTER(_U64)]),

@@ -289,6 +289,23 @@ class Context:
         self._check(self.lib.swgpu_merge(self.h, data.ctypes.data, rec_off.ctypes.data, rec_off.shape[0] - 1,
                                          C.byref(s), cols.n, int(seq_base), id_hi.ctypes.data, id_lo.ctypes.data))
 
+    def decode_merge(self, fmt: str, data, rec_off, seq_base: int, id_hi, id_lo, status=None) -> int:
+        """swgpu_decode_merge: decode a host-resident batch and fold it into the device state in one call
+        (ids per RECORD).  Returns the number of rows merged; ``status`` (uint8[n]) is filled when given."""
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
+        id_hi = np.ascontiguousarray(id_hi, dtype=np.uint64)
+        id_lo = np.ascontiguousarray(id_lo, dtype=np.uint64)
+        n = rec_off.shape[0] - 1
+        if id_hi.shape[0] < n or id_lo.shape[0] < n:
+            raise ValueError("one event id per record is required")
+        rows = C.c_uint32()
+        self._check(self.lib.swgpu_decode_merge(
+            self.h, 1 if fmt == "json" else 0, data.ctypes.data if data.size else None, rec_off.ctypes.data, n,
+            int(seq_base), id_hi.ctypes.data, id_lo.ctypes.data, status.ctypes.data if status is not None else None,
+            C.byref(rows)))
+        return int(rows.value)
+
     def merge_dev(self, bytes_t, off_t, n_records, cols: DeviceCols, n_rows, n_rows_t, seq_base, id_hi_t, id_lo_t):
         s = cols.struct()
         self._check(self.lib.swgpu_merge_dev(self.h, bytes_t.data_ptr(), off_t.data_ptr(), int(n_records), C.byref(s),
@@ -542,6 +559,12 @@ class DeviceStateProcessingLogic:
     def process(self, data, rec_off, cols: HostCols, id_hi, id_lo):
         self.ctx.merge(data, rec_off, cols, self.seq, id_hi, id_lo)
         self.seq += cols.n
+
+    def process_records(self, fmt: str, data, rec_off, id_hi, id_lo) -> int:
+        """process(List<ConsumerRecord>) on raw record payloads: one fused native call (decode + merge)."""
+        rows = self.ctx.decode_merge(fmt, data, rec_off, self.seq, id_hi, id_lo)
+        self.seq += rows
+        return rows
 
     def snapshot(self):
         return self.ctx.state_snapshot()

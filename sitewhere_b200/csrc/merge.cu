@@ -70,6 +70,7 @@ struct MgArgs {
     const uint32_t *n_rows_dev;
     uint64_t seq_base;
     const uint64_t *id_hi, *id_lo;
+    uint32_t ids_by_record;  // 1: id arrays are indexed by source record (every row of a record carries its id)
     uint32_t *fix_row;   // fix-up list: row ...
     uint64_t *fix_slot;  // ... and its slot
 };
@@ -154,7 +155,8 @@ __global__ void __launch_bounds__(MG_THREADS) merge_upsert_kernel(MgArgs a) {
         for (uint32_t i = 0; i < 2; i++) kw[5 + i] = i < nw ? mg_payload_word(name + 8 * i, min(8u, nl - 8 * i)) : 0ull;
     }
     // the payload this row would store (most rows do: one row per key per batch is the common case)
-    const uint64_t v_hi = __ldg(a.id_hi + r), v_lo = __ldg(a.id_lo + r);
+    const uint32_t idx = a.ids_by_record ? SWGPU_META_REC(m) : r;
+    const uint64_t v_hi = __ldg(a.id_hi + idx), v_lo = __ldg(a.id_lo + idx);
     const int64_t v_date = __ldg(a.event_date + r);
     const double v_val = __ldg(a.v0 + r);
     for (uint64_t probes = 0; probes <= a.mask; probes++, s = (s + 1) & a.mask) {
@@ -247,8 +249,9 @@ __global__ void __launch_bounds__(MG_THREADS) merge_fixup_kernel(MgArgs a) {
         const uint32_t r = a.fix_row[k];
         MgSlot *sl = a.slots + a.fix_slot[k];
         if (sl->best != a.seq_base + r + 1) continue;  // a later event of this key won
-        sl->id_hi = __ldg(a.id_hi + r);
-        sl->id_lo = __ldg(a.id_lo + r);
+        const uint32_t idx = a.ids_by_record ? SWGPU_META_REC(__ldg(a.meta + r)) : r;
+        sl->id_hi = __ldg(a.id_hi + idx);
+        sl->id_lo = __ldg(a.id_lo + idx);
         sl->date = __ldg(a.event_date + r);
         sl->value = __ldg(a.v0 + r);
     }
@@ -360,10 +363,20 @@ extern "C" int32_t swgpu_state_reserve(swgpu_ctx *ctx, uint64_t max_keys, uint64
     return mg_reserve(ctx, max_keys, max_key_bytes);
 }
 
+int sw_merge_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n_records,
+                    const swgpu_decoded_cols *rows, uint32_t n_rows, const uint32_t *n_rows_dev, uint64_t seq_base,
+                    const uint64_t *id_hi, const uint64_t *id_lo, bool ids_by_record);
+
 extern "C" int32_t swgpu_merge_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off,
                                    uint32_t n_records, const swgpu_decoded_cols *rows, uint32_t n_rows,
                                    const uint32_t *n_rows_dev, uint64_t seq_base, const uint64_t *id_hi,
                                    const uint64_t *id_lo) {
+    return sw_merge_launch(ctx, bytes, rec_off, n_records, rows, n_rows, n_rows_dev, seq_base, id_hi, id_lo, false);
+}
+
+int sw_merge_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n_records,
+                    const swgpu_decoded_cols *rows, uint32_t n_rows, const uint32_t *n_rows_dev, uint64_t seq_base,
+                    const uint64_t *id_hi, const uint64_t *id_lo, bool ids_by_record) {
     (void)n_records;
     if (!ctx) return SWGPU_E_INVALID;
     if (n_rows == 0) return SWGPU_OK;
@@ -415,6 +428,7 @@ extern "C" int32_t swgpu_merge_dev(swgpu_ctx *ctx, const uint8_t *bytes, const u
     a.seq_base = seq_base;
     a.id_hi = id_hi;
     a.id_lo = id_lo;
+    a.ids_by_record = ids_by_record ? 1u : 0u;
     a.fix_slot = (uint64_t *)st->fix.p;
     a.fix_row = (uint32_t *)((uint8_t *)st->fix.p + (((size_t)n_rows * 8 + 63) & ~(size_t)63));
     const unsigned nb = (n_rows + MG_THREADS - 1) / MG_THREADS;
@@ -472,6 +486,88 @@ extern "C" int32_t swgpu_merge(swgpu_ctx *ctx, const uint8_t *bytes, const uint6
     MgState *st = (MgState *)ctx->state;
     MgCounters c;
     if (int rc2 = mg_read_counters(ctx, st, &c)) return rc2;
+    st->keys_upper = c.n_keys;
+    st->arena_upper = c.arena_top < st->arena_cap ? c.arena_top : st->arena_cap;
+    if (c.table_full || c.arena_full) {
+        SW_SET_ERR(ctx, "state table capacity exceeded (table_full=%llu arena_full=%llu)", c.table_full, c.arena_full);
+        return SWGPU_E_CAPACITY;
+    }
+    return SWGPU_OK;
+}
+
+// ---- fused host-buffer call of the device-state consumer: decode a poll() batch and fold it into the state,
+// without the rows ever leaving the GPU (swgpu_decode_* followed by swgpu_merge would download the decoded
+// columns and upload them again).
+int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
+                        const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev,
+                        uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next);
+int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
+                          const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev,
+                          uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next);
+
+extern "C" int32_t swgpu_decode_merge(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off,
+                                      uint32_t n, uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo,
+                                      uint8_t *status, uint32_t *out_rows) {
+    if (!ctx) return SWGPU_E_INVALID;
+    if (!rec_off || !out_rows || (format != SWGPU_FMT_PROTOBUF && format != SWGPU_FMT_JSON) ||
+        (n && (!id_hi || !id_lo || (rec_off[n] && !bytes)))) {
+        SW_SET_ERR(ctx, "swgpu_decode_merge: bad argument");
+        return SWGPU_E_INVALID;
+    }
+    *out_rows = 0;
+    if (n == 0) return SWGPU_OK;
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    const uint64_t total = rec_off[n];
+    if (int rc = sw_ensure(ctx, ctx->d_bytes, total + 64)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_off, (size_t)(n + 1) * 8)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_status, (size_t)n + 16)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_first, (size_t)(n + 2) * 4 + 16)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_ids, (size_t)n * 16 + 64)) return rc;
+    if (int rc = sw_ensure_pinned(ctx, ctx->h_small, 64)) return rc;
+    if (total) SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_bytes.p, bytes, total, cudaMemcpyHostToDevice, s));
+    SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_off.p, rec_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, s));
+    uint64_t *ids = (uint64_t *)ctx->d_ids.p;
+    SW_CUDA(ctx, cudaMemcpyAsync(ids, id_hi, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+    SW_CUDA(ctx, cudaMemcpyAsync(ids + n, id_lo, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+    uint32_t *d_first = (uint32_t *)ctx->d_first.p, *d_rows = d_first + (n + 1);
+    uint32_t cap = n + 64, rows = 0;
+    swgpu_decoded_cols d;
+    for (int attempt = 0;; attempt++) {  // a DeviceMeasurements payload can fan out: second try with the exact size
+        if (int rc = sw_ensure(ctx, ctx->d_cols, (size_t)cap * 8 * 9 + 64)) return rc;
+        memset(&d, 0, sizeof d);
+        uint64_t **dp = (uint64_t **)&d;
+        for (int c = 0; c < 9; c++) dp[c] = (uint64_t *)ctx->d_cols.p + (size_t)c * cap;
+        const int rc = format == SWGPU_FMT_JSON
+                           ? sw_decode_json_launch(ctx, (const uint8_t *)ctx->d_bytes.p, (const uint64_t *)ctx->d_off.p, n, cap,
+                                                   &d, (uint8_t *)ctx->d_status.p, d_first, d_rows, 0, nullptr, nullptr)
+                           : sw_decode_pb_launch(ctx, (const uint8_t *)ctx->d_bytes.p, (const uint64_t *)ctx->d_off.p, n, cap,
+                                                 &d, (uint8_t *)ctx->d_status.p, d_first, d_rows, 0, nullptr, nullptr);
+        if (rc) return rc;
+        SW_CUDA(ctx, cudaMemcpyAsync(ctx->h_small.p, d_rows, 4, cudaMemcpyDeviceToHost, s));
+        SW_CUDA(ctx, cudaStreamSynchronize(s));
+        rows = *(const uint32_t *)ctx->h_small.p;
+        if (rows <= cap) break;
+        if (attempt) {
+            SW_SET_ERR(ctx, "swgpu_decode_merge: row count changed between two decodes of the same batch");
+            return SWGPU_E_CUDA;
+        }
+        cap = rows;
+    }
+    if (status) SW_CUDA(ctx, cudaMemcpyAsync(status, ctx->d_status.p, n, cudaMemcpyDeviceToHost, s));
+    *out_rows = rows;
+    if (rows) {
+        if (int rc = sw_merge_launch(ctx, (const uint8_t *)ctx->d_bytes.p, (const uint64_t *)ctx->d_off.p, n, &d, rows, nullptr,
+                                     seq_base, ids, ids + n, true))
+            return rc;
+    }
+    MgState *st = (MgState *)ctx->state;
+    if (!st) {
+        SW_CUDA(ctx, cudaStreamSynchronize(s));
+        return SWGPU_OK;
+    }
+    MgCounters c;
+    if (int rc2 = mg_read_counters(ctx, st, &c)) return rc2;  // (synchronises: `status` has landed too)
     st->keys_upper = c.n_keys;
     st->arena_upper = c.arena_top < st->arena_cap ? c.arena_top : st->arena_cap;
     if (c.table_full || c.arena_full) {

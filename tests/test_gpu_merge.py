@@ -101,3 +101,49 @@ def test_colliding_bucket_keys_are_told_apart_by_bytes(ctx):
     assert s["seq"].shape[0] == 6
     snap_equal(s, st.snapshot())
     ctx.state_clear()
+
+
+def test_fused_decode_merge_matches_decode_then_merge(ctx):
+    """swgpu_decode_merge (one host-buffer call, rows never leave the GPU) leaves the same state as the oracle's
+    decode + sequential fold: several batches, failed records, a fan-out record (ids are per RECORD: every row of
+    a record carries its id), both formats"""
+    from tests import pb_cases, json_cases
+    ctx.state_clear()
+    st = oracle.State()
+    logic = sw.DeviceStateProcessingLogic(ctx)
+    seq = 0
+    rng = np.random.default_rng(9)
+    for b in range(3):
+        good, goff, _ = S.pb_mixed(20_000, 700, seed=500 + b)
+        raw = good.tobytes()
+        recs = [raw[int(goff[i]): int(goff[i + 1])] for i in range(20_000)]
+        for c in pb_cases.cases():
+            recs.insert(int(rng.integers(0, len(recs))), c[1])
+        recs.insert(100, S.pb_measurements_record("fan%d" % b, [("m%03d" % k, float(k + b)) for k in range(300)], date=7 + b))
+        data, rec_off = S.pack_records(recs)
+        n = len(recs)
+        id_hi = np.full(n, 40 + b, np.uint64)
+        id_lo = rng.integers(0, 1 << 62, size=n).astype(np.uint64)
+        status = np.zeros(n, np.uint8)
+        rows = ctx.decode_merge("pb", data, rec_off, seq, id_hi, id_lo, status)
+        ocols, ostatus, ofirst, total = oracle.decode_pb(data, rec_off)
+        assert rows == total and np.array_equal(status, ostatus[:n])
+        rec_of_row = (ocols.meta[:total].view(np.uint64) >> np.uint64(32)).astype(np.int64)
+        st.merge(data, rec_off, ocols, seq, id_hi[rec_of_row], id_lo[rec_of_row])
+        seq += total
+    jrecs = [c[1] for c in json_cases.cases()]
+    for i in range(3000):
+        jrecs.append(S.json_measurement(S.token_str(i % 97), "fuel.level", repr(float(i) / 7), S.EVENT_DATE_BASE + i))
+    data, rec_off = S.pack_records(jrecs)
+    n = len(jrecs)
+    id_hi = np.full(n, 99, np.uint64)
+    id_lo = np.arange(n, dtype=np.uint64)
+    logic.seq = seq
+    rows = logic.process_records("json", data, rec_off, id_hi, id_lo)
+    ocols, ostatus, ofirst, total = oracle.decode_json(data, rec_off)
+    assert rows == total
+    rec_of_row = (ocols.meta[:total].view(np.uint64) >> np.uint64(32)).astype(np.int64)
+    st.merge(data, rec_off, ocols, seq, id_hi[rec_of_row], id_lo[rec_of_row])
+    snap_equal(ctx.state_snapshot(), st.snapshot())
+    assert ctx.decode_merge("pb", np.zeros(0, np.uint8), np.zeros(1, np.uint64), 0, np.zeros(0, np.uint64), np.zeros(0, np.uint64)) == 0
+    ctx.state_clear()
