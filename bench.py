@@ -270,6 +270,28 @@ def run_extras(ctx, sw, torch, stream, dev, peak):
                         "merge_events_per_s": n / (ms_mrg * 1e-3), "algorithmic_bytes": bytes_mrg,
                         "GBps": bytes_mrg / (ms_mrg * 1e-3) / 1e9, "frac_hbm": bytes_mrg / (ms_mrg * 1e-3) / 1e9 / peak}
         ctx.state_clear()
+        # ---- the same batch end to end through the host-buffer call of the state consumer (pinned payload in,
+        #      state on the GPU; one upload of payload + offsets + ids, a 10 MB status download)
+        try:
+            from sitewhere_b200.api import pinned_array
+            p_data = pinned_array((data.shape[0],), np.uint8)
+            p_data[:] = data
+            p_off = pinned_array((n + 1,), np.uint64)
+            p_off[:] = rec_off
+            p_ids = pinned_array((n,), np.uint64)
+            p_ids[:] = np.arange(n, dtype=np.uint64)
+            p_st = pinned_array((n,), np.uint8)
+            ctx.state_reserve(20_000_000, 20_000_000 * 40)
+            ctx.decode_merge("pb", p_data, p_off, 0, p_ids, p_ids, p_st)
+            t0 = time.perf_counter()
+            for k in range(3):
+                ctx.decode_merge("pb", p_data, p_off, (k + 1) * n, p_ids, p_ids, p_st)
+            dt = (time.perf_counter() - t0) / 3
+            out["merge"]["e2e_decode_merge_events_per_s"] = n / dt
+            out["merge"]["e2e_h2d_bytes"] = int(data.shape[0] + 8 * (n + 1) + 16 * n)
+            ctx.state_clear()
+        except Exception as e:  # secondary number
+            out["merge"]["e2e_error"] = repr(e)[:160]
     return out
 
 
