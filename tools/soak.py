@@ -1,0 +1,63 @@
+"""Differential soak: the fuzzers of tests/test_gpu_fuzz.py with fresh seeds for a given number of seconds.
+    python tools/soak.py 240        (prints one line per round, stops at the first mismatch)"""
+import sys, time
+sys.path.insert(0, '.')
+import numpy as np
+import oracle
+import sitewhere_b200 as sw
+from sitewhere_b200 import synth as S
+from tests import test_gpu_fuzz as F, pb_cases, json_cases
+from tests.helpers import check_decode_parity
+
+budget = float(sys.argv[1]) if len(sys.argv) > 1 else 120.0
+ctx = sw.Context()
+t_end = time.time() + budget
+seed = int(time.time()) & 0xffffff
+rnd = 0
+d0, o0, _ = S.pb_mixed(3000, 200, seed=77)
+pb_base = F._records(d0, o0) + [bytes(c[1]) for c in pb_cases.cases()]
+d1, o1, _ = S.json_measurements(1500, 100, seed=78)
+js_base = F._records(d1, o1) + [bytes(c[1]) for c in json_cases.cases()]
+js_base += [S.json_location("00001-SYNTH-000000001", "34.5", "-84.25", "12.5", 1540000000000),
+            S.json_alert("00001-SYNTH-000000002", "engine.overheat", "too hot", 1540000000001)]
+tot = dict(pb=0, json=0, zone=0, pipe=0)
+while time.time() < t_end:
+    rng = np.random.default_rng(seed + rnd)
+    recs = F._mutate(rng, pb_base, F.PB_SPECIALS, 50_000, max_mut=1 + rnd % 4)
+    data, off = S.pack_records(recs)
+    check_decode_parity(ctx.decode_pb(data, off), data, off, "decode_pb"); tot["pb"] += len(recs)
+    recs = F._mutate(rng, js_base, F.JSON_SPECIALS, 30_000, max_mut=1 + rnd % 3)
+    data, off = S.pack_records(recs)
+    check_decode_parity(ctx.decode_json(data, off), data, off, "decode_json"); tot["json"] += len(recs)
+    # lattice polygons
+    T = 120
+    vo, zx, zy = [0], [], []
+    for t in range(T):
+        nv = int(rng.integers(1, 16)); cx, cy = rng.integers(-20, 20, size=2); span = int(rng.integers(1, 9))
+        sc = (1.0, 0.5, 0.125, 3.0)[rnd % 4]
+        zx += list((cx + rng.integers(-span, span + 1, size=nv)).astype(np.float64) * sc)
+        zy += list((cy + rng.integers(-span, span + 1, size=nv)).astype(np.float64) * sc)
+        vo.append(len(zx))
+    zones = (np.array(vo, np.uint32), np.array(zx), np.array(zy), rng.integers(0, 2, size=T).astype(np.uint8))
+    n = 8000
+    lon = rng.integers(-60, 61, size=n).astype(np.float64) * sc * 0.5
+    lat = rng.integers(-60, 61, size=n).astype(np.float64) * sc * 0.5
+    lon[: n // 4] += rng.choice([1e-9, -1e-9, 2.0 ** -40, 0.25], size=n // 4)
+    ctx.set_zones(*zones)
+    got = ctx.zone_test(lon, lat, max_pairs=n * (T + 1))
+    want, total = oracle.zone_test(*zones, lon, lat)
+    assert got.shape[0] == total and np.array_equal(got, want), "zone mismatch round %d seed %d" % (rnd, seed)
+    tot["zone"] += n
+    # the fused pipeline on a mutated protobuf batch with random chunking
+    recs = F._mutate(rng, pb_base, F.PB_SPECIALS, 20_000, max_mut=1)
+    data, off = S.pack_records(recs)
+    chunk = int(rng.choice([0, 333, 1000, 4096, 7777]))
+    cols, status, first_row, n_rows, pairs = ctx.decode_zone_test("pb", data, off, chunk_records=chunk)
+    ocols, ostatus, ofirst, ototal = oracle.decode_pb(data, off)
+    assert n_rows == ototal and np.array_equal(status, ostatus) and np.array_equal(first_row, ofirst)
+    want, total = oracle.zone_test(*zones, ocols.v1[:ototal], ocols.v0[:ototal], meta=ocols.meta[:ototal])
+    assert np.array_equal(pairs, want), "pipeline mismatch round %d seed %d chunk %d" % (rnd, seed, chunk)
+    tot["pipe"] += len(recs)
+    rnd += 1
+    print("round", rnd, tot, flush=True)
+print("soak ok: seed", seed, "rounds", rnd, tot)
