@@ -58,6 +58,31 @@ while time.time() < t_end:
     want, total = oracle.zone_test(*zones, ocols.v1[:ototal], ocols.v0[:ototal], meta=ocols.meta[:ototal])
     assert np.array_equal(pairs, want), "pipeline mismatch round %d seed %d chunk %d" % (rnd, seed, chunk)
     tot["pipe"] += len(recs)
+    # device-state fold: a fresh state every fourth round, hot keys (few devices) or many keys, damaged records
+    if rnd % 4 == 0:
+        ctx.state_clear()
+        ost = oracle.State()
+        seq = 0
+    ndev = int(rng.choice([3, 40, 5000]))
+    d2, o2, _ = S.pb_mixed(15_000, ndev, seed=int(rng.integers(1 << 30)))
+    recs = F._records(d2, o2)
+    recs = recs + F._mutate(rng, recs[:2000], F.PB_SPECIALS, 2000, max_mut=1)
+    order = rng.permutation(len(recs))
+    recs = [recs[i] for i in order]
+    data, off = S.pack_records(recs)
+    ids_hi = rng.integers(0, 1 << 62, size=len(recs)).astype(np.uint64)
+    ids_lo = rng.integers(0, 1 << 62, size=len(recs)).astype(np.uint64)
+    rows = ctx.decode_merge("pb", data, off, seq, ids_hi, ids_lo)
+    ocols, ostatus, ofirst, ototal = oracle.decode_pb(data, off)
+    assert rows == ototal
+    rec_of_row = (ocols.meta[:ototal].view(np.uint64) >> np.uint64(32)).astype(np.int64)
+    ost.merge(data, off, ocols, seq, ids_hi[rec_of_row], ids_lo[rec_of_row])
+    seq += ototal
+    a, b = ctx.state_snapshot(), ost.snapshot()
+    for k in ("seq", "id_hi", "id_lo", "event_date", "key_off", "key_bytes"):
+        assert np.array_equal(a[k], b[k]), "state mismatch %s round %d seed %d" % (k, rnd, seed)
+    assert np.array_equal(a["value"].view(np.uint64), b["value"].view(np.uint64))
+    tot["merge"] = tot.get("merge", 0) + ototal
     rnd += 1
     print("round", rnd, tot, flush=True)
 print("soak ok: seed", seed, "rounds", rnd, tot)
