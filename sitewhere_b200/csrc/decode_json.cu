@@ -59,6 +59,7 @@ struct JsonScan {
     __device__ __forceinline__ void skip_ws() {
         while (pos < n) {
             uint32_t c = b.byte(pos);
+            if (c > ' ') break;  // the usual case (compact JSON): one comparison
             if (c == ' ' || c == '\t' || c == '\n' || c == '\r')
                 pos++;
             else
