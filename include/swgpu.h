@@ -135,6 +135,15 @@ const char *swgpu_last_error(swgpu_ctx *ctx); /* ctx may be NULL: error of the l
 int32_t swgpu_abi_version(void);
 void *swgpu_stream(swgpu_ctx *ctx);
 int32_t swgpu_sync(swgpu_ctx *ctx);
+/* Named integer options of a context (no counterpart in the reference: they pick between code paths that
+ * give identical results, so that tests can cover each path, or switch on work counters):
+ *   "zone.force_ray"        0 = the zone walk picks its ray per point (default); 1..4 = always walk the
+ *                           +x, -x, +y or -y copy of a ring, even for a zone whose table entry restricts the
+ *                           choice (JTS 1.13 casts +x: RayCrossingCounter, called from the zone test at
+ *                           RP/processors/geospatial/ZoneTestRuleProcessor.java:50)
+ *   "zone.scan_sequential"  1 = scan the per-tile alert counts on one CTA
+ *   "zone.stats"            1 = zone tests also count their work (read it with swgpu_zone_stats)        */
+int32_t swgpu_set_option(swgpu_ctx *ctx, const char *name, int64_t value);
 /* Pinned host staging the Java side wraps as a direct ByteBuffer / MemorySegment.             */
 void *swgpu_alloc_pinned(size_t bytes);
 void swgpu_free_pinned(void *p);
@@ -199,6 +208,12 @@ int32_t swgpu_zone_test(swgpu_ctx *ctx, const double *lon, const double *lat, co
 int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const double *lat,
                             const uint64_t *meta, uint32_t n, const uint32_t *n_rows_dev,
                             uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev);
+
+/* Measurement aid (no counterpart in the reference): work done by the last swgpu_zone_test[_dev] that ran
+ * with option "zone.stats" = 1.  out[0] = grid-cell zone records read, out[1] = edge records read,
+ * out[2] = straddle tests (an edge whose ends lie on either side of the ray: the exact-sign determinant of
+ * RayCrossingCounter.countSegment), out[3] = locations.  Waits for the context's stream.                  */
+int32_t swgpu_zone_stats(swgpu_ctx *ctx, uint64_t out[4]);
 
 /* ---- fused host-buffer path ------------------------------------------------------------------------
  * Decode + zone test of one micro-batch held in HOST memory, in one call: what the Java binding's

@@ -695,6 +695,12 @@ uint64_t orc_zone_test(uint32_t n_tests, const uint32_t *vtx_off, const double *
         }
         for (uint32_t t = 0; t < n_tests; t++) {
             uint32_t npts = (uint32_t)(coff[t + 1] - coff[t]);
+            /* 1 or 2 bounds close to a ring of 2 or 3 points: GeometryFactory.createLinearRing throws
+             * IllegalArgumentException (JTS 1.13 LinearRing.validateConstruction: 0 or >= 4 points) from
+             * getZonePolygon (ZoneTestRuleProcessor.java:49,72-84; GeoUtils.java:55-67), the polygon is never
+             * cached, and onLocation ends there for every location: tests after it never fire.  (The GPU
+             * library refuses such a table in swgpu_set_zones.) */
+            if (npts < 4) break;
             int inside = contains_prepared(cx + coff[t], cy + coff[t], npts, env[4 * t], env[4 * t + 1],
                                            env[4 * t + 2], env[4 * t + 3], rect[t], plon[i], plat[i]);
             /* containment == test.getCondition()  (Inside = 0, Outside = 1)   :50-53 */

@@ -59,6 +59,7 @@ SIGNATURES = {
     "swgpu_abi_version": (_I32, []),
     "swgpu_stream": (_P, [_P]),
     "swgpu_sync": (_I32, [_P]),
+    "swgpu_set_option": (_I32, [_P, C.c_char_p, C.c_int64]),
     "swgpu_alloc_pinned": (_P, [C.c_size_t]),
     "swgpu_free_pinned": (None, [_P]),
     "swgpu_set_zones": (_I32, [_P, _U32, _P, _P, _P, _P]),
@@ -71,6 +72,7 @@ SIGNATURES = {
     "swgpu_decode_json_dev": (_I32, [_P, _P, _P, _U32, _U32, _COLS, _P, _P, _P]),
     "swgpu_zone_test": (_I32, [_P, _P, _P, _P, _U32, _U64, _P, _P]),
     "swgpu_zone_test_dev": (_I32, [_P, _P, _P, _P, _U32, _P, _U64, _P, _P]),
+    "swgpu_zone_stats": (_I32, [_P, _P]),
     "swgpu_decode_zone_test": (_I32, [_P, _I32, _P, _P, _U32, _U32, _COLS, _P, _P, _P, _U64, _P, _P, _U32]),
     "swgpu_zone_test_noalloc_dev": (_I32, [_P, _P, _P, _P, _U32, _P, _U64, _P, _P]),
     "swgpu_state_reserve": (_I32, [_P, _U64, _U64]),

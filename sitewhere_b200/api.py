@@ -141,6 +141,10 @@ class Context:
     def sync(self):
         self._check(self.lib.swgpu_sync(self.h))
 
+    def set_option(self, name: str, value: int):
+        """swgpu_set_option: pick between code paths that give identical results (used by the tests)."""
+        self._check(self.lib.swgpu_set_option(self.h, name.encode(), int(value)))
+
     @property
     def stream(self) -> int:
         return int(self.lib.swgpu_stream(self.h) or 0)
@@ -236,6 +240,12 @@ class Context:
             self.h, lon_t.data_ptr(), lat_t.data_ptr(), meta_t.data_ptr() if meta_t is not None else None, int(n),
             n_rows_t.data_ptr() if n_rows_t is not None else None, pairs_t.numel(), pairs_t.data_ptr(),
             n_pairs_t.data_ptr()))
+
+    def zone_stats(self) -> dict:
+        """swgpu_zone_stats: work counters of the last zone test run with option zone.stats = 1."""
+        out = (C.c_uint64 * 4)()
+        self._check(self.lib.swgpu_zone_stats(self.h, out))
+        return dict(cell_records=int(out[0]), edge_records=int(out[1]), straddle_tests=int(out[2]), locations=int(out[3]))
 
     # ---- fused host-buffer path (chunked, overlapped) -------------------------------------------------
     def decode_zone_test(self, fmt: str, data, rec_off, cols: "HostCols" = None, status=None, first_row=None,

@@ -143,6 +143,30 @@ extern "C" int32_t swgpu_sync(swgpu_ctx *ctx) {
     return SWGPU_OK;
 }
 
+// Named integer options.  None of them changes a result; they select between equivalent code paths so that
+// the tests can cover each one, or switch on work counters (see include/swgpu.h).
+extern "C" int32_t swgpu_set_option(swgpu_ctx *ctx, const char *name, int64_t value) {
+    if (!ctx || !name) return SWGPU_E_INVALID;
+    if (!strcmp(name, "zone.force_ray")) {
+        if (value < 0 || value > 4) {
+            SW_SET_ERR(ctx, "swgpu_set_option: zone.force_ray takes 0 (choose) or 1..4 (+x, -x, +y, -y)");
+            return SWGPU_E_INVALID;
+        }
+        ctx->opt_zone_force_ray = (uint32_t)value;
+        return SWGPU_OK;
+    }
+    if (!strcmp(name, "zone.scan_sequential")) {
+        ctx->opt_zone_scan_sequential = value ? 1u : 0u;
+        return SWGPU_OK;
+    }
+    if (!strcmp(name, "zone.stats")) {
+        ctx->opt_zone_stats = value ? 1u : 0u;
+        return SWGPU_OK;
+    }
+    SW_SET_ERR(ctx, "swgpu_set_option: unknown option '%s'", name);
+    return SWGPU_E_INVALID;
+}
+
 extern "C" void *swgpu_alloc_pinned(size_t bytes) {
     void *p = nullptr;
     if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;

@@ -2,12 +2,13 @@
 // (reference: service-event-sources/src/main/java/com/sitewhere/sources/decoder/protobuf/
 //  ProtobufDeviceEventDecoder.java:75-304; schema sitewhere-communication/src/main/proto/sitewhere.proto).
 //
-// One CTA decodes a tile of 256 consecutive records.  The tile's byte range is contiguous in the
-// batch buffer, so it is staged into shared memory with coalesced 16-byte streaming loads; each
-// thread then walks its own record out of shared memory (proto2 wire format, protobuf-java lite
-// semantics), and rows are written to the SoA columns at positions given by a single-pass ordered
-// scan (decoupled look-back), so output order is the reference's order with no second pass over
-// the payload.  HBM traffic = payload once + offsets + columns: the kernel is HBM-bound.
+// Two kernels, launched back to back.  pb_decode_dense_kernel is the optimistic pass: a warp takes four
+// consecutive tiles of 32 records, each tile's contiguous bytes arrive in the warp's shared-memory slice by
+// one TMA bulk copy (double-buffered, mbarrier completion), each lane walks one record (proto2 wire format,
+// protobuf-java lite semantics) and writes its row at row index = record index; it raises a flag when some
+// record yields 0 or several rows.  pb_decode_ordered_kernel returns at once unless that flag is up; then it
+// redoes the batch with exact ordered placement (ticketed tiles + decoupled look-back).  HBM traffic =
+// payload once + offsets + columns: the dense kernel is HBM-bound.
 #include <algorithm>
 
 #include "swgpu_common.cuh"
@@ -495,22 +496,13 @@ __device__ __forceinline__ void pb_write_rows(const PbArgs &a, B bytes, const Pb
     }
 }
 
-// A CTA owns a tile of 256 consecutive records (its position in the ordered scan); inside it every WARP
-// stages the contiguous bytes of its own 32 records into its private slice of shared memory (coalesced
-// 16-byte streaming loads, __syncwarp only) and each lane walks one record.  The only block barriers are
-// the ticket and the two of the ordered scan.
-//
-// Two instantiations, launched back to back on the same stream:
-//   DENSE = true   the optimistic pass.  Almost every batch is "dense": each record decodes to exactly one
-//                  row, so row index = record index and no tile depends on another — no ticket, no scan, no
-//                  waiting; the kernel runs at the speed of its memory traffic.  A record that yields 0 rows
-//                  (failed / pass-through / empty DeviceMeasurements) or several raises *not_dense.
-//   DENSE = false  the ordered pass (ticketed tiles + decoupled look-back).  It returns at once unless
-//                  *not_dense was raised; then it redoes the batch with exact ordered placement.  In that
-//                  pass every tile waits for the slowest of the few hundred tiles in flight, which is why
-//                  it is ~2.5x slower than the dense pass (measured; DESIGN.md "ordered placement").
-// one tile = PB_THREADS records, one per thread
-template <bool DENSE>
+// ---- ordered pass (exact redo).  A CTA owns a tile of 256 consecutive records (its position in the ordered
+// scan); inside it every WARP stages the contiguous bytes of its own 32 records into its private slice of
+// shared memory (coalesced 16-byte streaming loads, __syncwarp only) and each lane walks one record.  The only
+// block barriers are the ticket and the two of the ordered scan.  Rows are placed by ticketed tiles +
+// decoupled look-back; every tile waits for the slowest of the few hundred tiles in flight, which is why this
+// pass is ~2.5x slower than the dense one (measured; DESIGN.md "ordered placement") and only runs when the
+// dense pass found a record that does not decode to exactly one row.
 __device__ __forceinline__ void pb_decode_tile(const PbArgs &a, const uint32_t tile, uint8_t *smem, uint64_t *s_warp) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint64_t rec0_64 = (uint64_t)tile * PB_THREADS + warp * 32;
@@ -546,19 +538,14 @@ __device__ __forceinline__ void pb_decode_tile(const PbArgs &a, const uint32_t t
         else
             pb_parse_record(GmemBytes{a.bytes + r0}, len, o);
     }
-    uint64_t tile_total = 0, row0;
-    if (DENSE) {
-        row0 = (uint64_t)rec0 + lane;  // row index = record index
-        if (lane < nrec && o.count != 1) atomicOr(a.not_dense, 1u);
-    } else {
-        row0 = sw_block_ordered_offset<PB_THREADS>(o.count, a.tile_state, tile, s_warp, &tile_total);
-    }
+    uint64_t tile_total = 0;
+    const uint64_t row0 = sw_block_ordered_offset<PB_THREADS>(o.count, a.tile_state, tile, s_warp, &tile_total);
     const uint64_t row_base = a.row_base ? (uint64_t)__ldg(a.row_base) : 0ull;  // rows of earlier chunks
     if (lane < nrec) {
         const uint32_t rec = rec0 + lane;
         a.status[rec] = (uint8_t)o.status;
         a.first_row[rec] = (uint32_t)(row_base + row0);
-        if (DENSE ? o.count == 1 : o.count != 0) {
+        if (o.count != 0) {
             if (staged)
                 pb_write_rows(a, SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, o, rec, row0);
             else
@@ -566,26 +553,20 @@ __device__ __forceinline__ void pb_decode_tile(const PbArgs &a, const uint32_t t
         }
     }
     if ((uint64_t)tile * PB_THREADS + PB_THREADS >= a.n && tid == 0) {  // the tile holding the last record
-        const uint64_t total = DENSE ? (uint64_t)a.n : row0 + tile_total;  // thread 0's offset is the tile base
+        const uint64_t total = row0 + tile_total;  // thread 0's offset is the tile base
         a.first_row[a.n] = (uint32_t)(row_base + total);
         *a.out_rows = (uint32_t)total;
         if (a.row_next) *a.row_next = (uint32_t)(row_base + total);
     }
 }
 
-// DENSE: one CTA per tile (kept for reference and for the JSON decoder's twin; the protobuf dense pass
-// now runs pb_decode_dense_kernel below).  Ordered pass: a few CTAs per SM take tiles by ticket (tickets
-// are handed out in start order, which is what the look-back needs), so when the dense pass was exact —
-// the usual case — the launch costs a few hundred CTAs that read one flag, not one CTA per tile.
-template <bool DENSE>
-__global__ void __launch_bounds__(PB_THREADS) pb_decode_kernel(PbArgs a) {
+// A few CTAs per SM take tiles by ticket (tickets are handed out in start order, which is what the look-back
+// needs), so when the dense pass was exact — the usual case — the launch costs a few hundred CTAs that read
+// one flag, not one CTA per tile.
+__global__ void __launch_bounds__(PB_THREADS) pb_decode_ordered_kernel(PbArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];  // PB_WARPS * (PB_WSTAGE + 32)
     __shared__ uint64_t s_warp[PB_THREADS / 32 + 2];
     __shared__ uint32_t s_tile;
-    if (DENSE) {
-        pb_decode_tile<true>(a, blockIdx.x, smem, s_warp);
-        return;
-    }
     if (__ldg(a.not_dense) == 0) return;  // the dense pass was exact: nothing to redo
     const uint32_t ntiles = (uint32_t)(((uint64_t)a.n + PB_THREADS - 1) / PB_THREADS);
     for (;;) {
@@ -593,12 +574,12 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_kernel(PbArgs a) {
         __syncthreads();
         const uint32_t tile = s_tile;
         if (tile >= ntiles) return;
-        pb_decode_tile<false>(a, tile, smem, s_warp);
+        pb_decode_tile(a, tile, smem, s_warp);
         __syncthreads();  // s_tile, s_warp and the staging buffers are reused
     }
 }
 
-// ---- dense pass, pipelined.  Same work per warp-tile (32 records) as pb_decode_tile<true>, but a warp goes
+// ---- dense pass, pipelined.  Same work per warp-tile (32 records) as pb_decode_tile, but a warp goes
 // through PD_TILES consecutive tiles with the NEXT tile's payload already on its way into the other half
 // of its shared-memory slice (one TMA bulk copy per tile, completion on an mbarrier) and the offsets of the tile after that
 // already requested, so the two serial round trips at the head of a tile (offsets, then payload: half of
@@ -798,7 +779,7 @@ int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
         std::lock_guard<std::mutex> lk(mu);
         const int d = ctx->device & 63;
         if (!done[d]) {
-            SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_ordered_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
             SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               PB_WARPS * 2 * (PD_STAGE + 32)));
             done[d] = true;
@@ -813,7 +794,7 @@ int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
     }
     SW_CUDA(ctx, cudaGetLastError());
     const uint32_t nredo = std::min<uint32_t>(ntiles, (uint32_t)ctx->sm_count * 4u);
-    pb_decode_kernel<false><<<nredo, PB_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
+    pb_decode_ordered_kernel<<<nredo, PB_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
 }

@@ -71,6 +71,7 @@ static_assert(sizeof(ZnCellRec) == 32, "ZnCellRec layout");
 #define ZC_OUTSIDE 1u   // alert condition == Outside
 #define ZC_RECT 2u      // JTS isRectangle: RectangleContains on the exact envelope
 #define ZC_RANGES 4u    // uneven slabs: {start,end} ranges instead of a fixed stride
+#define ZC_XONLY 8u     // rays along x only (see build_zone_blob: translations p_i - p are not always exact)
 #define ZC_EMPTY 0x40u  // no zone envelope overlaps the cell
 #define ZC_LIST 0x80u   // list head
 #define ZC_MAX_STRIDE 4095u
@@ -148,6 +149,15 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
             SW_SET_ERR(ctx, "swgpu_set_zones: test %u has no bounds", t);
             return SWGPU_E_INVALID;
         }
+        if (nv < 3) {
+            // GeoUtils.createPolygonForLocations closes the ring with the first bound: 1 or 2 bounds give 2 or 3
+            // points, and JTS 1.13 LinearRing.validateConstruction throws IllegalArgumentException ("Invalid
+            // number of points in LinearRing (found N - must be 0 or >= 4)").  In the reference every
+            // onLocation then fails at this test (the polygon is never cached); here the table is refused.
+            SW_SET_ERR(ctx, "swgpu_set_zones: test %u has %u bounds; JTS needs at least 3 (a closed ring of >= 4 points)",
+                       t, nv);
+            return SWGPU_E_INVALID;
+        }
         total_pts += nv + 1;
     }
     if (total_pts > 0x7fffffffull) {
@@ -198,7 +208,7 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
             }
         }
         bool rect = host_is_rectangle(xs.data(), ys.data(), z.npts, minx, maxx, miny, maxy);
-        z.flags = (cond[t] ? 1u : 0u) | (rect ? 2u : 0u);
+        z.flags = (cond[t] ? ZC_OUTSIDE : 0u) | (rect ? ZC_RECT : 0u);
         if (cond[t]) outside.push_back(t);
         gx0 = std::min(gx0, minx);
         gx1 = std::max(gx1, maxx);
@@ -226,6 +236,19 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
             // A closed ring crosses any line an even number of times (with the walk's half-open rule for
             // vertices on the line), so all four parities agree, and an edge the point lies on is in the
             // point's slab and is met before the walk stops, whichever way it goes.
+            //
+            // That argument is about EXACT orientation predicates.  JTS 1.13 decides a crossing from the
+            // coordinates translated in double (x1 = p1.x - p.x, ...): the sign it takes is exact for the
+            // ROUNDED differences.  The +x and -x walks test the same edges (those that straddle y = p.y) with
+            // the same determinant (negating x commutes with IEEE subtraction), so each such edge is classed
+            // left / right / on identically and the two parities agree whatever the rounding did.  The +-y
+            // walks test a different set of edges (those that straddle x = p.x): they agree with JTS's +x
+            // answer for sure only when every difference is exact, i.e. the predicate is the true orientation.
+            // By Sterbenz's lemma a - b is exact when a/2 <= b <= 2a; a point that reaches a sign test lies
+            // inside the envelope, so if on each axis the envelope keeps one sign and max <= 2 min in
+            // magnitude, every vertex - point difference is exact.  Only such zones (any geofence that does
+            // not touch an axis and is smaller than its distance from it) use the +-y copies; the others are
+            // flagged ZC_XONLY and walk along x only.
             const uint32_t nb = std::max(1u, std::min(64u, (z.npts - 1 + 3) / 4));
             const double *uc[2] = {xs.data(), ys.data()};  // axis 0: ray along x, slabs along y
             const double v0[2] = {miny, minx};  // slab origins
@@ -252,6 +275,10 @@ static int build_zone_blob(swgpu_ctx *ctx, uint32_t T, const uint32_t *vtx_off, 
             z.nbins = nb;
             z.inv_bin = inv[0];
             cr.inv16 = inv16[0] | (inv16[1] << 16);
+            auto sterbenz = [](double lo, double hi) {  // every a, b in [lo, hi]:  a/2 <= b <= 2a
+                return (lo > 0 && hi <= 2 * lo) || (hi < 0 && lo >= 2 * hi);
+            };
+            if (!(sterbenz(minx, maxx) && sterbenz(miny, maxy))) z.flags |= ZC_XONLY;
             auto put_slab = [&](std::vector<uint32_t> &v, int ax, int side) {
                 const double sg = side ? -1.0 : 1.0;
                 const double *u = uc[ax], *vc = uc[1 - ax];
@@ -506,6 +533,7 @@ struct ZnArgs {
     uint32_t *ticket;
     uint64_t *tile_state;
     const uint32_t *row_base;  // chunked pipeline: global index of row 0 (NULL = 0)
+    uint32_t force_ray;        // test knob (swgpu_set_option "zone.force_ray"): 0 = choose, 1..4 = +x, -x, +y, -y
 };
 
 // exact sign of x1*y2 - y1*x2: products with their rounding errors (fma), compared as the
@@ -569,8 +597,11 @@ __device__ __forceinline__ ZnD4 zn_ld256(const void *p) {
 // The walk runs in the frame of the chosen copy of the ring (see the table builder): `u` is the
 // coordinate along the ray (x, -x, y or -y), `v` the one across it, `slab` the copy's slab number.
 // All four copies give the same answer for every point, so the choice is free.
+struct ZnCnt {  // work counters of one location; only zone_count_kernel<true> reads them (dead code elsewhere)
+    uint32_t cells, records, straddles;
+};
 __device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, uint32_t info, uint32_t bin_off, uint32_t slab,
-                                                 double px, double py) {
+                                                 double px, double py, ZnCnt &cnt) {
     const ZnD4 *er = (const ZnD4 *)(a.blob + a.h.off_bin_items);  // edge records, 32 B each (one sector)
     uint32_t k, k1;
     if (info & ZC_RANGES) {
@@ -586,9 +617,11 @@ __device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, uint32_t info,
         // one 256-bit load per edge record: every lane reads a different record, so the cost is L1
         // wavefronts per load instruction, not bytes
         const ZnD4 e = zn_ld256(er + k);  // p1 = (x,y)  p2 = (z,w)
+        cnt.records++;
         if (e.x < px && e.z < px) break;  // slab edges are ordered by max x, descending: the rest are left too
         const bool up1 = e.y > py, up2 = e.w > py;
         if (up1 != up2) {
+            cnt.straddles++;
             // sign of x1*y2 - y1*x2 on the translated coordinates, flipped when y2 < y1.  With the ends on
             // different sides, y2 < y1 is exactly `up1` (a difference of unequal doubles never rounds to 0),
             // and rounded products that differ already order the exact ones (see zn_sign_det).
@@ -614,7 +647,7 @@ __device__ __forceinline__ bool zn_ring_interior(const ZnArgs &a, uint32_t info,
 
 // Visit the tests whose polygon contains (px,py), in ascending test order.
 template <typename F>
-__device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, double py, F f) {
+__device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, double py, ZnCnt &cnt, F f) {
     const ZoneHeader &h = a.h;
     if (!(px >= h.gx0 && px <= h.gx1 && py >= h.gy0 && py <= h.gy1)) return;  // outside every envelope (or NaN)
     uint32_t cx = zn_cell(px, h.gx0, h.inv_cx, h.grid_nx), cy = zn_cell(py, h.gy0, h.inv_cy, h.grid_ny);
@@ -630,6 +663,7 @@ __device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, d
     }
     for (uint32_t k = 0;;) {
         const uint32_t t = (uint32_t)__double2loint(r.w), info = (uint32_t)__double2hiint(r.w);
+        cnt.cells++;
         bool in;
         if (info & ZC_RECT) {  // RectangleContains: inside the exact envelope and not on its border
             const ZnD4 ev = zn_ld256((const ZoneTestRec *)(a.blob + h.off_tests) + t);
@@ -641,12 +675,16 @@ __device__ __forceinline__ void zn_for_each_inside(const ZnArgs &a, double px, d
             const double sy = (double)__int_as_float(i16 << 16), sx = (double)__int_as_float(i16 & 0xffff0000u);
             const double tl = zn_cell_pos(px, r.x, sx), tb = zn_cell_pos(py, r.y, sy);
             const double tr = (double)nb - tl, tt = (double)nb - tb;
-            const bool alongy = fmin(tb, tt) < fmin(tl, tr);
-            const bool neg = alongy ? tb < tt : tl < tr;
+            bool alongy = !(info & ZC_XONLY) && fmin(tb, tt) < fmin(tl, tr);
+            bool neg = alongy ? tb < tt : tl < tr;
+            if (a.force_ray) {  // tests only: walk the given copy whatever the flags say
+                alongy = ((a.force_ray - 1u) >> 1) != 0;
+                neg = ((a.force_ray - 1u) & 1u) != 0;
+            }
             // ray along x: slabs by y (copies 0 .. 2nb-1); along y: slabs by x (copies 2nb .. 4nb-1)
             const uint32_t sl = alongy ? nb + zn_cell_clamp(tl, nb) : zn_cell_clamp(tb, nb);
             const double u = alongy ? py : px, v = alongy ? px : py;
-            in = zn_ring_interior(a, info, (uint32_t)__double2hiint(r.z), 2u * sl + (neg ? 1u : 0u), neg ? -u : u, v);
+            in = zn_ring_interior(a, info, (uint32_t)__double2hiint(r.z), 2u * sl + (neg ? 1u : 0u), neg ? -u : u, v, cnt);
         }
         if (in) f(t, info & ZC_OUTSIDE);
         if (++k >= n) break;
@@ -680,7 +718,8 @@ __device__ __forceinline__ void zn_eval_point(const ZnArgs &a, bool valid, doubl
     L.n_in = 0;
     uint32_t n_in_icond = 0, n_in_ocond = 0;
     if (valid) {
-        zn_for_each_inside(a, L.px, L.py, [&](uint32_t t, uint32_t outside_cond) {
+        ZnCnt cnt{0, 0, 0};
+        zn_for_each_inside(a, L.px, L.py, cnt, [&](uint32_t t, uint32_t outside_cond) {
             if (L.n_in < ZN_MAXIN) L.ins[L.n_in] = (t << 1) | outside_cond;
             L.n_in++;
             if (outside_cond)
@@ -738,7 +777,8 @@ __device__ __forceinline__ void zn_emit(const ZnArgs &a, uint32_t i, const ZnLoc
             const ZoneTestRec *tests = (const ZoneTestRec *)(a.blob + a.h.off_tests);
             for (uint32_t t = 0; t < a.h.n_tests; t++) {
                 bool in = false;
-                zn_for_each_inside(a, px, py, [&](uint32_t tt, uint32_t) {
+                ZnCnt cnt{0, 0, 0};
+                zn_for_each_inside(a, px, py, cnt, [&](uint32_t tt, uint32_t) {
                     if (tt == t) in = true;
                 });
                 bool outside_cond = (__ldg(&tests[t].flags) & 1u) != 0;
@@ -783,8 +823,12 @@ struct ZnWork {
     uint64_t *park;       // [n] bits 0..1: alerts (3 = "see bits 2.."), then either two 31-bit test ids or the count
     uint64_t *tile_tot;   // [ntiles]
     uint64_t *tile_base;  // [ntiles]
+    unsigned long long *stats;  // [3] cell records, edge records, straddle tests (zone_count_kernel<true> only)
 };
 
+// STATS = true: the same kernel, also summing how many cell records, edge records and straddle tests the
+// batch took (bench.py reports the zone stage in those units; the timed kernel is STATS = false).
+template <bool STATS>
 __global__ void __launch_bounds__(ZN_THREADS, 6) zone_count_kernel(ZnArgs a, ZnWork w) {
     __shared__ uint32_t s_part[ZN_THREADS / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -793,8 +837,9 @@ __global__ void __launch_bounds__(ZN_THREADS, 6) zone_count_kernel(ZnArgs a, ZnW
     // only the count and the first two containing tests are kept here; a location with more alerts (or
     // with Outside-condition tests) is evaluated again by the emit kernel
     uint32_t id0 = 0, id1 = 0, n_in = 0, n_oc = 0, count = 0;
+    ZnCnt cnt{0, 0, 0};
     if (zn_row_valid(a, i, n_live)) {
-        zn_for_each_inside(a, __ldg(a.lon + i), __ldg(a.lat + i), [&](uint32_t t, uint32_t outside_cond) {
+        zn_for_each_inside(a, __ldg(a.lon + i), __ldg(a.lat + i), cnt, [&](uint32_t t, uint32_t outside_cond) {
             if (n_in == 0) id0 = t;
             if (n_in == 1) id1 = t;
             n_in++;
@@ -808,6 +853,20 @@ __global__ void __launch_bounds__(ZN_THREADS, 6) zone_count_kernel(ZnArgs a, ZnW
             w.park[i] = (uint64_t)count | ((uint64_t)id0 << 2) | ((uint64_t)id1 << 33);
         else
             w.park[i] = 3u | ((uint64_t)count << 2);
+    }
+    if (STATS) {
+        uint32_t c0 = cnt.cells, c1 = cnt.records, c2 = cnt.straddles;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            c0 += __shfl_xor_sync(SW_FULL, c0, o);
+            c1 += __shfl_xor_sync(SW_FULL, c1, o);
+            c2 += __shfl_xor_sync(SW_FULL, c2, o);
+        }
+        if (lane == 0) {
+            atomicAdd(w.stats + 0, (unsigned long long)c0);
+            atomicAdd(w.stats + 1, (unsigned long long)c1);
+            atomicAdd(w.stats + 2, (unsigned long long)c2);
+        }
     }
     uint32_t s = count;
 #pragma unroll
@@ -992,9 +1051,11 @@ int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const u
     // work area: one parked word (8 B) per location, totals and bases (8 B each) per tile
     const size_t off_tot = ((size_t)n * 8 + 255) / 256 * 256;
     const size_t off_base = off_tot + (size_t)ntiles * 8;
-    const size_t work_bytes = off_base + (size_t)ntiles * 8;
+    const size_t off_stats = off_base + (size_t)ntiles * 8;
+    const size_t work_bytes = off_stats + 32;
     if (int rc = sw_ensure(ctx, ctx->d_zwork, work_bytes)) return rc;
     ZnWork w;
+    w.stats = (unsigned long long *)((uint8_t *)ctx->d_zwork.p + off_stats);
     w.park = (uint64_t *)ctx->d_zwork.p;
     w.tile_tot = (uint64_t *)((uint8_t *)ctx->d_zwork.p + off_tot);
     w.tile_base = (uint64_t *)((uint8_t *)ctx->d_zwork.p + off_base);
@@ -1012,11 +1073,17 @@ int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const u
     a.ticket = nullptr;
     a.tile_state = nullptr;
     a.row_base = row_base;
-    zone_count_kernel<<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a, w);
+    a.force_ray = ctx->opt_zone_force_ray;
+    if (ctx->opt_zone_stats) {
+        SW_CUDA(ctx, cudaMemsetAsync(w.stats, 0, 24, ctx->stream));
+        zone_count_kernel<true><<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a, w);
+        SW_CUDA(ctx, cudaMemcpyAsync(ctx->zone_stats, w.stats, 24, cudaMemcpyDeviceToHost, ctx->stream));
+        ctx->zone_stats[3] = n;
+    } else
+        zone_count_kernel<false><<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a, w);
     SW_CUDA(ctx, cudaGetLastError());
-    // (SWGPU_ZONE_SCAN=seq forces the sequential kernel: lets the tests cover it without a 67 M batch)
-    const char *scan_env = getenv("SWGPU_ZONE_SCAN");
-    if (ntiles <= ZS_MC_MAX_TILES && !(scan_env && scan_env[0] == 's'))
+    // (option "zone.scan_sequential" forces the sequential kernel: lets the tests cover it without a 67 M batch)
+    if (ntiles <= ZS_MC_MAX_TILES && !ctx->opt_zone_scan_sequential)
         zone_scan_mc_kernel<<<(ntiles + ZS_THREADS - 1) / ZS_THREADS, ZS_THREADS, 0, ctx->stream>>>(w.tile_tot, w.tile_base,
                                                                                                   ntiles, n_pairs_dev);
     else
@@ -1024,6 +1091,15 @@ int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const u
     SW_CUDA(ctx, cudaGetLastError());
     zone_emit_kernel<<<(ntiles + ZN_THREADS / 32 - 1) / (ZN_THREADS / 32), ZN_THREADS, 0, ctx->stream>>>(a, w);
     SW_CUDA(ctx, cudaGetLastError());
+    return SWGPU_OK;
+}
+
+// Work counters of the last zone test run with option "zone.stats" = 1 (synchronises the stream).
+extern "C" int32_t swgpu_zone_stats(swgpu_ctx *ctx, uint64_t out[4]) {
+    if (!ctx || !out) return SWGPU_E_INVALID;
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < 4; k++) out[k] = ctx->zone_stats[k];
     return SWGPU_OK;
 }
 
@@ -1158,6 +1234,7 @@ extern "C" int32_t swgpu_zone_test_noalloc_dev(swgpu_ctx *ctx, const double *lon
     a.ticket = (uint32_t *)scratch;
     a.tile_state = (uint64_t *)((uint8_t *)scratch + SW_SCRATCH_HDR);
     a.row_base = nullptr;
+    a.force_ray = ctx->opt_zone_force_ray;
     zone_test_kernel<<<ntiles, ZN_THREADS, 0, ctx->stream>>>(a);
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;

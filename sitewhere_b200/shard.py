@@ -60,6 +60,10 @@ def broadcast_zone_table(ctx, dist, device, rank: int, src: int = 0):
         ctx.zone_table_export(blob)
     dist.broadcast(blob, src)
     if rank != src:
+        # NCCL broadcasts are ordered against torch's CURRENT stream only and return before the bytes have
+        # landed; the import copies on the context's own (non-blocking) stream.  Wait for the receive first.
+        if getattr(device, "type", str(device)) == "cuda":
+            torch.cuda.current_stream(device).synchronize()
         ctx.zone_table_import(blob, nbytes)
     return nbytes
 

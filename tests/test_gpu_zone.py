@@ -108,15 +108,22 @@ def test_meta_filter_capacity_and_empty(ctx):
 
 
 def test_degenerate_zones(ctx):
-    """zero-area and collinear rings, duplicate vertices, a single-vertex zone"""
-    vo = np.array([0, 1, 3, 7, 11], np.uint32)
-    zlon = np.array([1.0,  0.0, 2.0,  0.0, 1.0, 1.0, 0.0,  0.0, 2.0, 4.0, 2.0])
-    zlat = np.array([1.0,  0.0, 2.0,  0.0, 0.0, 1.0, 1.0,  0.0, 0.0, 0.0, 0.0])
-    cond = np.array([0, 0, 0, 1], np.uint8)
+    """zero-area and collinear rings, duplicate vertices; zones JTS cannot construct are refused"""
+    vo = np.array([0, 3, 7, 11], np.uint32)
+    zlon = np.array([0.0, 2.0, 0.0,  0.0, 1.0, 1.0, 0.0,  0.0, 2.0, 4.0, 2.0])
+    zlat = np.array([0.0, 2.0, 0.0,  0.0, 0.0, 1.0, 1.0,  0.0, 0.0, 0.0, 0.0])
+    cond = np.array([0, 0, 1], np.uint8)
     rng = np.random.default_rng(3)
     lon = np.concatenate([zlon, rng.uniform(-1, 5, 500), [1.0, 0.5, 3.0]])
     lat = np.concatenate([zlat, rng.uniform(-1, 3, 500), [1.0, 0.5, 0.0]])
     run_both(ctx, (vo, zlon, zlat, cond), lon, lat)
+    # 1 or 2 bounds close to a ring of 2 or 3 points: LinearRing's constructor throws in the reference
+    from sitewhere_b200._lib import SwgpuError
+    for nb in (1, 2):
+        with pytest.raises(SwgpuError, match="at least 3"):
+            ctx.set_zones(np.array([0, nb], np.uint32), zlon[:nb], zlat[:nb], np.zeros(1, np.uint8))
+    want, total = oracle.zone_test(vo, zlon, zlat, cond, lon[:10], lat[:10])
+    assert np.array_equal(ctx.zone_test(lon[:10], lat[:10]), want)   # the previous table is still in place
 
 
 def _comb(x0, y0, teeth, tall):
@@ -173,3 +180,97 @@ def test_coordinates_beyond_float_range_and_float_envelope_margin(ctx):
     lat = np.concatenate([ys, rng.uniform(0.09, 0.71, 2000), rng.uniform(-1, 4, 500) * 1e39,
                           rng.uniform(0.9, 1.6, 500) * big, rng.uniform(-0.1, 1.1, 500) * tiny])
     run_both(ctx, (vo, zlon, zlat, cond), lon, lat)
+
+
+# ---- the walk's choice of ray against the reference's single +x ray ------------------------------------------
+# JTS 1.13 RayCrossingCounter casts one ray (+x) and takes the sign of the determinant of the coordinates
+# translated IN DOUBLE (oracle/sw_oracle.c ring_interior).  The kernel walks whichever of four axis-parallel
+# rays leaves the envelope soonest (zone.cu build_zone_blob explains when that is provably the same answer
+# and flags the other zones ZC_XONLY).  Here every ray is forced in turn on points a few ulps around edge
+# midpoints, points on edges and vertices of oblique edges.
+def _ulp_shift(x, k):
+    """x moved by k units in the last place (k may be an array)"""
+    i = np.ascontiguousarray(x, np.float64).view(np.int64)
+    lo = np.int64(-(2 ** 63))
+    o = np.where(i >= 0, i, lo - i) + np.asarray(k, np.int64)
+    return np.where(o >= 0, o, lo - o).astype(np.int64).view(np.float64)
+
+
+def _near_edge_points(vo, zlon, zlat, rng, kmax=8):
+    T = len(vo) - 1
+    ks = np.arange(-kmax, kmax + 1)
+    xs, ys = [], []
+    for t in range(T):
+        a, b = int(vo[t]), int(vo[t + 1])
+        x1, y1 = zlon[a:b], zlat[a:b]
+        x2, y2 = np.roll(x1, -1), np.roll(y1, -1)
+        tt = rng.uniform(0.05, 0.95, size=x1.shape[0])
+        for bx, by in (((x1 + x2) / 2, (y1 + y2) / 2),            # edge midpoints
+                       (x1 + tt * (x2 - x1), y1 + tt * (y2 - y1)),  # a point on (next to) each edge
+                       (x1, y1)):                                   # the vertices
+            xs.append(_ulp_shift(bx[:, None], ks[None, :]).ravel()); ys.append(np.repeat(by, ks.size))
+            xs.append(np.repeat(bx, ks.size)); ys.append(_ulp_shift(by[:, None], ks[None, :]).ravel())
+            kd = rng.integers(-kmax, kmax + 1, size=(bx.size, 4, 2))
+            xs.append(_ulp_shift(bx[:, None], kd[:, :, 0]).ravel()); ys.append(_ulp_shift(by[:, None], kd[:, :, 1]).ravel())
+    return np.concatenate(xs), np.concatenate(ys)
+
+
+def _mismatches(ctx, zones, lon, lat, force):
+    ctx.set_option("zone.force_ray", force)
+    try:
+        got = ctx.zone_test(lon, lat, max_pairs=max(4 * lon.shape[0], 1024))
+    finally:
+        ctx.set_option("zone.force_ray", 0)
+    want, total = oracle.zone_test(*zones, lon, lat, max_pairs=max(4 * lon.shape[0], 1024))
+    if got.shape[0] == total and np.array_equal(got, want):
+        return 0
+    return int(np.setxor1d(got, want).shape[0])
+
+
+def test_near_edge_all_directions(ctx):
+    rng = np.random.default_rng(77)
+    report = {}
+    # (1) zones where every vertex - point difference is exact (Sterbenz): all four rays must agree with +x
+    zones = S.star_zones(26, nvert=16, seed=31)      # 676 zones, 10,816 oblique edges
+    ctx.set_zones(*zones)
+    lon, lat = _near_edge_points(zones[0], zones[1], zones[2], rng)
+    assert lon.shape[0] > 1_000_000
+    for force in (0, 1, 2, 3, 4):
+        bad = _mismatches(ctx, zones, lon, lat, force)
+        report[f"exact_translation_zones/ray{force}"] = bad
+        assert bad == 0, (force, bad)
+    # (2) zones that straddle the axes (differences round): the kernel restricts itself to +-x, which test
+    #     the same edges with the same determinant as the reference.  The +-y rays are measured, not asserted.
+    zones = S.star_zones(12, nvert=16, lon0=-1.0, lon1=3.0, lat0=-0.5, lat1=2.0, seed=32)
+    ctx.set_zones(*zones)
+    lon, lat = _near_edge_points(zones[0], zones[1], zones[2], rng)
+    for force in (0, 1, 2):
+        bad = _mismatches(ctx, zones, lon, lat, force)
+        report[f"rounded_translation_zones/ray{force}"] = bad
+        assert bad == 0, (force, bad)
+    for force in (3, 4):
+        report[f"rounded_translation_zones/ray{force} (not used by the kernel)"] = _mismatches(ctx, zones, lon, lat, force)
+    # (3) thin slivers with nearly collinear vertices around the origin: the geometry in which a rounded
+    #     translation can mis-order a point and an edge
+    vo, zx, zy = [0], [], []
+    for k in range(200):
+        x0, y0 = rng.uniform(-2, 2, 2)
+        dx, dy = rng.uniform(0.2, 1.5, 2) * rng.choice([-1, 1], 2)
+        eps = rng.uniform(1e-17, 1e-13)
+        zx += [x0, x0 + dx, x0 + 2 * dx, x0 + dx]
+        zy += [y0, y0 + dy, y0 + 2 * dy * (1 + eps), y0 + dy * (1 + 1e-9)]
+        vo.append(len(zx))
+    zones = (np.array(vo, np.uint32), np.array(zx), np.array(zy), np.zeros(200, np.uint8))
+    ctx.set_zones(*zones)
+    lon, lat = _near_edge_points(zones[0], zones[1], zones[2], rng)
+    for force in (0, 1, 2):
+        bad = _mismatches(ctx, zones, lon, lat, force)
+        report[f"slivers/ray{force}"] = bad
+        assert bad == 0, (force, bad)
+    for force in (3, 4):
+        report[f"slivers/ray{force} (not used by the kernel)"] = _mismatches(ctx, zones, lon, lat, force)
+    print("near-edge report:", report)
+    import json, os
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(out):
+        json.dump(report, open(os.path.join(out, "near_edge_report.json"), "w"), indent=1)

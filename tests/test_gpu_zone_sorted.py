@@ -59,12 +59,15 @@ def test_sorted_path_rectangles_and_single_cell_grid(ctx):
     run_both(ctx, one, rng.uniform(-0.5, 1.5, 40_000), rng.uniform(-0.5, 1.5, 40_000))
 
 
-def test_sequential_scan_kernel_matches(ctx, monkeypatch):
+def test_sequential_scan_kernel_matches(ctx):
     """batches above 67 M locations scan their tile totals with the single-CTA kernel; force it here"""
     zones = S.star_zones(8, nvert=16, cond_mode="alternate")
     lon, lat = S.locations_for_zones(70_000, *zones[:3], seed=21, boundary_rate=0.01)
     ctx.set_zones(*zones)
     want = ctx.zone_test(lon, lat, max_pairs=70_000 * 40)
-    monkeypatch.setenv("SWGPU_ZONE_SCAN", "seq")
-    got = ctx.zone_test(lon, lat, max_pairs=70_000 * 40)
+    ctx.set_option("zone.scan_sequential", 1)
+    try:
+        got = ctx.zone_test(lon, lat, max_pairs=70_000 * 40)
+    finally:
+        ctx.set_option("zone.scan_sequential", 0)
     assert np.array_equal(got, want) and len(got) > 70_000

@@ -3,15 +3,18 @@ while a batch is in flight (a consumer thread sharing the GPU with other context
 would stall every stream; or a process whose memory budget is already committed to the state table).
 
 Called through the C ABI on device buffers, twice in a row on different batches, and compared with
-swgpu_zone_test_dev: the alert pairs and their count must be identical (bit-exact, as everywhere in
-this suite).  The second call also shows that the shared in-library scratch is cleared between calls.
-This file is collected last so that a failure here cannot hide any other test.
+swgpu_zone_test_dev and with the CPU oracle's index-free loop: the alert pairs and their count must be
+identical (bit-exact, as everywhere in this suite).  The second call also shows that the shared
+in-library scratch is cleared between calls.  One more run fills the fixed scratch completely
+(SWGPU_NOALLOC_MAX_LOCATIONS locations).  This file is collected last so that a failure here cannot
+hide any other test.
 """
 import ctypes as C
 
 import numpy as np
 import pytest
 
+import oracle
 from sitewhere_b200 import _lib as L
 from sitewhere_b200 import synth as S
 
@@ -55,6 +58,39 @@ def test_noalloc_matches_allocating_entry_point_twice_in_a_row(ctx):
         got_n, got = _run(ctx, ctx.zone_test_noalloc_dev, lon_, lat_, meta_, dev)
         assert got_n == want_n and want_n > 0
         assert np.array_equal(got, want)
+        ref, ref_n = oracle.zone_test(*zones, lon_, lat_, meta=meta_)     # and against the checker itself
+        assert got_n == ref_n and np.array_equal(got, ref)
+
+
+def test_noalloc_at_its_documented_limit(ctx):
+    """n = SWGPU_NOALLOC_MAX_LOCATIONS: 65,536 tiles, every byte of the in-library scratch in use"""
+    import torch
+
+    dev = torch.device("cuda", ctx.device)
+    zones = S.star_zones(8, nvert=64)                      # Inside conditions only: ~0.3 alerts per location
+    ctx.set_zones(*zones)
+    n = L.NOALLOC_MAX_LOCATIONS
+    lon, lat = S.locations_for_zones(n, *zones[:3], seed=903, boundary_rate=1e-4)
+    d_lon = torch.from_numpy(lon).to(dev)
+    d_lat = torch.from_numpy(lat).to(dev)
+    res = []
+    for fn in (ctx.zone_test_dev, ctx.zone_test_noalloc_dev):
+        d_pairs = torch.full((n,), -1, dtype=torch.int64, device=dev)
+        d_np = torch.full((1,), -1, dtype=torch.int64, device=dev)
+        fn(d_lon, d_lat, None, n, None, d_pairs, d_np)
+        ctx.sync()
+        total = int(d_np.item())
+        assert 0 < total <= n
+        res.append(d_pairs[:total].cpu().numpy().view(np.uint64))
+    assert np.array_equal(res[0], res[1])
+    # the oracle on the head and the tail of the batch (the last tile is the one that publishes the total)
+    k = 100_000
+    loc = res[1] >> np.uint64(32)
+    for a, b in ((0, k), (n - k, n)):
+        ref, ref_n = oracle.zone_test(*zones, lon[a:b], lat[a:b])
+        got = res[1][(loc >= a) & (loc < b)]
+        assert got.shape[0] == ref_n
+        assert np.array_equal(got - (np.uint64(a) << np.uint64(32)), ref)
 
 
 def test_noalloc_rejects_batches_beyond_its_fixed_scratch(ctx):

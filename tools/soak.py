@@ -33,7 +33,7 @@ while time.time() < t_end:
     T = 120
     vo, zx, zy = [0], [], []
     for t in range(T):
-        nv = int(rng.integers(1, 16)); cx, cy = rng.integers(-20, 20, size=2); span = int(rng.integers(1, 9))
+        nv = int(rng.integers(3, 16)); cx, cy = rng.integers(-20, 20, size=2); span = int(rng.integers(1, 9))
         sc = (1.0, 0.5, 0.125, 3.0)[rnd % 4]
         zx += list((cx + rng.integers(-span, span + 1, size=nv)).astype(np.float64) * sc)
         zy += list((cy + rng.integers(-span, span + 1, size=nv)).astype(np.float64) * sc)
