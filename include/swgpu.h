@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define SWGPU_ABI_VERSION 1
+#define SWGPU_ABI_VERSION 2
 
 /* ---- call-level error codes ------------------------------------------------------------ */
 #define SWGPU_OK 0
@@ -264,13 +264,22 @@ int32_t swgpu_zone_test_noalloc_dev(swgpu_ctx *ctx, const double *lon, const dou
  * State key = (device token bytes, kind, name bytes) where name is the measurement name, the
  * alert type, or empty for a location (lastLocationEventId / lastMeasurementEventIds[name] /
  * lastAlertEventIds[type]).  Per key the winner is the event with the largest sequence number
- * seq_base + row (arrival order, as the reference's sequential loop).  The table keeps, per key,
- * the winner's sequence, 128-bit event id, event date and value.  Keys are compared by BYTES
- * (hashes only pick the bucket).
+ * (arrival order, as the reference's sequential loop).  The table keeps, per key, the winner's sequence,
+ * 128-bit event id, event date and value.  Keys are compared by BYTES (hashes only pick the bucket).
+ * Rows without a device token (SWGPU_F_NULL_TOKEN) or with a null request (SWGPU_F_NULL_REQUEST: the
+ * reference drops them at ES/EventSourcesManager.java:155) do not reach the state.
  *
- * rows come from a decode call on the same `bytes`/`rec_off`; id_hi/id_lo are the event ids the
- * persistence layer assigned (EM/persistence/DeviceEventManagementPersistence.java:82).           */
-int32_t swgpu_state_reserve(swgpu_ctx *ctx, uint64_t max_keys, uint64_t max_key_bytes);
+ * swgpu_merge / swgpu_merge_dev fold rows that a decode call produced on the same `bytes`/`rec_off`:
+ * row r has sequence seq_base + r; id_hi/id_lo[r] are the event ids the persistence layer assigned
+ * (EM/persistence/DeviceEventManagementPersistence.java:82).  Advance seq_base by n_rows.
+ *
+ * Capacity.  The host-buffer calls (swgpu_merge, swgpu_decode_merge) grow the table as needed and return
+ * when the batch is folded.  The *_dev calls only enqueue: they grow the table from a host-side upper bound
+ * before launching, but rows they cannot place (table full after a fan-out of new keys, keys longer than 72
+ * bytes when the long-key arena is full, token or name beyond 65,535 bytes) are dropped and counted; the next
+ * swgpu_state_size reports that as SWGPU_E_CAPACITY (once).  After swgpu_state_reserve the dropped batches can
+ * be replayed: folding a batch again with the same sequence numbers changes nothing.                    */
+int32_t swgpu_state_reserve(swgpu_ctx *ctx, uint64_t max_keys, uint64_t max_long_key_bytes);
 int32_t swgpu_merge(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n_records,
                     const swgpu_decoded_cols *rows, uint32_t n_rows, uint64_t seq_base,
                     const uint64_t *id_hi, const uint64_t *id_lo);
@@ -278,16 +287,30 @@ int32_t swgpu_merge_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
                         uint32_t n_records, const swgpu_decoded_cols *rows, uint32_t n_rows,
                         const uint32_t *n_rows_dev, uint64_t seq_base, const uint64_t *id_hi,
                         const uint64_t *id_lo);
-/* Number of live keys and bytes in the key arena.                                             */
-/* Fused host-buffer call of the device-state consumer: decode the batch and fold every decoded row into the
- * state, rows staying on the GPU.  Replaces, for one poll() batch, DeviceStateProcessingLogic.process
- * (DS/processing/DeviceStateProcessingLogic.java:65-67: unmarshal each record, then processDeviceStateEvent
- * :116-160) — the same result as swgpu_decode_{pb,json} followed by swgpu_merge with seq = seq_base + row.
+/* Fused call of the device-state consumer: decode the batch and fold every decoded row into the state in ONE
+ * kernel — the row's key bytes and payload go from the decoder's registers and shared memory into the table;
+ * no decoded columns are written or read back.  Replaces, for one poll() batch,
+ * DeviceStateProcessingLogic.process (DS/processing/DeviceStateProcessingLogic.java:65-67: unmarshal each
+ * record, then processDeviceStateEvent :116-160).  The state afterwards is what swgpu_decode_{pb,json} followed
+ * by swgpu_merge leaves, with these sequence numbers: row k of record i (k counts the rows of a
+ * DeviceMeasurements fan-out) has  seq_base + (i << SWGPU_SEQ_RECORD_SHIFT) + min(k, 4095)  — arrival order,
+ * independent of how many rows other records yield, so nothing has to be placed in order first.  Advance
+ * seq_base by SWGPU_SEQ_STRIDE(n) per batch.
  * id_hi/id_lo[n]: the persisted event id of each RECORD; a record that decodes to several rows gives all of
- * them its id.  status[n] (may be NULL) as in swgpu_decode_*; *out_rows = rows merged (advance seq_base by it). */
+ * them its id.  status[n] as in swgpu_decode_* (host variant: may be NULL); *out_rows = rows decoded.
+ * swgpu_decode_merge takes HOST pointers and returns when the batch is folded; swgpu_decode_merge_dev takes
+ * DEVICE pointers (payload readable as for swgpu_decode_*_dev), enqueues on the context's stream, and
+ * out_rows_dev is one uint32 on the device.                                                               */
+#define SWGPU_SEQ_RECORD_SHIFT 12
+#define SWGPU_SEQ_STRIDE(n_records) ((uint64_t)(n_records) << SWGPU_SEQ_RECORD_SHIFT)
 int32_t swgpu_decode_merge(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
                            uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo, uint8_t *status,
                            uint32_t *out_rows);
+int32_t swgpu_decode_merge_dev(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
+                               uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo, uint8_t *status,
+                               uint32_t *out_rows_dev);
+/* Number of live keys and the bytes of their public form (see swgpu_state_rows).  Returns SWGPU_E_CAPACITY
+ * (once; the counts are still valid) when a *_dev merge since the last check had to drop rows.          */
 int32_t swgpu_state_size(swgpu_ctx *ctx, uint64_t *n_keys, uint64_t *key_bytes);
 /* Snapshot (host pointers): one row per live key, in unspecified order.  key_off has n_keys+1
  * entries into key_bytes; a key is  token length (2 bytes LE) | kind byte | token bytes | name bytes.               */

@@ -87,6 +87,8 @@ def lib() -> C.CDLL:
         L.orc_state_free.argtypes = [C.c_void_p]
         L.orc_state_merge.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(_ColsStruct), C.c_uint32,
                                       C.c_uint64, C.c_void_p, C.c_void_p]
+        L.orc_state_merge_seq.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(_ColsStruct), C.c_uint32,
+                                          C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_state_size.restype = C.c_uint64
         L.orc_state_size.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
         L.orc_state_snapshot.argtypes = [C.c_void_p] * 8
@@ -199,7 +201,10 @@ class State:
         except Exception:
             pass
 
-    def merge(self, data, rec_off, cols: Cols, seq_base: int, id_hi, id_lo):
+    def merge(self, data, rec_off, cols: Cols, seq_base: int, id_hi, id_lo, seq=None):
+        """Sequential fold of the rows; row r has sequence seq_base + r, or seq_base + seq[r] when given."""
+        if seq is not None:
+            return self._merge_seq(data, rec_off, cols, seq_base, id_hi, id_lo, seq)
         data = _u8(data)
         rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
         id_hi = np.ascontiguousarray(id_hi, dtype=np.uint64)
@@ -207,6 +212,32 @@ class State:
         s = cols.struct()
         lib().orc_state_merge(self._h, data.ctypes.data, rec_off.ctypes.data, C.byref(s), cols.n, seq_base,
                               id_hi.ctypes.data, id_lo.ctypes.data)
+
+    def _merge_seq(self, data, rec_off, cols, seq_base, id_hi, id_lo, seq):
+        data = _u8(data)
+        rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
+        id_hi = np.ascontiguousarray(id_hi, dtype=np.uint64)
+        id_lo = np.ascontiguousarray(id_lo, dtype=np.uint64)
+        seq = np.ascontiguousarray(seq, dtype=np.uint64)
+        s = cols.struct()
+        lib().orc_state_merge_seq(self._h, data.ctypes.data, rec_off.ctypes.data, C.byref(s), cols.n, seq_base,
+                                  seq.ctypes.data, id_hi.ctypes.data, id_lo.ctypes.data)
+
+    def merge_by_record(self, data, rec_off, cols: Cols, total: int, seq_base: int, id_hi_rec, id_lo_rec, shift: int = 12):
+        """The fold swgpu_decode_merge performs: ids per RECORD, row k of record i has sequence
+        seq_base + (i << shift) + min(k, 2**shift - 1)  (include/swgpu.h SWGPU_SEQ_RECORD_SHIFT)."""
+        rec = (cols.meta[:total].view(np.uint64) >> np.uint64(32)).astype(np.int64)
+        first = np.r_[True, rec[1:] != rec[:-1]] if total else np.zeros(0, bool)
+        start = np.maximum.accumulate(np.where(first, np.arange(total), 0)) if total else np.zeros(0, np.int64)
+        k = np.minimum(np.arange(total) - start, (1 << shift) - 1)
+        seq = (rec.astype(np.uint64) << np.uint64(shift)) + k.astype(np.uint64)
+        old_n = cols.n
+        cols.n = total
+        try:
+            self._merge_seq(data, rec_off, cols, seq_base, np.asarray(id_hi_rec, np.uint64)[rec],
+                            np.asarray(id_lo_rec, np.uint64)[rec], seq)
+        finally:
+            cols.n = old_n
 
     def snapshot(self) -> dict:
         kb = C.c_uint64()

@@ -26,6 +26,7 @@
 #define F_HAS_V2 (1u << 8)
 #define F_HAS_NAME (1u << 10)
 #define F_HAS_MESSAGE (1u << 11)
+#define F_NULL_REQUEST (1u << 13)
 
 #define ST_OK 0
 #define ST_DECODE_EXCEPTION 1
@@ -798,6 +799,12 @@ static st_entry *st_get(orc_state *s, const uint8_t *key, uint32_t klen) {
 }
 void orc_state_merge(orc_state *s, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
                      uint32_t n_rows, uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo) {
+    orc_state_merge_seq(s, bytes, rec_off, rows, n_rows, seq_base, NULL, id_hi, id_lo);
+}
+/* seq == NULL: row r has sequence seq_base + r; else seq_base + seq[r] (rows are in arrival order either way) */
+void orc_state_merge_seq(orc_state *s, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
+                         uint32_t n_rows, uint64_t seq_base, const uint64_t *seq, const uint64_t *id_hi,
+                         const uint64_t *id_lo) {
     uint8_t *kb = NULL;
     size_t kcap = 0;
     for (uint32_t r = 0; r < n_rows; r++) {
@@ -806,6 +813,9 @@ void orc_state_merge(orc_state *s, const uint8_t *bytes, const uint64_t *rec_off
         /* only Alert / Location / Measurement touch these fields  :122-127 */
         if (kind > KIND_ALERT) continue;
         if (fl & F_NULL_TOKEN) continue; /* no device -> never reaches device state */
+        /* "request": null decodes to a DecodedDeviceRequest with a null request, which EventSourcesManager
+         * drops before it is sent on (ES/EventSourcesManager.java:155): it never reaches device state */
+        if (fl & F_NULL_REQUEST) continue;
         const uint8_t *rec = bytes + rec_off[m >> 32];
         uint64_t ts = rows->token_span[r], ns = rows->name_span[r];
         uint32_t tl = (uint32_t)(ts >> 32), nl = (kind == KIND_LOCATION) ? 0 : (uint32_t)(ns >> 32);
@@ -822,7 +832,7 @@ void orc_state_merge(orc_state *s, const uint8_t *bytes, const uint64_t *rec_off
         memcpy(kb + 3, rec + (uint32_t)ts, tl);
         if (nl) memcpy(kb + 3 + tl, rec + (uint32_t)ns, nl);
         st_entry *e = st_get(s, kb, (uint32_t)kl);
-        e->seq = seq_base + r; /* sequential: the later event overwrites */
+        e->seq = seq_base + (seq ? seq[r] : r); /* sequential: the later event overwrites */
         e->id_hi = id_hi[r];
         e->id_lo = id_lo[r];
         e->date = rows->event_date[r];

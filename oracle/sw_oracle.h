@@ -69,6 +69,9 @@ orc_state *orc_state_new(void);
 void orc_state_free(orc_state *);
 void orc_state_merge(orc_state *, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
                      uint32_t n_rows, uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo);
+void orc_state_merge_seq(orc_state *, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
+                         uint32_t n_rows, uint64_t seq_base, const uint64_t *seq, const uint64_t *id_hi,
+                         const uint64_t *id_lo);
 uint64_t orc_state_size(orc_state *, uint64_t *key_bytes);
 /* rows sorted by key bytes; key_off has n+1 entries */
 void orc_state_snapshot(orc_state *, uint64_t *seq, uint64_t *id_hi, uint64_t *id_lo,

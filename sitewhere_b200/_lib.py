@@ -30,6 +30,8 @@ F_STR_ESCAPED = 1 << 9
 F_HAS_NAME = 1 << 10
 F_HAS_MESSAGE = 1 << 11
 F_NAME_COERCED = 1 << 12
+F_NULL_REQUEST = 1 << 13
+SEQ_RECORD_SHIFT = 12
 
 
 class SwgpuError(RuntimeError):
@@ -78,6 +80,7 @@ SIGNATURES = {
     "swgpu_state_reserve": (_I32, [_P, _U64, _U64]),
     "swgpu_merge": (_I32, [_P, _P, _P, _U32, _COLS, _U32, _U64, _P, _P]),
     "swgpu_decode_merge": (_I32, [_P, _I32, _P, _P, _U32, _U64, _P, _P, _P, C.POINTER(_U32)]),
+    "swgpu_decode_merge_dev": (_I32, [_P, _I32, _P, _P, _U32, _U64, _P, _P, _P, _P]),
     "swgpu_merge_dev": (_I32, [_P, _P, _P, _U32, _COLS, _U32, _P, _U64, _P, _P]),
     "swgpu_state_size": (_I32, [_P, C.POINTER(_U64), C.POINTER(_U64)]),
     "swgpu_state_snapshot": (_I32, [_P, _U64, _U64, _ROWS, C.POINTER(_U64)]),
@@ -103,7 +106,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.swgpu_abi_version() != 1:
+    if lib.swgpu_abi_version() != 2:
         raise RuntimeError("libswgpu.so ABI version mismatch")
     _lib = lib
     return lib

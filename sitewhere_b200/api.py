@@ -316,6 +316,12 @@ class Context:
             C.byref(rows)))
         return int(rows.value)
 
+    def decode_merge_dev(self, fmt: str, bytes_t, off_t, n, seq_base, id_hi_t, id_lo_t, status_t, n_rows_t):
+        """swgpu_decode_merge_dev: the fused decode + merge kernel on device-resident buffers (async)."""
+        self._check(self.lib.swgpu_decode_merge_dev(self.h, 1 if fmt == "json" else 0, bytes_t.data_ptr(), off_t.data_ptr(),
+                                                    int(n), int(seq_base), id_hi_t.data_ptr(), id_lo_t.data_ptr(),
+                                                    status_t.data_ptr(), n_rows_t.data_ptr()))
+
     def merge_dev(self, bytes_t, off_t, n_records, cols: DeviceCols, n_rows, n_rows_t, seq_base, id_hi_t, id_lo_t):
         s = cols.struct()
         self._check(self.lib.swgpu_merge_dev(self.h, bytes_t.data_ptr(), off_t.data_ptr(), int(n_records), C.byref(s),
@@ -573,7 +579,7 @@ class DeviceStateProcessingLogic:
     def process_records(self, fmt: str, data, rec_off, id_hi, id_lo) -> int:
         """process(List<ConsumerRecord>) on raw record payloads: one fused native call (decode + merge)."""
         rows = self.ctx.decode_merge(fmt, data, rec_off, self.seq, id_hi, id_lo)
-        self.seq += rows
+        self.seq += (len(rec_off) - 1) << L.SEQ_RECORD_SHIFT      # SWGPU_SEQ_STRIDE(n)
         return rows
 
     def snapshot(self):

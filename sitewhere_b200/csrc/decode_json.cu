@@ -13,6 +13,7 @@
 // the StdDateFormat rules.  Rows are placed by the ordered single-pass scan.  HBM-bound by design;
 // what limits it today is instruction issue (byte-at-a-time scanning), see DESIGN.md.
 #include "dparse.cuh"
+#include "merge_table.cuh"
 #include "swgpu_common.cuh"
 
 #define JS_THREADS 128
@@ -35,6 +36,10 @@ struct JsArgs {
     const uint32_t *row_base;
     uint32_t *row_next;
     uint32_t *not_dense;
+    // fused decode + merge (json_decode_merge_kernel): the state table, per-RECORD event ids, sequence base
+    MgTable mt;
+    const uint64_t *id_hi, *id_lo;
+    uint64_t seq_base;
 };
 
 enum { JK_NONE = 0, JK_OBJECT, JK_ARRAY, JK_STRING, JK_INT, JK_FLOAT, JK_TRUE, JK_FALSE, JK_NULL };
@@ -1044,6 +1049,106 @@ __global__ void __launch_bounds__(JS_THREADS) json_decode_kernel(JsArgs a) {
         json_decode_tile<false>(a, tile, smem, s_warp);
         __syncthreads();  // s_tile, s_warp and the staging buffers are reused
     }
+}
+
+// ---- fused decode + merge: the same staging and record decode, the row goes straight into the device-state
+// table (merge_table.cuh) with sequence number seq_base + (record << SWGPU_SEQ_RECORD_SHIFT); no columns.
+__global__ void __launch_bounds__(JS_THREADS) json_decode_merge_kernel(JsArgs a) {
+    extern __shared__ __align__(16) uint8_t smem[];  // JS_WARPS * (JS_WSTAGE + 32)
+    __shared__ MgLocalCnt s_cnt[JS_WARPS];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (lane == 0) s_cnt[warp].keys = s_cnt[warp].bytes = 0;
+    const uint64_t rec0_64 = (uint64_t)blockIdx.x * JS_THREADS + warp * 32;
+    const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
+    const uint32_t nrec = min(32u, a.n - rec0);
+    uint8_t *ws = smem + warp * (JS_WSTAGE + 32);
+    uint64_t r0 = 0, r1 = 0;
+    if (lane < nrec) {
+        r0 = a.rec_off[rec0 + lane];
+        r1 = a.rec_off[rec0 + lane + 1];
+    }
+    const uint64_t b0 = __shfl_sync(SW_FULL, r0, 0);
+    const uint64_t b1 = __shfl_sync(SW_FULL, r1, nrec ? nrec - 1 : 0);
+    const uintptr_t addr = (uintptr_t)(a.bytes + b0);
+    const uint32_t lead = (uint32_t)(addr & 15);
+    const uint64_t span = (uint64_t)lead + (b1 - b0);
+    const bool staged = span <= JS_WSTAGE;
+    if (staged && nrec) {
+        const uint4 *src = (const uint4 *)(addr - lead);
+        uint4 *dst = (uint4 *)ws;
+        const uint32_t nvec = (uint32_t)((span + 15) >> 4);
+        for (uint32_t i = lane; i < nvec; i += 32) dst[i] = sw_ld_stream_u4(src + i);
+    }
+    __syncwarp();
+    uint32_t count = 0;
+    if (lane < nrec) {
+        const uint32_t rec = rec0 + lane;
+        const uint64_t l64 = r1 - r0;
+        const uint32_t len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
+        JsRow r;
+        if (staged)
+            json_decode_record(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, len, a.rec_base + rec, r);
+        else
+            json_decode_record(GmemBytes{a.bytes + r0}, len, a.rec_base + rec, r);
+        a.status[rec] = (uint8_t)r.status;
+        count = r.status == SWGPU_ST_OK ? 1u : 0u;
+        const uint32_t kind = SWGPU_META_KIND(r.meta), fl = SWGPU_META_FLAGS(r.meta);
+        if (count && !(fl & (SWGPU_F_NULL_TOKEN | SWGPU_F_NULL_REQUEST))) {
+            const uint32_t tl = SWGPU_SPAN_LEN(r.tspan), nl = kind == SWGPU_KIND_LOCATION ? 0u : SWGPU_SPAN_LEN(r.nspan);
+            if (tl > 0xffffu || nl > 0xffffu) {
+                atomicAdd(&a.mt.ctr->key_too_long, 1ull);
+            } else {
+                const uint32_t kindbyte = mg_kindbyte(kind, fl);
+                const uint64_t h = mg_mix(r.th, kind == SWGPU_KIND_LOCATION ? 0ull : r.nh, kindbyte);
+                const uint64_t seq1 = a.seq_base + ((uint64_t)(a.rec_base + rec) << SWGPU_SEQ_RECORD_SHIFT) + 1;
+                const uint64_t ihi = __ldg(a.id_hi + rec), ilo = __ldg(a.id_lo + rec);
+                if (staged) {
+                    MgKeyBytes<SmemBytes> key{SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, SWGPU_SPAN_OFF(r.tspan), tl,
+                                              SWGPU_SPAN_OFF(r.nspan), nl};
+                    mg_upsert(a.mt, &s_cnt[warp], h, tl, nl, kindbyte, key, seq1, ihi, ilo, (uint64_t)r.date, r.v0);
+                } else {
+                    MgKeyBytes<GmemBytes> key{GmemBytes{a.bytes + r0}, SWGPU_SPAN_OFF(r.tspan), tl, SWGPU_SPAN_OFF(r.nspan), nl};
+                    mg_upsert(a.mt, &s_cnt[warp], h, tl, nl, kindbyte, key, seq1, ihi, ilo, (uint64_t)r.date, r.v0);
+                }
+            }
+        }
+    }
+    __syncwarp();
+    count = __reduce_add_sync(SW_FULL, count);
+    if (lane == 0) {
+        if (count) atomicAdd(a.out_rows, count);
+        mg_flush_counts(a.mt, &s_cnt[warp]);
+    }
+}
+
+int sw_decode_merge_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, const MgTable &t,
+                                uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo, uint8_t *status,
+                                uint32_t *out_rows_dev) {
+    JsArgs a;
+    memset(&a, 0, sizeof a);
+    a.bytes = bytes;
+    a.rec_off = rec_off;
+    a.n = n;
+    a.status = status;
+    a.out_rows = out_rows_dev;
+    a.mt = t;
+    a.id_hi = id_hi;
+    a.id_lo = id_lo;
+    a.seq_base = seq_base;
+    const int smem = JS_WARPS * (JS_WSTAGE + 32);
+    {
+        static std::mutex mu;
+        static bool done[64] = {false};
+        std::lock_guard<std::mutex> lk(mu);
+        const int d = ctx->device & 63;
+        if (!done[d]) {
+            SW_CUDA(ctx, cudaFuncSetAttribute(json_decode_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            done[d] = true;
+        }
+    }
+    json_decode_merge_kernel<<<(n + JS_THREADS - 1) / JS_THREADS, JS_THREADS, smem, ctx->stream>>>(a);
+    SW_CUDA(ctx, cudaGetLastError());
+    return SWGPU_OK;
 }
 
 int sw_stage_decode(swgpu_ctx *ctx, bool json, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,

@@ -11,6 +11,7 @@
 // payload once + offsets + columns: the dense kernel is HBM-bound.
 #include <algorithm>
 
+#include "merge_table.cuh"
 #include "swgpu_common.cuh"
 
 #define PB_THREADS 256
@@ -34,6 +35,10 @@ struct PbArgs {
     const uint32_t *row_base;
     uint32_t *row_next;
     uint32_t *not_dense;  // raised by the dense pass when some record does not yield exactly one row
+    // fused decode + merge (pb_decode_dense_kernel<true>): the state table, per-RECORD event ids, sequence base
+    MgTable mt;
+    const uint64_t *id_hi, *id_lo;
+    uint64_t seq_base;
 };
 
 template <typename B>
@@ -496,6 +501,33 @@ __device__ __forceinline__ void pb_write_rows(const PbArgs &a, B bytes, const Pb
     }
 }
 
+// Fused decode + merge: the record's rows go straight into the device-state table (merge_table.cuh) instead of
+// the columns.  Row k of record `rec` has sequence number seq_base + (rec << SWGPU_SEQ_RECORD_SHIFT) + min(k,
+// 4095): it does not depend on how many rows other records yield, so no ordered placement is needed.
+template <typename B>
+__device__ __forceinline__ void pb_merge_rows(const PbArgs &a, MgLocalCnt *local, B bytes, const PbOut &o, uint32_t rec) {
+    const uint32_t kind = o.cmd == 3 ? SWGPU_KIND_LOCATION : (o.cmd == 4 ? SWGPU_KIND_ALERT : SWGPU_KIND_MEASUREMENT);
+    const uint32_t kindbyte = mg_kindbyte(kind, o.flags);
+    const uint64_t th = sw_hash64(bytes, o.hw_off, o.hw_len);
+    const uint64_t ihi = __ldg(a.id_hi + rec), ilo = __ldg(a.id_lo + rec);
+    const uint64_t seq0 = a.seq_base + ((uint64_t)(a.rec_base + rec) << SWGPU_SEQ_RECORD_SHIFT) + 1;
+    for (uint32_t k = 0; k < o.count; k++) {
+        uint32_t noff = o.name_off, nlen = o.name_len;
+        uint64_t v0 = o.v0;
+        if (k > 0) pb_nth_measurement(bytes, o, k, noff, nlen, v0);
+        const uint32_t nl = kind == SWGPU_KIND_LOCATION ? 0u : nlen;
+        if (o.hw_len > 0xffffu || nl > 0xffffu) {
+            atomicAdd(&a.mt.ctr->key_too_long, 1ull);
+            continue;
+        }
+        const uint64_t nh = kind == SWGPU_KIND_LOCATION ? 0ull : sw_hash64(bytes, noff, nlen);
+        MgKeyBytes<B> key{bytes, o.hw_off, o.hw_len, noff, nl};
+        mg_upsert(a.mt, local, mg_mix(th, nh, kindbyte), o.hw_len, nl, kindbyte, key,
+                  seq0 + (k < (1u << SWGPU_SEQ_RECORD_SHIFT) - 1 ? k : (1u << SWGPU_SEQ_RECORD_SHIFT) - 1), ihi, ilo,
+                  (uint64_t)o.date, v0);
+    }
+}
+
 // ---- ordered pass (exact redo).  A CTA owns a tile of 256 consecutive records (its position in the ordered
 // scan); inside it every WARP stages the contiguous bytes of its own 32 records into its private slice of
 // shared memory (coalesced 16-byte streaming loads, __syncwarp only) and each lane walks one record.  The only
@@ -657,9 +689,14 @@ __device__ __forceinline__ bool pd_issue(const PbArgs &a, uint32_t wt, uint32_t 
     return go;
 }
 
+// MERGE = false: rows -> columns (swgpu_decode_pb[_dev]).  MERGE = true: rows -> device-state table
+// (swgpu_decode_merge[_dev]): no columns, no first_row, no ordered redo; *out_rows counts the decoded rows.
+template <bool MERGE>
 __global__ void __launch_bounds__(PB_THREADS) pb_decode_dense_kernel(PbArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];  // PB_WARPS * 2 * (PD_STAGE + 32)
     __shared__ __align__(8) uint64_t s_bar[PB_WARPS][2];
+    __shared__ MgLocalCnt s_cnt[PB_WARPS];
+    uint32_t my_rows = 0;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t nwt = (a.n + 31u) / 32u;  // warp tiles in the batch
     const uint32_t first = (blockIdx.x * PB_WARPS + warp) * PD_TILES;
@@ -670,6 +707,7 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_dense_kernel(PbArgs a) {
         pd_bar_init(&bar[0]);
         pd_bar_init(&bar[1]);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        s_cnt[warp].keys = s_cnt[warp].bytes = 0;
     }
     __syncwarp();
     const uint64_t row_base = a.row_base ? (uint64_t)__ldg(a.row_base) : 0ull;  // rows of earlier chunks
@@ -705,26 +743,43 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_dense_kernel(PbArgs a) {
             else
                 pb_parse_record(GmemBytes{a.bytes + cur.r0}, len, o);
             const uint32_t rec = g.rec0 + lane;
-            const uint64_t row0 = rec;  // row index = record index
-            if (o.count != 1) atomicOr(a.not_dense, 1u);
             a.status[rec] = (uint8_t)o.status;
-            a.first_row[rec] = (uint32_t)(row_base + row0);
-            if (o.count == 1) {
-                if (g.staged)
-                    pb_write_rows(a, SmemBytes{ws + g.lead + (uint32_t)(cur.r0 - g.b0)}, o, rec, row0);
-                else
-                    pb_write_rows(a, GmemBytes{a.bytes + cur.r0}, o, rec, row0);
-            }
-            if (rec == a.n - 1) {  // the last record of the batch
-                a.first_row[a.n] = (uint32_t)(row_base + a.n);
-                *a.out_rows = a.n;
-                if (a.row_next) *a.row_next = (uint32_t)(row_base + a.n);
+            if (MERGE) {
+                my_rows += o.count;
+                if (o.count) {
+                    if (g.staged)
+                        pb_merge_rows(a, &s_cnt[warp], SmemBytes{ws + g.lead + (uint32_t)(cur.r0 - g.b0)}, o, rec);
+                    else
+                        pb_merge_rows(a, &s_cnt[warp], GmemBytes{a.bytes + cur.r0}, o, rec);
+                }
+            } else {
+                const uint64_t row0 = rec;  // row index = record index
+                if (o.count != 1) atomicOr(a.not_dense, 1u);
+                a.first_row[rec] = (uint32_t)(row_base + row0);
+                if (o.count == 1) {
+                    if (g.staged)
+                        pb_write_rows(a, SmemBytes{ws + g.lead + (uint32_t)(cur.r0 - g.b0)}, o, rec, row0);
+                    else
+                        pb_write_rows(a, GmemBytes{a.bytes + cur.r0}, o, rec, row0);
+                }
+                if (rec == a.n - 1) {  // the last record of the batch
+                    a.first_row[a.n] = (uint32_t)(row_base + a.n);
+                    *a.out_rows = a.n;
+                    if (a.row_next) *a.row_next = (uint32_t)(row_base + a.n);
+                }
             }
         }
         __syncwarp();  // every lane is done reading this buffer: it is refilled two tiles from now
         cur = nxt;
         nxt = nn;
         cur_copy = nxt_copy;
+    }
+    if (MERGE) {
+        my_rows = __reduce_add_sync(SW_FULL, my_rows);
+        if (lane == 0) {
+            if (my_rows) atomicAdd(a.out_rows, my_rows);
+            mg_flush_counts(a.mt, &s_cnt[warp]);
+        }
     }
 }
 
@@ -780,7 +835,9 @@ int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
         const int d = ctx->device & 63;
         if (!done[d]) {
             SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_ordered_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-            SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_dense_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              PB_WARPS * 2 * (PD_STAGE + 32)));
+            SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_dense_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               PB_WARPS * 2 * (PD_STAGE + 32)));
             done[d] = true;
         }
@@ -790,11 +847,44 @@ int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
         const int dsmem = PB_WARPS * 2 * (PD_STAGE + 32);
         const uint32_t nwt = (n + 31u) / 32u;
         const uint32_t per_cta = PB_WARPS * PD_TILES;
-        pb_decode_dense_kernel<<<(nwt + per_cta - 1) / per_cta, PB_THREADS, dsmem, ctx->stream>>>(a);
+        pb_decode_dense_kernel<false><<<(nwt + per_cta - 1) / per_cta, PB_THREADS, dsmem, ctx->stream>>>(a);
     }
     SW_CUDA(ctx, cudaGetLastError());
     const uint32_t nredo = std::min<uint32_t>(ntiles, (uint32_t)ctx->sm_count * 4u);
     pb_decode_ordered_kernel<<<nredo, PB_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
+    SW_CUDA(ctx, cudaGetLastError());
+    return SWGPU_OK;
+}
+
+// Fused decode + merge launch (swgpu_decode_merge[_dev]); the caller (merge.cu) prepared the table.
+int sw_decode_merge_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, const MgTable &t,
+                              uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo, uint8_t *status,
+                              uint32_t *out_rows_dev) {
+    PbArgs a;
+    memset(&a, 0, sizeof a);
+    a.bytes = bytes;
+    a.rec_off = rec_off;
+    a.n = n;
+    a.status = status;
+    a.out_rows = out_rows_dev;
+    a.mt = t;
+    a.id_hi = id_hi;
+    a.id_lo = id_lo;
+    a.seq_base = seq_base;
+    const int dsmem = PB_WARPS * 2 * (PD_STAGE + 32);
+    {
+        static std::mutex mu;
+        static bool done[64] = {false};
+        std::lock_guard<std::mutex> lk(mu);
+        const int d = ctx->device & 63;
+        if (!done[d]) {
+            SW_CUDA(ctx, cudaFuncSetAttribute(pb_decode_dense_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dsmem));
+            done[d] = true;
+        }
+    }
+    const uint32_t nwt = (n + 31u) / 32u;
+    const uint32_t per_cta = PB_WARPS * PD_TILES;
+    pb_decode_dense_kernel<true><<<(nwt + per_cta - 1) / per_cta, PB_THREADS, dsmem, ctx->stream>>>(a);
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
 }

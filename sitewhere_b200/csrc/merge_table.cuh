@@ -24,6 +24,7 @@
 #define MG_KEY_INLINE_WORDS 10u  // header + 9 words (72 bytes) of token and name
 #define MG_PENDING 2ull          // tag bit: the claimer has not published the key words yet
 #define MG_TOMB 4ull             // tag of a slot whose claimer could not store its (long) key: equal to no key
+#define MG_MAX_PROBES 8192ull
 #define MG_HDR_SET (1ull << 63)  // a header is never zero
 #define MG_HDR_LONG (1ull << 62)  // key words are in the arena: word 1 = byte offset, word 2 = word count
 
@@ -38,7 +39,9 @@ struct __align__(128) MgSlot {
 static_assert(sizeof(MgSlot) == 128, "MgSlot layout");
 
 struct MgCounters {  // device
-    unsigned long long n_keys, key_bytes, arena_top, table_full, arena_full, key_too_long, n_fix, fix_overflow;
+    unsigned long long n_keys, key_bytes, arena_top, table_full;
+    unsigned long long arena_full;  // 8-byte words of long keys that did not fit the arena
+    unsigned long long key_too_long, n_fix, fix_overflow;
 };
 struct MgFix {  // a row that must write its payload once more after the launch (see mg_upsert)
     uint64_t slot, seq1, id_hi, id_lo, date, value;
@@ -149,7 +152,10 @@ __device__ __forceinline__ void mg_upsert(const MgTable &t, MgLocalCnt *local, u
     const uint64_t want = (h & ~7ull) | 1ull;
     uint64_t s = (h >> 3) & t.mask;
     bool found = false, inserted = false, dropped = false;
-    for (uint64_t probes = 0; probes <= t.mask; probes++, s = (s + 1) & t.mask) {
+    // (the table is kept at most half full, so probe sequences are short; the bound only keeps a table that a
+    //  device-resident caller overfilled from spinning: such rows are counted in table_full)
+    const uint64_t max_probes = t.mask < MG_MAX_PROBES ? t.mask + 1 : MG_MAX_PROBES;
+    for (uint64_t probes = 0; probes < max_probes; probes++, s = (s + 1) & t.mask) {
         uint64_t *w = t.slots[s].w;
         // optimistic read of sectors 0-1: tag, best and key words 0..5 in one round trip
         const ulonglong2 a0 = mg_ldcg2(w + 0), a1 = mg_ldcg2(w + 2), a2 = mg_ldcg2(w + 4), a3 = mg_ldcg2(w + 6);
@@ -166,10 +172,13 @@ __device__ __forceinline__ void mg_upsert(const MgTable &t, MgLocalCnt *local, u
                 } else {
                     const unsigned long long off = atomicAdd(&t.ctr->arena_top, (unsigned long long)(nw - 1));
                     if (off + (nw - 1) > t.arena_cap) {
-                        // no room for the key words: the slot becomes a tombstone (it cannot be handed back:
-                        // other keys may already have probed past it) and the row is reported as dropped;
-                        // the host grows the arena and replays the batch
-                        atomicAdd(&t.ctr->arena_full, 1ull);
+                        // no room for the key words: the reservation is handed back (an allocation that succeeds
+                        // lies wholly below the end of the arena, one that fails reaches beyond it, so they never
+                        // overlap), the words asked for are counted so that the host can grow the arena and replay
+                        // the batch, and the slot becomes a tombstone (it cannot be freed: other keys may already
+                        // have probed past it)
+                        atomicAdd(&t.ctr->arena_top, (unsigned long long)(0ull - (unsigned long long)(nw - 1)));
+                        atomicAdd(&t.ctr->arena_full, (unsigned long long)(nw - 1));
                         ok = false;
                     } else {
                         for (uint32_t i = 1; i < nw; i++) t.arena[off + i - 1] = key.word(i);

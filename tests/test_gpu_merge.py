@@ -128,9 +128,8 @@ def test_fused_decode_merge_matches_decode_then_merge(ctx):
         rows = ctx.decode_merge("pb", data, rec_off, seq, id_hi, id_lo, status)
         ocols, ostatus, ofirst, total = oracle.decode_pb(data, rec_off)
         assert rows == total and np.array_equal(status, ostatus[:n])
-        rec_of_row = (ocols.meta[:total].view(np.uint64) >> np.uint64(32)).astype(np.int64)
-        st.merge(data, rec_off, ocols, seq, id_hi[rec_of_row], id_lo[rec_of_row])
-        seq += total
+        st.merge_by_record(data, rec_off, ocols, total, seq, id_hi, id_lo)
+        seq += n << 12                      # SWGPU_SEQ_STRIDE(n)
     jrecs = [c[1] for c in json_cases.cases()]
     for i in range(3000):
         jrecs.append(S.json_measurement(S.token_str(i % 97), "fuel.level", repr(float(i) / 7), S.EVENT_DATE_BASE + i))
@@ -142,8 +141,103 @@ def test_fused_decode_merge_matches_decode_then_merge(ctx):
     rows = logic.process_records("json", data, rec_off, id_hi, id_lo)
     ocols, ostatus, ofirst, total = oracle.decode_json(data, rec_off)
     assert rows == total
-    rec_of_row = (ocols.meta[:total].view(np.uint64) >> np.uint64(32)).astype(np.int64)
-    st.merge(data, rec_off, ocols, seq, id_hi[rec_of_row], id_lo[rec_of_row])
+    st.merge_by_record(data, rec_off, ocols, total, seq, id_hi, id_lo)
     snap_equal(ctx.state_snapshot(), st.snapshot())
     assert ctx.decode_merge("pb", np.zeros(0, np.uint8), np.zeros(1, np.uint64), 0, np.zeros(0, np.uint64), np.zeros(0, np.uint64)) == 0
+    ctx.state_clear()
+
+
+def test_long_keys_inline_arena_and_growth(ctx):
+    """keys of every size class: in the slot's first two sectors, in its fourth, and in the long-key arena
+    (which starts small and must grow and replay); 200-byte tokens and names as in ADVICE r1"""
+    ctx.state_clear()
+    st = oracle.State()
+    rng = np.random.default_rng(21)
+    seq = 0
+    for b in range(3):
+        recs = []
+        for i in range(3000):
+            tl = int(rng.choice([1, 7, 8, 21, 36, 40, 64, 65, 200, 300]))
+            nl = int(rng.choice([0, 1, 8, 12, 16, 33, 200]))
+            tok = "t%d_" % (i % 400) + "x" * max(0, tl - 5)
+            name = "n%d_" % (i % 7) + "y" * max(0, nl - 3)
+            recs.append(S.pb_measurements_record(tok, [(name, float(i))], date=1000 * b + i))
+        recs.append(S.pb_measurements_record("\x00" * 16, [("\x00" * 8, 1.5)], date=5))       # all-zero key words
+        recs.append(S.pb_measurements_record("\x00" * 16, [("\x00" * 9, 2.5)], date=6))
+        data, rec_off = S.pack_records(recs)
+        n = len(recs)
+        ids = np.arange(n, dtype=np.uint64) + np.uint64(b * 10_000)
+        if b == 1:                       # unfused path on the same key population
+            res = ctx.decode_pb(data, rec_off)
+            ocols, _, _, total = oracle.decode_pb(data, rec_off)
+            ctx.merge(data, rec_off, res.cols, seq, ids[:total], ids[:total])
+            st.merge(data, rec_off, ocols, seq, ids[:total], ids[:total])
+            seq += total
+        else:
+            rows = ctx.decode_merge("pb", data, rec_off, seq, ids, ids)
+            ocols, _, _, total = oracle.decode_pb(data, rec_off)
+            assert rows == total
+            st.merge_by_record(data, rec_off, ocols, total, seq, ids, ids)
+            seq += n << 12
+    a, b_ = ctx.state_snapshot(), st.snapshot()
+    snap_equal(a, b_)
+    ctx.state_restore(a)
+    snap_equal(ctx.state_snapshot(), b_)
+    ctx.state_clear()
+
+
+def test_null_request_rows_do_not_reach_state(ctx):
+    """JSON "request": null decodes to an OK row flagged NULL_REQUEST; the reference drops it before the state"""
+    ctx.state_clear()
+    recs = [b'{"deviceToken":"d1","type":"DeviceMeasurement","request":null}',
+            S.json_measurement("d1", "fuel.level", "1.5", S.EVENT_DATE_BASE),
+            b'{"deviceToken":"d2","type":"DeviceLocation","request":null}']
+    data, rec_off = S.pack_records(recs)
+    ids = np.arange(3, dtype=np.uint64)
+    rows = ctx.decode_merge("json", data, rec_off, 0, ids, ids)
+    assert rows == 3
+    snap = ctx.state_snapshot()
+    assert snap["seq"].shape[0] == 1 and int(snap["id_lo"][0]) == 1
+    st = oracle.State()
+    ocols, _, _, total = oracle.decode_json(data, rec_off)
+    st.merge_by_record(data, rec_off, ocols, total, 0, ids, ids)
+    snap_equal(snap, st.snapshot())
+    res = ctx.decode_json(data, rec_off)              # and through the unfused path
+    ctx.state_clear()
+    ctx.merge(data, rec_off, res.cols, 0, ids, ids)
+    assert ctx.state_snapshot()["seq"].shape[0] == 1
+    ctx.state_clear()
+
+
+def test_merge_dev_reports_dropped_rows(ctx):
+    """a device-resident merge cannot grow the long-key arena: the drop is reported by swgpu_state_size (once),
+    and after a reserve the replayed batch lands"""
+    import torch
+    from sitewhere_b200._lib import SwgpuError
+    ctx.state_clear()
+    dev = torch.device("cuda", ctx.device)
+    recs = [S.pb_measurements_record("L%04d" % i + "z" * 300, [("m", float(i))], date=i) for i in range(2000)]
+    data, rec_off = S.pack_records(recs)
+    n = len(recs)
+    d_bytes = torch.zeros(data.shape[0] + 64, dtype=torch.uint8, device=dev)
+    d_bytes[: data.shape[0]].copy_(torch.from_numpy(data))
+    d_off = torch.from_numpy(rec_off.view(np.int64)).to(dev)
+    ids = torch.arange(n, dtype=torch.int64, device=dev)
+    d_status = torch.zeros(n, dtype=torch.uint8, device=dev)
+    d_rows = torch.zeros(1, dtype=torch.int32, device=dev)
+    ctx.decode_merge_dev("pb", d_bytes, d_off, n, 0, ids, ids, d_status, d_rows)
+    ctx.sync()
+    assert int(d_rows.item()) == n
+    with pytest.raises(SwgpuError, match="replay"):
+        ctx.state_size()
+    ctx.state_reserve(4 * n, n * 400)
+    ctx.decode_merge_dev("pb", d_bytes, d_off, n, 0, ids, ids, d_status, d_rows)
+    ctx.sync()
+    keys, _ = ctx.state_size()
+    assert keys == n
+    st = oracle.State()
+    ocols, _, _, total = oracle.decode_pb(data, rec_off)
+    idn = np.arange(n, dtype=np.uint64)
+    st.merge_by_record(data, rec_off, ocols, total, 0, idn, idn)
+    snap_equal(ctx.state_snapshot(), st.snapshot())
     ctx.state_clear()

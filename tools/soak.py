@@ -75,9 +75,8 @@ while time.time() < t_end:
     rows = ctx.decode_merge("pb", data, off, seq, ids_hi, ids_lo)
     ocols, ostatus, ofirst, ototal = oracle.decode_pb(data, off)
     assert rows == ototal
-    rec_of_row = (ocols.meta[:ototal].view(np.uint64) >> np.uint64(32)).astype(np.int64)
-    ost.merge(data, off, ocols, seq, ids_hi[rec_of_row], ids_lo[rec_of_row])
-    seq += ototal
+    ost.merge_by_record(data, off, ocols, ototal, seq, ids_hi, ids_lo)
+    seq += len(recs) << 12            # SWGPU_SEQ_STRIDE(n)
     a, b = ctx.state_snapshot(), ost.snapshot()
     for k in ("seq", "id_hi", "id_lo", "event_date", "key_off", "key_bytes"):
         assert np.array_equal(a[k], b[k]), "state mismatch %s round %d seed %d" % (k, rnd, seed)
