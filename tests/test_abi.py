@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, s), f"libswgpu.so does not export {s}"
         assert s in L.SIGNATURES, f"python binding lacks a signature for {s}"
     assert set(L.SIGNATURES) == set(syms)
-    assert lib.swgpu_abi_version() == 1
+    assert lib.swgpu_abi_version() == 2
 
 
 def test_host_partition_helper_matches_kafka_vectors():
