@@ -1058,7 +1058,8 @@ __global__ void __launch_bounds__(JS_THREADS) json_decode_merge_kernel(JsArgs a)
     __shared__ MgLocalCnt s_cnt[JS_WARPS];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (lane == 0) s_cnt[warp].keys = s_cnt[warp].bytes = 0;
-    const uint64_t rec0_64 = (uint64_t)blockIdx.x * JS_THREADS + warp * 32;
+    // newest records first (CTA 0 takes the end of the batch): see pb_decode_dense_kernel<true>
+    const uint64_t rec0_64 = (uint64_t)(gridDim.x - 1 - blockIdx.x) * JS_THREADS + (JS_WARPS - 1 - warp) * 32;
     const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
     const uint32_t nrec = min(32u, a.n - rec0);
     uint8_t *ws = smem + warp * (JS_WSTAGE + 32);

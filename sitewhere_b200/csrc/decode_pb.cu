@@ -699,8 +699,14 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_dense_kernel(PbArgs a) {
     uint32_t my_rows = 0;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t nwt = (a.n + 31u) / 32u;  // warp tiles in the batch
-    const uint32_t first = (blockIdx.x * PB_WARPS + warp) * PD_TILES;
+    // MERGE: newest records first (CTAs start roughly in index order, so CTA 0 takes the END of the batch and
+    // each warp walks its tiles backwards): for a key with several rows in the batch the winner tends to arrive
+    // first and the older rows lose their atomicMax at once, instead of each raising the maximum in turn
+    const uint32_t blk = MERGE ? gridDim.x - 1 - blockIdx.x : blockIdx.x;
+    const uint32_t first = (blk * PB_WARPS + (MERGE ? PB_WARPS - 1 - warp : warp)) * PD_TILES;
     if (first >= nwt) return;
+    const uint32_t cnt = min((uint32_t)PD_TILES, nwt - first);  // tiles of this warp
+    auto tile_of = [&](uint32_t k) -> uint32_t { return k < cnt ? (MERGE ? first + cnt - 1 - k : first + k) : nwt; };
     uint8_t *const slice = smem + (size_t)(warp * 2) * (PD_STAGE + 32);
     uint64_t *const bar = s_bar[warp];
     if (lane == 0) {
@@ -712,19 +718,17 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_dense_kernel(PbArgs a) {
     __syncwarp();
     const uint64_t row_base = a.row_base ? (uint64_t)__ldg(a.row_base) : 0ull;  // rows of earlier chunks
     PdTile cur, nxt, nn;
-    pd_load_offsets(a, first, nwt, lane, cur);
-    pd_load_offsets(a, first + 1, nwt, lane, nxt);
+    pd_load_offsets(a, tile_of(0), nwt, lane, cur);
+    pd_load_offsets(a, tile_of(1), nwt, lane, nxt);
     uint32_t parity = 0;                                           // bit b: phase of buffer b's barrier
-    bool cur_copy = pd_issue(a, first, nwt, lane, cur, slice, &bar[0]);
+    bool cur_copy = pd_issue(a, tile_of(0), nwt, lane, cur, slice, &bar[0]);
 #pragma unroll 1
-    for (uint32_t k = 0; k < PD_TILES; k++) {
-        const uint32_t wt = first + k;
-        if (wt >= nwt) break;  // past the end of the batch
+    for (uint32_t k = 0; k < cnt; k++) {
+        const uint32_t wt = tile_of(k);
         // tile k+1: bytes on their way (the warp's last tile has no successor of its own); tile k+2: offsets requested
         const uint32_t b = k & 1;
-        const bool nxt_copy = pd_issue(a, k + 1 < PD_TILES ? wt + 1 : nwt, nwt, lane, nxt,
-                                       slice + (b ^ 1) * (PD_STAGE + 32), &bar[b ^ 1]);
-        pd_load_offsets(a, k + 2 < PD_TILES ? wt + 2 : nwt, nwt, lane, nn);
+        const bool nxt_copy = pd_issue(a, tile_of(k + 1), nwt, lane, nxt, slice + (b ^ 1) * (PD_STAGE + 32), &bar[b ^ 1]);
+        pd_load_offsets(a, tile_of(k + 2), nwt, lane, nn);
         if (cur_copy) {
             pd_bar_wait(&bar[b], (parity >> b) & 1u);
             parity ^= 1u << b;

@@ -209,12 +209,12 @@ def test_null_request_rows_do_not_reach_state(ctx):
     ctx.state_clear()
 
 
-def test_merge_dev_reports_dropped_rows(ctx):
+def test_merge_dev_reports_dropped_rows():
     """a device-resident merge cannot grow the long-key arena: the drop is reported by swgpu_state_size (once),
     and after a reserve the replayed batch lands"""
     import torch
     from sitewhere_b200._lib import SwgpuError
-    ctx.state_clear()
+    ctx = sw.Context(0)          # a fresh context: its long-key arena has its initial, small size
     dev = torch.device("cuda", ctx.device)
     recs = [S.pb_measurements_record("L%04d" % i + "z" * 300, [("m", float(i))], date=i) for i in range(2000)]
     data, rec_off = S.pack_records(recs)
@@ -240,4 +240,5 @@ def test_merge_dev_reports_dropped_rows(ctx):
     idn = np.arange(n, dtype=np.uint64)
     st.merge_by_record(data, rec_off, ocols, total, 0, idn, idn)
     snap_equal(ctx.state_snapshot(), st.snapshot())
-    ctx.state_clear()
+    assert ctx.state_size()[0] == n      # the drop was reported once; nothing is pending now
+    ctx.close()
