@@ -1,0 +1,64 @@
+// randacc.cu — what B200 gives for the state merge's access pattern: one random 128-byte slot per row in a table
+// of S bytes; per row a 64-byte read (sectors 0-1), optionally an atomicMax on word 1 and a 32-byte store to sector 2.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/exp/randacc tools/exp/randacc.cu && tools/exp/randacc
+// Prints one JSON line per (table size, variant): rows/s.
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+__device__ __forceinline__ uint64_t mix(uint64_t h) {
+    h ^= h >> 33; h *= 0xff51afd7ed558ccdull; h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ull; h ^= h >> 33;
+    return h;
+}
+template <int MODE>  // 0 read 64 B; 1 + atomicMax; 2 + 32-byte store; 3 atomicMax only (no read); 4 read 32 B only
+__global__ void __launch_bounds__(256) k(uint64_t *tab, uint64_t mask, uint64_t n, uint64_t seed, uint64_t *sink) {
+    const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    uint64_t *w = tab + (mix(i + seed) & mask) * 16;
+    uint64_t acc = 0;
+    if (MODE != 3) {
+        ulonglong2 a0 = __ldcg((const ulonglong2 *)w), a1 = __ldcg((const ulonglong2 *)(w + 2));
+        acc = a0.x ^ a0.y ^ a1.x ^ a1.y;
+        if (MODE != 4) {
+            ulonglong2 a2 = __ldcg((const ulonglong2 *)(w + 4)), a3 = __ldcg((const ulonglong2 *)(w + 6));
+            acc ^= a2.x ^ a2.y ^ a3.x ^ a3.y;
+        }
+    }
+    if (MODE == 1 || MODE == 2 || MODE == 3) {
+        const unsigned long long old = atomicMax((unsigned long long *)(w + 1), (unsigned long long)(seed + i + (acc & 1)));
+        acc ^= old;
+    }
+    if (MODE == 2) {
+        *(ulonglong2 *)(w + 8) = make_ulonglong2(i, acc);
+        *(ulonglong2 *)(w + 10) = make_ulonglong2(seed, i);
+    }
+    if (acc == 0x1234567) *sink = acc;
+}
+template <int MODE> float run(uint64_t *tab, uint64_t mask, uint64_t n, uint64_t *sink) {
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; rep++) {
+        cudaEventRecord(e0);
+        k<MODE><<<(unsigned)((n + 255) / 256), 256>>>(tab, mask, n, 1000003ull * (rep + 1), sink);
+        cudaEventRecord(e1); cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        if (rep && ms < best) best = ms;
+    }
+    return best;
+}
+int main() {
+    const uint64_t n = 10000000;
+    uint64_t *sink; cudaMalloc(&sink, 8);
+    const char *names[] = {"read64", "read64+atomicMax", "read64+atomicMax+store32", "atomicMax only", "read32"};
+    for (uint64_t slots = 1ull << 20; slots <= (1ull << 26); slots <<= 2) {  // 128 MB .. 8 GB
+        uint64_t *tab; if (cudaMalloc(&tab, slots * 128) != cudaSuccess) break;
+        cudaMemset(tab, 0, slots * 128);
+        float t[5] = {run<0>(tab, slots - 1, n, sink), run<1>(tab, slots - 1, n, sink), run<2>(tab, slots - 1, n, sink),
+                      run<3>(tab, slots - 1, n, sink), run<4>(tab, slots - 1, n, sink)};
+        for (int m = 0; m < 5; m++)
+            printf("{\"table_MB\": %llu, \"variant\": \"%s\", \"ms_per_10M_rows\": %.4f, \"rows_per_s\": %.4e}\n",
+                   (unsigned long long)(slots * 128 >> 20), names[m], t[m], n / (t[m] * 1e-3));
+        cudaFree(tab);
+    }
+    printf("{\"cuda_error\": \"%s\"}\n", cudaGetErrorString(cudaGetLastError()));
+    return 0;
+}
