@@ -142,6 +142,8 @@ int32_t swgpu_sync(swgpu_ctx *ctx);
  *                           choice (JTS 1.13 casts +x: RayCrossingCounter, called from the zone test at
  *                           RP/processors/geospatial/ZoneTestRuleProcessor.java:50)
  *   "zone.scan_sequential"  1 = scan the per-tile alert counts on one CTA
+ *   "json.fast_path"        0 = every JSON record takes the general structural pass instead of trying the
+ *                           straight-line pass for plainly shaped requests first (default 1)
  *   "zone.stats"            1 = zone tests also count their work (read it with swgpu_zone_stats)        */
 int32_t swgpu_set_option(swgpu_ctx *ctx, const char *name, int64_t value);
 /* Pinned host staging the Java side wraps as a direct ByteBuffer / MemorySegment.             */

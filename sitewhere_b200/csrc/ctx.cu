@@ -159,6 +159,10 @@ extern "C" int32_t swgpu_set_option(swgpu_ctx *ctx, const char *name, int64_t va
         ctx->opt_zone_scan_sequential = value ? 1u : 0u;
         return SWGPU_OK;
     }
+    if (!strcmp(name, "json.fast_path")) {
+        ctx->opt_json_fast = value ? 1u : 0u;
+        return SWGPU_OK;
+    }
     if (!strcmp(name, "zone.stats")) {
         ctx->opt_zone_stats = value ? 1u : 0u;
         return SWGPU_OK;

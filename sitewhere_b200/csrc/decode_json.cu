@@ -40,6 +40,7 @@ struct JsArgs {
     MgTable mt;
     const uint64_t *id_hi, *id_lo;
     uint64_t seq_base;
+    uint32_t fast;  // option "json.fast_path": try the fast structural pass first (default 1)
 };
 
 enum { JK_NONE = 0, JK_OBJECT, JK_ARRAY, JK_STRING, JK_INT, JK_FLOAT, JK_TRUE, JK_FALSE, JK_NULL };
@@ -247,6 +248,181 @@ struct JsonScan {
             return -1;
         }
         return -1;
+    }
+
+    // ---- fast structural pass for the common shape ---------------------------------------------------------------
+    // A request as clients send it: a root object whose members are the four envelope keys (each at most once, any
+    // order), scalar values, "request" an object of known request properties with scalar values; strings are plain
+    // printable ASCII (no escape, no control character, no byte >= 0x80).  For such a record this fills `slots`
+    // exactly as run() does, in straight-line code: no nesting stack, keys taken from two 8-byte loads and matched
+    // as words, strings closed by an 8-byte scan.  ANYTHING else — an unknown or repeated key, a container value, an
+    // escape, odd white space, a grammar error — returns 3 and the caller takes run() from the start, so this
+    // path never decides an error.  Only for records staged in shared memory (8-byte reads may run past the
+    // record's end, into the tile's slack).
+    static __device__ __forceinline__ uint64_t stop_mask(uint64_t w) {  // 0x80 in every byte that ends plain string content
+        const uint64_t l = w & 0x7f7f7f7f7f7f7f7full;
+        const uint64_t q = l ^ 0x2222222222222222ull, bs = l ^ 0x5c5c5c5c5c5c5c5cull;
+        return (w | ~(l + 0x6060606060606060ull) | ~(q + 0x7f7f7f7f7f7f7f7full) | ~(bs + 0x7f7f7f7f7f7f7f7full)) &
+               0x8080808080808080ull;
+    }
+    static __device__ __forceinline__ uint64_t low_bytes(uint64_t w, uint32_t k) {  // the first k (< 8) bytes of w
+        return w & ((1ull << (8 * k)) - 1ull);
+    }
+    static constexpr __device__ uint64_t lit8(const char *lit, uint32_t l) {
+        uint64_t v = 0;
+        for (uint32_t k = 0; k < 8 && k < l; k++) v |= (uint64_t)(uint8_t)lit[k] << (8 * k);
+        return v;
+    }
+    // plain string body from pos (just after the opening quote): false = not plain / not closed inside the record
+    __device__ __forceinline__ bool fast_string(JSlot &s) {
+        const uint32_t start = pos;
+        for (;;) {
+            if (pos >= n) return false;
+            const uint64_t m = stop_mask(b.le64(pos));
+            if (m == 0) {
+                pos += 8;
+                continue;
+            }
+            pos += (uint32_t)(__ffsll((long long)m) - 1) >> 3;
+            break;
+        }
+        if (pos >= n || b.byte(pos) != '"') return false;
+        s.off = start;
+        s.len = pos - start;
+        s.info = JK_STRING;
+        pos++;
+        return true;
+    }
+    __device__ __forceinline__ bool fast_scalar(JSlot &s) {
+        if (pos >= n) return false;
+        const uint32_t c = b.byte(pos), off = pos;
+        if (c == '"') {
+            pos++;
+            return fast_string(s);
+        }
+        uint32_t info;
+        if (c == '-' || (c - '0') <= 9u) {
+            if (!scan_number(info)) return false;
+        } else if (c == 't') {
+            if (!scan_literal("true", 4)) return false;
+            info = JK_TRUE;
+        } else if (c == 'f') {
+            if (!scan_literal("false", 5)) return false;
+            info = JK_FALSE;
+        } else if (c == 'n') {
+            if (!scan_literal("null", 4)) return false;
+            info = JK_NULL;
+        } else
+            return false;
+        s.off = off;
+        s.len = pos - off;
+        s.info = info;
+        return true;
+    }
+    // key at pos (just after its opening quote): slot id, or -1; pos moves past the closing quote
+    __device__ __forceinline__ int fast_key(bool in_request) {
+        if (pos + 2 > n) return -1;
+        const uint64_t k0 = b.le64(pos), k1 = b.le64(pos + 8);
+        const uint64_t m0 = stop_mask(k0);
+        uint32_t kl;
+        if (m0)
+            kl = (uint32_t)(__ffsll((long long)m0) - 1) >> 3;
+        else {
+            const uint64_t m1 = stop_mask(k1);
+            if (!m1) return -1;  // longer than any key we know
+            kl = 8 + ((uint32_t)(__ffsll((long long)m1) - 1) >> 3);
+        }
+        if (pos + kl >= n) return -1;
+        if ((uint32_t)(((kl < 8 ? k0 : k1) >> (8 * (kl & 7))) & 0xff) != '"') return -1;  // stopped on something else
+        int slot = -1;
+        const uint64_t a = kl < 8 ? low_bytes(k0, kl) : k0, c = kl > 8 ? low_bytes(k1, kl - 8) : 0ull;
+        if (!in_request) {
+            switch (kl) {
+            case 4: if (a == lit8("type", 4)) slot = S_TYPE; break;
+            case 7: if (a == lit8("request", 7)) slot = S_REQUEST; break;
+            case 10: if (a == lit8("originat", 8) && c == lit8("or", 2)) slot = S_ORIG; break;
+            case 11: if (a == lit8("deviceTo", 8) && c == lit8("ken", 3)) slot = S_TOKEN; break;
+            }
+        } else {
+            switch (kl) {
+            case 4: slot = a == lit8("name", 4) ? S_NAME : a == lit8("type", 4) ? S_ATYPE : -1; break;
+            case 5: slot = a == lit8("value", 5) ? S_VALUE : a == lit8("level", 5) ? S_LEVEL : -1; break;
+            case 6: if (a == lit8("source", 6)) slot = S_SOURCE; break;
+            case 7: if (a == lit8("message", 7)) slot = S_MSG; break;
+            case 8: if (a == lit8("latitude", 8)) slot = S_LAT; break;  // ("metadata": an object, not for this path)
+            case 9:
+                if (c == lit8("e", 1))
+                    slot = a == lit8("eventDat", 8) ? S_EDATE : a == lit8("eventTyp", 8) ? S_ETYPE : a == lit8("longitud", 8) ? S_LON : -1;
+                else if (c == lit8("n", 1) && a == lit8("elevatio", 8))
+                    slot = S_ELEV;
+                break;
+            case 11:
+                if (a == lit8("updateSt", 8) && c == lit8("ate", 3)) slot = S_UPD;
+                else if (a == lit8("alternat", 8) && c == lit8("eId", 3)) slot = S_ALT;
+                break;
+            }
+        }
+        pos += kl + 1;
+        return slot;
+    }
+    __device__ int run_fast(JSlot *slots) {
+        esc_key = false;
+        req_unknown = false;
+        root_object = true;
+#pragma unroll
+        for (int k = 0; k < S_COUNT; k++) slots[k].info = JK_NONE;
+        skip_ws();
+        if (pos >= n || b.byte(pos) != '{') return 3;
+        pos++;
+        uint32_t seen = 0;
+        for (;;) {  // members of the root object
+            skip_ws();
+            if (pos >= n || b.byte(pos) != '"') return 3;
+            pos++;
+            const int slot = fast_key(false);
+            if (slot < 0 || ((seen >> slot) & 1u)) return 3;
+            seen |= 1u << slot;
+            skip_ws();
+            if (pos >= n || b.byte(pos) != ':') return 3;
+            pos++;
+            skip_ws();
+            if (pos >= n) return 3;
+            if (slot == S_REQUEST && b.byte(pos) == '{') {
+                const uint32_t obj = pos;
+                pos++;
+                for (;;) {  // members of the request object
+                    skip_ws();
+                    if (pos >= n || b.byte(pos) != '"') return 3;
+                    pos++;
+                    const int rs = fast_key(true);
+                    if (rs < 0 || ((seen >> rs) & 1u)) return 3;
+                    seen |= 1u << rs;
+                    skip_ws();
+                    if (pos >= n || b.byte(pos) != ':') return 3;
+                    pos++;
+                    skip_ws();
+                    if (!fast_scalar(slots[rs])) return 3;
+                    skip_ws();
+                    if (pos >= n) return 3;
+                    const uint32_t d = b.byte(pos);
+                    pos++;
+                    if (d == ',') continue;
+                    if (d == '}') break;
+                    return 3;
+                }
+                slots[S_REQUEST].off = obj;
+                slots[S_REQUEST].len = pos - obj;
+                slots[S_REQUEST].info = JK_OBJECT;
+            } else if (!fast_scalar(slots[slot]))
+                return 3;
+            skip_ws();
+            if (pos >= n) return 3;
+            const uint32_t d = b.byte(pos);
+            pos++;
+            if (d == ',') continue;
+            if (d == '}') return 0;
+            return 3;
+        }
     }
 
     // One structural pass over the first JSON value.  0 = ok, 1 = JsonParseException, 2 = nesting too deep.
@@ -728,8 +904,12 @@ struct JsRow {
     uint64_t v0, v1, v2;
 };
 
+// the fast structural pass reads 8 bytes at a time past the record's end: only where the record sits in a staged tile
+template <typename B> struct JsFastOk { static constexpr bool value = false; };
+template <> struct JsFastOk<SmemBytes> { static constexpr bool value = true; };
+
 template <typename B>
-__device__ void json_decode_record(B bytes, uint32_t n, uint32_t rec, JsRow &r) {
+__device__ void json_decode_record(B bytes, uint32_t n, uint32_t rec, JsRow &r, bool FAST = true) {
     r.status = SWGPU_ST_DECODE_EXCEPTION;
     r.meta = r.th = r.nh = r.tspan = r.nspan = r.ospan = r.mspan = r.mdspan = r.aspan = 0;
     r.date = 0;
@@ -748,7 +928,12 @@ __device__ void json_decode_record(B bytes, uint32_t n, uint32_t rec, JsRow &r) 
     sc.b = bytes;
     sc.n = n;
     sc.pos = start;
-    const int rc = sc.run(slots);
+    int rc = 3;
+    if (FAST && JsFastOk<B>::value) rc = sc.run_fast(slots);
+    if (rc == 3) {
+        sc.pos = start;
+        rc = sc.run(slots);
+    }
     if (rc == 2) {
         r.status = SWGPU_ST_PASSTHROUGH;
         return;
@@ -985,9 +1170,9 @@ __device__ __forceinline__ void json_decode_tile(const JsArgs &a, const uint32_t
         const uint64_t l64 = r1 - r0;
         const uint32_t len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
         if (staged)
-            json_decode_record(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, len, a.rec_base + rec0 + lane, r);
+            json_decode_record(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, len, a.rec_base + rec0 + lane, r, a.fast != 0);
         else
-            json_decode_record(GmemBytes{a.bytes + r0}, len, a.rec_base + rec0 + lane, r);
+            json_decode_record(GmemBytes{a.bytes + r0}, len, a.rec_base + rec0 + lane, r, a.fast != 0);
         count = r.status == SWGPU_ST_OK ? 1u : 0u;
     }
     uint64_t tile_total = 0, row;
@@ -1088,9 +1273,9 @@ __global__ void __launch_bounds__(JS_THREADS) json_decode_merge_kernel(JsArgs a)
         const uint32_t len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
         JsRow r;
         if (staged)
-            json_decode_record(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, len, a.rec_base + rec, r);
+            json_decode_record(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, len, a.rec_base + rec, r, a.fast != 0);
         else
-            json_decode_record(GmemBytes{a.bytes + r0}, len, a.rec_base + rec, r);
+            json_decode_record(GmemBytes{a.bytes + r0}, len, a.rec_base + rec, r, a.fast != 0);
         a.status[rec] = (uint8_t)r.status;
         count = r.status == SWGPU_ST_OK ? 1u : 0u;
         const uint32_t kind = SWGPU_META_KIND(r.meta), fl = SWGPU_META_FLAGS(r.meta);
@@ -1136,6 +1321,7 @@ int sw_decode_merge_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint
     a.id_hi = id_hi;
     a.id_lo = id_lo;
     a.seq_base = seq_base;
+    a.fast = ctx->opt_json_fast;
     const int smem = JS_WARPS * (JS_WSTAGE + 32);
     {
         static std::mutex mu;
@@ -1194,6 +1380,7 @@ int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *
     a.row_base = row_base;
     a.row_next = row_next;
     a.not_dense = (uint32_t *)ctx->scratch + 1;
+    a.fast = ctx->opt_json_fast;
     const int smem = JS_WARPS * (JS_WSTAGE + 32);
     {
         // per device, once: the attribute is a property of the loaded function

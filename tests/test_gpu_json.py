@@ -131,3 +131,63 @@ def test_mirror_api(ctx):
         dec.decode(b'{"deviceToken":"t","type":"DeviceMeasurement","request":{"bogus":1}}')
     with pytest.raises(sw.PassThrough):
         dec.decode(b'{"deviceToken":"t","type":"RegisterDevice","request":{}}')
+
+
+def test_fast_structural_pass_equals_general_pass(ctx):
+    """the straight-line pass for plainly shaped requests (option json.fast_path, default on) and the general
+    pass must give identical results: canonical records of the three event types in shuffled key order, with
+    white space, repeated / unknown keys, every known-answer vector, and mutated records"""
+    from tests.test_gpu_fuzz import _mutate, JSON_SPECIALS
+    rnd = random.Random(12)
+    rng = np.random.default_rng(12)
+    recs = [c[1] for c in json_cases.cases()]
+    base = []
+    for i in range(6000):
+        tok = S.token_str(rnd.randrange(500))
+        d = S.EVENT_DATE_BASE + i
+        k = i % 3
+        if k == 0:
+            r = S.json_measurement(tok, rnd.choice(S.MEASUREMENT_NAMES), repr(round(rnd.uniform(-1e3, 1e3), 3)), d)
+        elif k == 1:
+            r = S.json_location(tok, repr(rnd.uniform(34, 35)), repr(rnd.uniform(-85, -84)), "12.5", d)
+        else:
+            r = S.json_alert(tok, rnd.choice(S.ALERT_TYPES), "alert raised", d, level=rnd.choice(["Info", "Error"]))
+        base.append(r)
+    recs += base
+    import json as _json
+    for r in base[:3000]:           # shuffled member order, optional white space, an extra or repeated key now and then
+        o = _json.loads(r)
+        req = list(o["request"].items())
+        rnd.shuffle(req)
+        top = list(o.items())
+        rnd.shuffle(top)
+        sep = rnd.choice([(",", ":"), (", ", ": "), (" , ", " : ")])
+
+        def dump(items):
+            out = []
+            for k, v in items:
+                out.append(_json.dumps(k) + sep[1] + (dump(req) if k == "request" else _json.dumps(v)))
+            return "{" + sep[0].join(out) + "}"
+        txt = dump(top)
+        m = rnd.random()
+        if m < 0.05:
+            txt = txt[:-1] + ',"deviceToken":"again"}'
+        elif m < 0.10:
+            txt = txt[:-1] + ',"extra":[1,{"a":2}]}'
+        elif m < 0.15:
+            txt = txt.replace('"request"' + sep[1] + "{", '"request"' + sep[1] + '{"bogus":1,', 1)
+        recs.append(txt.encode())
+    recs += _mutate(rng, base[:2000], JSON_SPECIALS, 6000, max_mut=2)
+    data, rec_off = S.pack_records(recs)
+    fast = ctx.decode_json(data, rec_off)
+    ctx.set_option("json.fast_path", 0)
+    try:
+        slow = ctx.decode_json(data, rec_off)
+    finally:
+        ctx.set_option("json.fast_path", 1)
+    assert fast.n_rows == slow.n_rows and np.array_equal(fast.status, slow.status)
+    assert np.array_equal(fast.first_row, slow.first_row)
+    from tests.helpers import assert_cols_equal
+    assert_cols_equal(fast.cols, slow.cols, fast.n_rows)
+    check_decode_parity(fast, data, rec_off, fn="decode_json")
+    assert (fast.status == 0).sum() > 7000
