@@ -31,6 +31,27 @@ class _ColsStruct(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in COL_NAMES]
 
 
+ID_NAMES = ["event_hi", "event_lo", "assignment_hi", "assignment_lo", "device_hi", "device_lo"]
+
+
+class _IdsStruct(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ID_NAMES]
+
+
+class EventIds:
+    """ids carried by enriched events, one element per decoded row (orc_event_ids)"""
+
+    def __init__(self, capacity: int):
+        for name in ID_NAMES:
+            setattr(self, name, np.zeros(max(capacity, 1), dtype=np.uint64))
+
+    def struct(self) -> _IdsStruct:
+        s = _IdsStruct()
+        for name in ID_NAMES:
+            setattr(s, name, getattr(self, name).ctypes.data)
+        return s
+
+
 class Cols:
     """Decoded rows as numpy columns (same layout as include/swgpu.h swgpu_decoded_cols)."""
 
@@ -70,6 +91,11 @@ def lib() -> C.CDLL:
                 f.restype = C.c_uint64
                 f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.POINTER(_ColsStruct),
                               C.c_void_p, C.c_void_p]
+        L.orc_decode_enriched.restype = C.c_uint64
+        L.orc_decode_enriched.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.POINTER(_ColsStruct),
+                                          C.POINTER(_IdsStruct), C.c_void_p, C.c_void_p]
+        L.orc_state_merge_enriched.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(_ColsStruct),
+                                               C.POINTER(_IdsStruct), C.c_uint32, C.c_uint64, C.c_void_p]
         if hasattr(L, "orc_json_number_to_double"):
             L.orc_json_number_to_double.restype = C.c_int
             L.orc_json_number_to_double.argtypes = [C.c_char_p, C.c_uint32, C.POINTER(C.c_double)]
@@ -138,6 +164,24 @@ def decode_pb(data, rec_off, max_rows=None):
 
 def decode_json(data, rec_off, max_rows=None):
     return _decode("orc_decode_json", data, rec_off, max_rows)
+
+
+def decode_enriched(data, rec_off, max_rows=None):
+    """GEnrichedEventPayload records -> (cols, ids, status, first_row, total)"""
+    data = _u8(data)
+    rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
+    n = rec_off.shape[0] - 1
+    if max_rows is None:
+        max_rows = max(n, 1)
+    cols = Cols(max_rows)
+    ids = EventIds(max_rows)
+    status = np.zeros(max(n, 1), dtype=np.uint8)
+    first_row = np.zeros(n + 1, dtype=np.uint32)
+    s, si = cols.struct(), ids.struct()
+    total = lib().orc_decode_enriched(data.ctypes.data if data.size else None, rec_off.ctypes.data, n, max_rows, C.byref(s),
+                                      C.byref(si), status.ctypes.data, first_row.ctypes.data)
+    cols.n = min(int(total), max_rows)
+    return cols, ids, status[:n], first_row, int(total)
 
 
 def json_number_to_double(tok: str):
@@ -238,6 +282,17 @@ class State:
                             np.asarray(id_lo_rec, np.uint64)[rec], seq)
         finally:
             cols.n = old_n
+
+    def merge_enriched(self, data, rec_off, cols: Cols, ids: EventIds, total: int, seq_base: int, shift: int = 12):
+        """The fold swgpu_decode_merge performs on enriched records: key token = the assignment id's 16 bytes, event
+        id from the payload, sequence seq_base + (record << shift)."""
+        data = _u8(data)
+        rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
+        rec = (cols.meta[:total].view(np.uint64) >> np.uint64(32))
+        seq = np.ascontiguousarray(rec << np.uint64(shift), dtype=np.uint64)
+        s, si = cols.struct(), ids.struct()
+        lib().orc_state_merge_enriched(self._h, data.ctypes.data, rec_off.ctypes.data, C.byref(s), C.byref(si), total,
+                                       seq_base, seq.ctypes.data)
 
     def snapshot(self) -> dict:
         kb = C.c_uint64()

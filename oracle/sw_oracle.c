@@ -801,10 +801,11 @@ void orc_state_merge(orc_state *s, const uint8_t *bytes, const uint64_t *rec_off
                      uint32_t n_rows, uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo) {
     orc_state_merge_seq(s, bytes, rec_off, rows, n_rows, seq_base, NULL, id_hi, id_lo);
 }
-/* seq == NULL: row r has sequence seq_base + r; else seq_base + seq[r] (rows are in arrival order either way) */
-void orc_state_merge_seq(orc_state *s, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
-                         uint32_t n_rows, uint64_t seq_base, const uint64_t *seq, const uint64_t *id_hi,
-                         const uint64_t *id_lo) {
+/* seq == NULL: row r has sequence seq_base + r; else seq_base + seq[r] (rows are in arrival order either way).
+ * ids != NULL: enriched rows — the token is the assignment id's 16 bytes and the event id comes from `ids`. */
+static void state_merge_any(orc_state *s, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
+                            const orc_event_ids *ids, uint32_t n_rows, uint64_t seq_base, const uint64_t *seq,
+                            const uint64_t *id_hi, const uint64_t *id_lo) {
     uint8_t *kb = NULL;
     size_t kcap = 0;
     for (uint32_t r = 0; r < n_rows; r++) {
@@ -818,8 +819,18 @@ void orc_state_merge_seq(orc_state *s, const uint8_t *bytes, const uint64_t *rec
         if (fl & F_NULL_REQUEST) continue;
         const uint8_t *rec = bytes + rec_off[m >> 32];
         uint64_t ts = rows->token_span[r], ns = rows->name_span[r];
+        uint8_t idkey[16];
+        const uint8_t *tok = rec + (uint32_t)ts;
         uint32_t tl = (uint32_t)(ts >> 32), nl = (kind == KIND_LOCATION) ? 0 : (uint32_t)(ns >> 32);
-        if (tl > 0xffff) continue; /* documented bound of the state key */
+        if (ids) {
+            for (int k = 0; k < 8; k++) {
+                idkey[k] = (uint8_t)(ids->assignment_hi[r] >> (8 * k));
+                idkey[8 + k] = (uint8_t)(ids->assignment_lo[r] >> (8 * k));
+            }
+            tok = idkey;
+            tl = 16;
+        }
+        if (tl > 0xffff || nl > 0xffff) continue; /* documented bound of the state key */
         size_t kl = (size_t)tl + 3 + nl;
         if (kl > kcap) {
             kcap = kl * 2;
@@ -829,16 +840,25 @@ void orc_state_merge_seq(orc_state *s, const uint8_t *bytes, const uint64_t *rec
         kb[0] = (uint8_t)(tl & 0xff);
         kb[1] = (uint8_t)(tl >> 8);
         kb[2] = (uint8_t)(kind | ((kind != KIND_LOCATION && !(fl & F_HAS_NAME)) ? 0x80 : 0));
-        memcpy(kb + 3, rec + (uint32_t)ts, tl);
+        memcpy(kb + 3, tok, tl);
         if (nl) memcpy(kb + 3 + tl, rec + (uint32_t)ns, nl);
         st_entry *e = st_get(s, kb, (uint32_t)kl);
         e->seq = seq_base + (seq ? seq[r] : r); /* sequential: the later event overwrites */
-        e->id_hi = id_hi[r];
-        e->id_lo = id_lo[r];
+        e->id_hi = ids ? ids->event_hi[r] : id_hi[r];
+        e->id_lo = ids ? ids->event_lo[r] : id_lo[r];
         e->date = rows->event_date[r];
         e->value = rows->v0[r];
     }
     free(kb);
+}
+void orc_state_merge_seq(orc_state *s, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
+                         uint32_t n_rows, uint64_t seq_base, const uint64_t *seq, const uint64_t *id_hi,
+                         const uint64_t *id_lo) {
+    state_merge_any(s, bytes, rec_off, rows, NULL, n_rows, seq_base, seq, id_hi, id_lo);
+}
+void orc_state_merge_enriched(orc_state *s, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
+                              const orc_event_ids *ids, uint32_t n_rows, uint64_t seq_base, const uint64_t *seq) {
+    state_merge_any(s, bytes, rec_off, rows, ids, n_rows, seq_base, seq, NULL, NULL);
 }
 uint64_t orc_state_size(orc_state *s, uint64_t *key_bytes) {
     uint64_t kb = 0;

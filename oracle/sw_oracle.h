@@ -40,6 +40,11 @@ typedef struct orc_cols {
         *alternate_id_span;
 } orc_cols;
 
+/* ids carried by an enriched event (one element per decoded row): GDeviceEvent.id, .deviceAssignmentId, .deviceId */
+typedef struct orc_event_ids {
+    uint64_t *event_hi, *event_lo, *assignment_hi, *assignment_lo, *device_hi, *device_lo;
+} orc_event_ids;
+
 uint32_t orc_murmur2(const uint8_t *data, uint32_t len);
 uint32_t orc_partition(const uint8_t *key, uint32_t len, uint32_t n_partitions);
 uint64_t orc_hash64(const uint8_t *data, uint32_t len);
@@ -49,6 +54,9 @@ uint64_t orc_decode_pb(const uint8_t *bytes, const uint64_t *rec_off, uint32_t n
                        const orc_cols *out, uint8_t *status, uint32_t *first_row);
 uint64_t orc_decode_json(const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint64_t max_rows,
                          const orc_cols *out, uint8_t *status, uint32_t *first_row);
+/* GEnrichedEventPayload records (sw_oracle_enriched.c); `ids` may be NULL */
+uint64_t orc_decode_enriched(const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint64_t max_rows,
+                             const orc_cols *out, const orc_event_ids *ids, uint8_t *status, uint32_t *first_row);
 /* one JSON number token -> double bits as Jackson + Double.parseDouble give; returns 0 on ok */
 int orc_json_number_to_double(const char *tok, uint32_t len, double *out);
 /* ISO-8601 / epoch handling of eventDate strings as Jackson StdDateFormat; returns 0 on ok */
@@ -72,6 +80,10 @@ void orc_state_merge(orc_state *, const uint8_t *bytes, const uint64_t *rec_off,
 void orc_state_merge_seq(orc_state *, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
                          uint32_t n_rows, uint64_t seq_base, const uint64_t *seq, const uint64_t *id_hi,
                          const uint64_t *id_lo);
+/* fold of enriched rows: the key's token is the 16 bytes of the assignment id (msb, lsb little-endian), the
+ * event id is the payload's own; seq as in orc_state_merge_seq */
+void orc_state_merge_enriched(orc_state *, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
+                              const orc_event_ids *ids, uint32_t n_rows, uint64_t seq_base, const uint64_t *seq);
 uint64_t orc_state_size(orc_state *, uint64_t *key_bytes);
 /* rows sorted by key bytes; key_off has n+1 entries */
 void orc_state_snapshot(orc_state *, uint64_t *seq, uint64_t *id_hi, uint64_t *id_lo,
