@@ -124,6 +124,15 @@ typedef struct swgpu_decoded_cols {
     uint64_t *alternate_id_span; /* optional (JSON only) */
 } swgpu_decoded_cols;
 
+/* Ids an enriched event carries (GDeviceEvent.id, .deviceAssignmentId, .deviceId: GUUID{msb, lsb},
+ * sitewhere-grpc-model/src/main/proto/sitewhere-common.proto:30-33), one element per decoded row.  Either all six
+ * pointers or none.                                                                                            */
+typedef struct swgpu_event_ids {
+    uint64_t *event_hi, *event_lo;           /* the persisted event's id            */
+    uint64_t *assignment_hi, *assignment_lo; /* the reference's device-state key    */
+    uint64_t *device_hi, *device_lo;
+} swgpu_event_ids;
+
 typedef struct swgpu_ctx swgpu_ctx;
 
 /* ---- context ---------------------------------------------------------------------------- */
@@ -194,6 +203,29 @@ int32_t swgpu_decode_json_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64
                               uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out,
                               uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev);
 
+/* Enriched events: what the rule-processing and device-state consumers read off the "inbound-enriched-events"
+ * topic.  Record i is one serialised GEnrichedEventPayload (proto3;
+ * sitewhere-grpc-event-management/src/main/proto/device-event-model.proto:321-324 with :139-215, :288-296).
+ * Replaces EventModelMarshaler.parseEnrichedEventPayloadMessage (.../grpc/client/event/EventModelMarshaler.java:204-206)
+ * + EventModelConverter.asApiEnrichedEventPayload (.../EventModelConverter.java:1926-1931) as called per record by
+ * DeviceStateProcessingLogic.processRecord (DS/processing/DeviceStateProcessingLogic.java:93-108) and
+ * KafkaRuleProcessorHost (RP/kafka/KafkaRuleProcessorHost.java:170-197).
+ * A record yields one row — kind = the oneof member (measurement / location / alert), eventType ordinal =
+ * GDeviceEvent.eventType, event_date valid iff eventDate != 0, v0/v1/v2 with SWGPU_F_HAS_V* = has{Latitude,
+ * Longitude,Elevation}, name = measurement name / alert type, message, alternateId; token_hash = hash of the 16
+ * bytes (msb, lsb little-endian) of deviceAssignmentId and token_span = 0 — or none: status
+ * SWGPU_ST_DECODE_EXCEPTION when the reference's parse or conversion throws (malformed message, invalid UTF-8 in a
+ * string, an enum number outside the schema, no event set: the consumers log and skip the record), or
+ * SWGPU_ST_PASSTHROUGH for the other event types.  `ids` (may be NULL) receives the ids per row.
+ * The rows feed swgpu_zone_test* unchanged; for the device state use swgpu_decode_merge* with
+ * SWGPU_FMT_ENRICHED (key = assignment id, event id = the payload's own: id_hi / id_lo are ignored).          */
+int32_t swgpu_decode_enriched(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
+                              uint32_t max_rows, const swgpu_decoded_cols *out, const swgpu_event_ids *ids,
+                              uint8_t *status, uint32_t *first_row, uint32_t *out_rows);
+int32_t swgpu_decode_enriched_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
+                                  uint32_t max_rows, const swgpu_decoded_cols *out, const swgpu_event_ids *ids,
+                                  uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev);
+
 /* ---- zone test ------------------------------------------------------------------------------
  * Replaces ZoneTestRuleProcessor.onLocation (RP/processors/geospatial/ZoneTestRuleProcessor.java:47-63)
  * applied to each location: for each test t in list order, inside = JTS-1.13
@@ -233,6 +265,7 @@ int32_t swgpu_zone_stats(swgpu_ctx *ctx, uint64_t out[4]);
  * pointer may be NULL (not copied back); `status` and `first_row` may be NULL too.                  */
 #define SWGPU_FMT_PROTOBUF 0
 #define SWGPU_FMT_JSON 1
+#define SWGPU_FMT_ENRICHED 2 /* records are GEnrichedEventPayload messages (swgpu_decode_enriched) */
 int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off,
                                uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
                                uint32_t *first_row, uint32_t *out_rows, uint64_t max_pairs, uint64_t *pairs,

@@ -194,7 +194,7 @@ static uint32_t pb_read_tag(pbr *r) {
     }
     return t;
 }
-#define PB_MAX_GROUP_DEPTH 16
+#define PB_MAX_GROUP_DEPTH 64
 /* UnknownFieldSetLite.mergeFieldFrom; returns 0 if the field was END_GROUP (caller stops) */
 static int pb_skip_unknown(pbr *r, uint32_t tag, int depth) {
     switch (tag & 7) {

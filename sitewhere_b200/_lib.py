@@ -44,6 +44,13 @@ class DecodedColsStruct(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in COL_NAMES]
 
 
+ID_NAMES = ["event_hi", "event_lo", "assignment_hi", "assignment_lo", "device_hi", "device_lo"]
+
+
+class EventIdsStruct(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ID_NAMES]
+
+
 class StateRowsStruct(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("seq", "id_hi", "id_lo", "event_date", "value", "key_off", "key_bytes")]
 
@@ -54,6 +61,7 @@ _lib = None
 _P, _U32, _U64, _I32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int32
 _COLS = C.POINTER(DecodedColsStruct)
 _ROWS = C.POINTER(StateRowsStruct)
+FMT = {"pb": 0, "json": 1, "enriched": 2}
 SIGNATURES = {
     "swgpu_create": (_I32, [_I32, _P, C.POINTER(_P)]),
     "swgpu_destroy": (None, [_P]),
@@ -72,6 +80,8 @@ SIGNATURES = {
     "swgpu_decode_json": (_I32, [_P, _P, _P, _U32, _U32, _COLS, _P, _P, _P]),
     "swgpu_decode_pb_dev": (_I32, [_P, _P, _P, _U32, _U32, _COLS, _P, _P, _P]),
     "swgpu_decode_json_dev": (_I32, [_P, _P, _P, _U32, _U32, _COLS, _P, _P, _P]),
+    "swgpu_decode_enriched": (_I32, [_P, _P, _P, _U32, _U32, _COLS, C.POINTER(EventIdsStruct), _P, _P, _P]),
+    "swgpu_decode_enriched_dev": (_I32, [_P, _P, _P, _U32, _U32, _COLS, C.POINTER(EventIdsStruct), _P, _P, _P]),
     "swgpu_zone_test": (_I32, [_P, _P, _P, _P, _U32, _U64, _P, _P]),
     "swgpu_zone_test_dev": (_I32, [_P, _P, _P, _P, _U32, _P, _U64, _P, _P]),
     "swgpu_zone_stats": (_I32, [_P, _P]),

@@ -202,6 +202,28 @@ class Context:
     def decode_json(self, data, rec_off, max_rows=None, optional_cols=True) -> DecodeResult:
         return self._decode(self.lib.swgpu_decode_json, data, rec_off, max_rows, optional_cols)
 
+    def decode_enriched(self, data, rec_off, max_rows=None, optional_cols=True):
+        """swgpu_decode_enriched: GEnrichedEventPayload records -> (DecodeResult, ids dict of uint64 arrays)"""
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
+        n = rec_off.shape[0] - 1
+        if max_rows is None:
+            max_rows = max(n, 1)
+        cols = HostCols(max_rows, optional=optional_cols)
+        ids = {k: np.zeros(max_rows, np.uint64) for k in L.ID_NAMES}
+        si = L.EventIdsStruct()
+        for k in L.ID_NAMES:
+            setattr(si, k, ids[k].ctypes.data)
+        status = np.zeros(max(n, 1), dtype=np.uint8)
+        first_row = np.zeros(n + 1, dtype=np.uint32)
+        out_rows = C.c_uint32()
+        s = cols.struct()
+        self._check(self.lib.swgpu_decode_enriched(self.h, data.ctypes.data if data.size else None, rec_off.ctypes.data, n,
+                                                   max_rows, C.byref(s), C.byref(si), status.ctypes.data,
+                                                   first_row.ctypes.data, C.byref(out_rows)))
+        cols.n = int(out_rows.value)
+        return DecodeResult(cols, status[:n], first_row, cols.n), {k: v[: cols.n] for k, v in ids.items()}
+
     # ---- decode (device buffers; async on the context stream) ---------------------------------------
     def decode_pb_dev(self, bytes_t, off_t, n, cols: DeviceCols, status_t, first_row_t, n_rows_t):
         s = cols.struct()
@@ -267,7 +289,7 @@ class Context:
         out_rows, n_pairs = C.c_uint32(), C.c_uint64()
         s = cols.struct()
         rc = self.lib.swgpu_decode_zone_test(
-            self.h, 1 if fmt == "json" else 0, data.ctypes.data if data.size else None, rec_off.ctypes.data, n,
+            self.h, L.FMT[fmt], data.ctypes.data if data.size else None, rec_off.ctypes.data, n,
             cols.capacity, C.byref(s), status.ctypes.data, first_row.ctypes.data, C.byref(out_rows), pairs.shape[0],
             pairs.ctypes.data, C.byref(n_pairs), int(chunk_records))
         if rc == L.E_CAPACITY:
@@ -304,22 +326,27 @@ class Context:
         (ids per RECORD).  Returns the number of rows merged; ``status`` (uint8[n]) is filled when given."""
         data = np.ascontiguousarray(data, dtype=np.uint8)
         rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
-        id_hi = np.ascontiguousarray(id_hi, dtype=np.uint64)
-        id_lo = np.ascontiguousarray(id_lo, dtype=np.uint64)
         n = rec_off.shape[0] - 1
-        if id_hi.shape[0] < n or id_lo.shape[0] < n:
-            raise ValueError("one event id per record is required")
+        hi_p = lo_p = None
+        if fmt != "enriched":           # (an enriched payload carries its own event id)
+            id_hi = np.ascontiguousarray(id_hi, dtype=np.uint64)
+            id_lo = np.ascontiguousarray(id_lo, dtype=np.uint64)
+            if id_hi.shape[0] < n or id_lo.shape[0] < n:
+                raise ValueError("one event id per record is required")
+            hi_p, lo_p = id_hi.ctypes.data, id_lo.ctypes.data
         rows = C.c_uint32()
         self._check(self.lib.swgpu_decode_merge(
-            self.h, 1 if fmt == "json" else 0, data.ctypes.data if data.size else None, rec_off.ctypes.data, n,
-            int(seq_base), id_hi.ctypes.data, id_lo.ctypes.data, status.ctypes.data if status is not None else None,
+            self.h, L.FMT[fmt], data.ctypes.data if data.size else None, rec_off.ctypes.data, n,
+            int(seq_base), hi_p, lo_p, status.ctypes.data if status is not None else None,
             C.byref(rows)))
         return int(rows.value)
 
     def decode_merge_dev(self, fmt: str, bytes_t, off_t, n, seq_base, id_hi_t, id_lo_t, status_t, n_rows_t):
         """swgpu_decode_merge_dev: the fused decode + merge kernel on device-resident buffers (async)."""
-        self._check(self.lib.swgpu_decode_merge_dev(self.h, 1 if fmt == "json" else 0, bytes_t.data_ptr(), off_t.data_ptr(),
-                                                    int(n), int(seq_base), id_hi_t.data_ptr(), id_lo_t.data_ptr(),
+        self._check(self.lib.swgpu_decode_merge_dev(self.h, L.FMT[fmt], bytes_t.data_ptr(), off_t.data_ptr(),
+                                                    int(n), int(seq_base),
+                                                    id_hi_t.data_ptr() if id_hi_t is not None else None,
+                                                    id_lo_t.data_ptr() if id_lo_t is not None else None,
                                                     status_t.data_ptr(), n_rows_t.data_ptr()))
 
     def merge_dev(self, bytes_t, off_t, n_records, cols: DeviceCols, n_rows, n_rows_t, seq_base, id_hi_t, id_lo_t):

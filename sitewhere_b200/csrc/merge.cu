@@ -384,12 +384,16 @@ int sw_decode_merge_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint
                                 uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo, uint8_t *status,
                                 uint32_t *out_rows_dev);
 
+int sw_decode_merge_enriched_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, const MgTable &t,
+                                    uint64_t seq_base, uint8_t *status, uint32_t *out_rows_dev);
+
 extern "C" int32_t swgpu_decode_merge_dev(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off,
                                           uint32_t n, uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo,
                                           uint8_t *status, uint32_t *out_rows_dev) {
     if (!ctx) return SWGPU_E_INVALID;
-    if (!out_rows_dev || (format != SWGPU_FMT_PROTOBUF && format != SWGPU_FMT_JSON) ||
-        (n && (!rec_off || !bytes || !id_hi || !id_lo || !status))) {
+    const bool enriched = format == SWGPU_FMT_ENRICHED;  // (event ids come from the payload: id_hi / id_lo unused)
+    if (!out_rows_dev || (format != SWGPU_FMT_PROTOBUF && format != SWGPU_FMT_JSON && !enriched) ||
+        (n && (!rec_off || !bytes || !status || (!enriched && (!id_hi || !id_lo))))) {
         SW_SET_ERR(ctx, "swgpu_decode_merge_dev: bad argument");
         return SWGPU_E_INVALID;
     }
@@ -398,7 +402,8 @@ extern "C" int32_t swgpu_decode_merge_dev(swgpu_ctx *ctx, int32_t format, const 
     if (n == 0) return SWGPU_OK;
     MgTable t;
     if (int rc = sw_state_prepare(ctx, n, n, seq_base, &t)) return rc;
-    const int rc = format == SWGPU_FMT_JSON
+    const int rc = enriched ? sw_decode_merge_enriched_launch(ctx, bytes, rec_off, n, t, seq_base, status, out_rows_dev)
+                   : format == SWGPU_FMT_JSON
                        ? sw_decode_merge_json_launch(ctx, bytes, rec_off, n, t, seq_base, id_hi, id_lo, status, out_rows_dev)
                        : sw_decode_merge_pb_launch(ctx, bytes, rec_off, n, t, seq_base, id_hi, id_lo, status, out_rows_dev);
     if (rc) return rc;
@@ -409,8 +414,9 @@ extern "C" int32_t swgpu_decode_merge(swgpu_ctx *ctx, int32_t format, const uint
                                       uint32_t n, uint64_t seq_base, const uint64_t *id_hi, const uint64_t *id_lo,
                                       uint8_t *status, uint32_t *out_rows) {
     if (!ctx) return SWGPU_E_INVALID;
-    if (!rec_off || !out_rows || (format != SWGPU_FMT_PROTOBUF && format != SWGPU_FMT_JSON) ||
-        (n && (!id_hi || !id_lo || (rec_off[n] && !bytes)))) {
+    const bool enriched = format == SWGPU_FMT_ENRICHED;
+    if (!rec_off || !out_rows || (format != SWGPU_FMT_PROTOBUF && format != SWGPU_FMT_JSON && !enriched) ||
+        (n && ((!enriched && (!id_hi || !id_lo)) || (rec_off[n] && !bytes)))) {
         SW_SET_ERR(ctx, "swgpu_decode_merge: bad argument");
         return SWGPU_E_INVALID;
     }
@@ -428,8 +434,10 @@ extern "C" int32_t swgpu_decode_merge(swgpu_ctx *ctx, int32_t format, const uint
     if (total) SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_bytes.p, bytes + off0, total, cudaMemcpyHostToDevice, s));
     SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_off.p, rec_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, s));
     uint64_t *ids = (uint64_t *)ctx->d_ids.p;
-    SW_CUDA(ctx, cudaMemcpyAsync(ids, id_hi, (size_t)n * 8, cudaMemcpyHostToDevice, s));
-    SW_CUDA(ctx, cudaMemcpyAsync(ids + n, id_lo, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+    if (!enriched) {
+        SW_CUDA(ctx, cudaMemcpyAsync(ids, id_hi, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+        SW_CUDA(ctx, cudaMemcpyAsync(ids + n, id_lo, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+    }
     uint32_t *d_rows = (uint32_t *)ctx->d_first.p;
     // record offsets are absolute: bias the byte pointer so that bytes_dev[off] is the staged copy
     const uint8_t *biased = (const uint8_t *)ctx->d_bytes.p - off0;

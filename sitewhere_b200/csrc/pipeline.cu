@@ -15,6 +15,9 @@ int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
 int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
                           const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev,
                           uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next);
+int sw_decode_enriched_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
+                              const swgpu_decoded_cols *out, const swgpu_event_ids *ids, uint8_t *status, uint32_t *first_row,
+                              uint32_t *out_rows_dev, uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next);
 int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta, uint32_t n,
                    const uint32_t *n_rows_dev, uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev,
                    const uint32_t *row_base);
@@ -160,7 +163,10 @@ static int pl_small(swgpu_ctx *ctx, Pipeline *p, int32_t format, const uint8_t *
     uint64_t *d_pairs_n = (uint64_t *)(dout + 8);
     // record offsets are absolute: bias the byte pointer so that bytes_dev[off] is the staged copy
     const uint8_t *biased = din + in_off_bytes - off0;
-    int rc = format == SWGPU_FMT_JSON
+    int rc = format == SWGPU_FMT_ENRICHED
+                 ? sw_decode_enriched_launch(ctx, biased, (const uint64_t *)din, n, rows_cap, &d, nullptr, dout + o_status,
+                                             (uint32_t *)(dout + o_first), d_rows, 0, nullptr, nullptr)
+             : format == SWGPU_FMT_JSON
                  ? sw_decode_json_launch(ctx, biased, (const uint64_t *)din, n, rows_cap, &d, dout + o_status,
                                          (uint32_t *)(dout + o_first), d_rows, 0, nullptr, nullptr)
                  : sw_decode_pb_launch(ctx, biased, (const uint64_t *)din, n, rows_cap, &d, dout + o_status,
@@ -196,7 +202,7 @@ extern "C" int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const 
                                           uint32_t *first_row, uint32_t *out_rows, uint64_t max_pairs, uint64_t *pairs,
                                           uint64_t *n_pairs, uint32_t chunk_records) {
     if (!ctx) return SWGPU_E_INVALID;
-    if (!rec_off || !out || !out_rows || !n_pairs || (format != SWGPU_FMT_PROTOBUF && format != SWGPU_FMT_JSON) ||
+    if (!rec_off || !out || !out_rows || !n_pairs || (format != SWGPU_FMT_PROTOBUF && format != SWGPU_FMT_JSON && format != SWGPU_FMT_ENRICHED) ||
         (max_pairs && !pairs) || (n && rec_off[n] && !bytes)) {
         SW_SET_ERR(ctx, "swgpu_decode_zone_test: bad argument");
         return SWGPU_E_INVALID;
@@ -288,7 +294,11 @@ extern "C" int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const 
         uint64_t *d_pairs_n = (uint64_t *)((uint8_t *)s.counts.p + 8);
         // record offsets are absolute: bias the byte pointer so that bytes_dev[off] is the chunk copy
         const uint8_t *biased = (const uint8_t *)s.bytes.p - off0;
-        int rc = format == SWGPU_FMT_JSON
+        int rc = format == SWGPU_FMT_ENRICHED
+                     ? sw_decode_enriched_launch(ctx, biased, (const uint64_t *)s.off.p, nc, s.rows_cap, &d, nullptr,
+                                                 (uint8_t *)s.status.p, (uint32_t *)s.first.p, d_rows, a, p->row_totals + c,
+                                                 p->row_totals + c + 1)
+                 : format == SWGPU_FMT_JSON
                      ? sw_decode_json_launch(ctx, biased, (const uint64_t *)s.off.p, nc, s.rows_cap, &d,
                                              (uint8_t *)s.status.p, (uint32_t *)s.first.p, d_rows, a, p->row_totals + c,
                                              p->row_totals + c + 1)
