@@ -16,8 +16,14 @@
 // conversion exception (status 1: the consumers log and skip the record) or an event type off the path
 // (status 3).  Rows go to the same columns as the device-payload decoders — the row's "token" is the 16 bytes of
 // the device assignment id, which is the reference's device-state key — plus the ids the payload carries; or,
-// fused, straight into the device-state table.  The rules of protobuf-java restated here (message fields that
-// occur again merge, proto3 strings must be valid UTF-8, ...) are spelled out in oracle/sw_oracle_enriched.c.
+// fused, straight into the device-state table.  Rules of protobuf-java 3.3.0 (full runtime, proto3; recalled)
+// restated here: a message-typed field that occurs again MERGES into the value held so far (generated code:
+// toBuilder().mergeFrom(readMessage())) — proto3 scalars of the later occurrence replace only when they are not
+// the default, sub-messages merge recursively, a different oneof member replaces and the same member merges,
+// while scalars repeated inside one occurrence take the last value; strings and map<string,string> entries are
+// read with readStringRequireUtf8 (invalid UTF-8 is an InvalidProtocolBufferException); an enum number outside
+// the schema becomes UNRECOGNIZED, for which SiteWhere's converters throw; parseFrom(byte[]) pushes the array
+// length as the outermost limit.
 #include "merge_table.cuh"
 #include "pb_reader.cuh"
 #include "swgpu_common.cuh"

@@ -1,14 +1,17 @@
 // pb_reader.cuh — protobuf wire-format reader shared by the device-payload decoder (decode_pb.cu: proto2,
 // protobuf-java 3.3.0 lite, parseDelimitedFrom on a stream) and the enriched-event decoder (decode_enriched.cu:
 // proto3, full runtime, parseFrom on a byte array).  The byte source `B` is one of swgpu_common.cuh's readers
-// (a record staged in shared memory, or global memory).  The rules restated here — readTag, the 10-byte varint,
-// unknown-field skipping with group end-tag checks, readMessage limits — are the ones cited in
-// oracle/sw_oracle.c and oracle/sw_oracle_enriched.c.
+// (a record staged in shared memory, or global memory).  The rules restated here are protobuf-java 3.3.0's
+// (third party, recalled): readTag returns 0 at the end of input and rejects field number 0; varints are at most
+// 10 bytes and 32-bit reads keep the low 32 bits; an unknown field is skipped by wire type, groups recursively
+// with the end tag checked, END_GROUP stops the message, wire types 6 and 7 are invalid; readMessage reads a
+// length (negative: error), pushes it as a limit (beyond the enclosing limit: error) and checks that the nested
+// message did not stop on an END_GROUP tag.
 #pragma once
 #include "swgpu_common.cuh"
 
 // Nesting of unknown-field groups followed before the record is declared malformed.  (protobuf-java recurses
-// until the JVM stack ends; the oracle uses the same bound.)
+// until the JVM stack ends; the test oracle uses the same bound.)
 #define PB_MAX_GROUP_DEPTH 64
 
 template <typename B>
