@@ -151,6 +151,11 @@ int32_t swgpu_sync(swgpu_ctx *ctx);
  *                           choice (JTS 1.13 casts +x: RayCrossingCounter, called from the zone test at
  *                           RP/processors/geospatial/ZoneTestRuleProcessor.java:50)
  *   "zone.scan_sequential"  1 = scan the per-tile alert counts on one CTA
+ *   "state.presence_now_ms" t > 0: every event folded into the device state from now on also touches its device's
+ *                           presence row with lastInteractionDate = t and presenceMissingDate = null
+ *                           (DS/processing/DeviceStateProcessingLogic.java:142-143; the reference takes new Date(),
+ *                           here the caller supplies the batch's time so that results are reproducible); 0 = off
+ *                           (default).  Set it before each batch.  Costs one more table access per event.
  *   "json.fast_path"        0 = every JSON record takes the general structural pass instead of trying the
  *                           straight-line pass for plainly shaped requests first (default 1)
  *   "zone.stats"            1 = zone tests also count their work (read it with swgpu_zone_stats)        */
@@ -347,6 +352,20 @@ int32_t swgpu_decode_merge_dev(swgpu_ctx *ctx, int32_t format, const uint8_t *by
 /* Number of live keys and the bytes of their public form (see swgpu_state_rows).  Returns SWGPU_E_CAPACITY
  * (once; the counts are still valid) when a *_dev merge since the last check had to drop rows.          */
 int32_t swgpu_state_size(swgpu_ctx *ctx, uint64_t *n_keys, uint64_t *key_bytes);
+/* Presence scan.  Replaces one round of DevicePresenceManager.PresenceChecker (DS/presence/DevicePresenceManager.java:
+ * 139-167; query DS/persistence/mongodb/MongoDeviceStateManagement.java:170-193): every device whose presence row
+ * has lastInteractionDate <= now_ms - interval_ms and presenceMissingDate == null (SendOnceNotificationStrategy,
+ * DS/presence/PresenceNotificationStrategies.java:24-31) is reported — the caller sends the "presence" state change —
+ * and gets presenceMissingDate := now_ms; an event folded later (with "state.presence_now_ms" set) clears it again.
+ * Host pointers.  Output ascending by (lastInteractionDate, key): last_interaction[k], and the device's key
+ * key_bytes[key_off[k] .. key_off[k+1]) = token length (2 bytes LE) | 0x7f | token bytes (for enriched events the
+ * token is the 16 bytes of the assignment id).  *n_found = all devices found missing; when they do not fit
+ * (max_devices, max_key_bytes) the ones that fit are reported and marked, the call returns SWGPU_E_CAPACITY and the
+ * next scan finds the rest.  A presence row also appears in swgpu_state_snapshot: kind byte 0x7f, seq =
+ * lastInteractionDate, event_date = presenceMissingDate (0 = null).                                                 */
+int32_t swgpu_presence_scan(swgpu_ctx *ctx, int64_t now_ms, int64_t interval_ms, uint64_t max_devices,
+                            uint64_t max_key_bytes, int64_t *last_interaction, uint64_t *key_off, uint8_t *key_bytes,
+                            uint64_t *n_reported, uint64_t *n_found);
 /* Snapshot (host pointers): one row per live key, in unspecified order.  key_off has n_keys+1
  * entries into key_bytes; a key is  token length (2 bytes LE) | kind byte | token bytes | name bytes.               */
 typedef struct swgpu_state_rows {

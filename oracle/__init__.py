@@ -115,6 +115,9 @@ def lib() -> C.CDLL:
                                       C.c_uint64, C.c_void_p, C.c_void_p]
         L.orc_state_merge_seq.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(_ColsStruct), C.c_uint32,
                                           C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_state_set_presence_now.argtypes = [C.c_void_p, C.c_uint64]
+        L.orc_presence_scan.restype = C.c_uint64
+        L.orc_presence_scan.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_state_size.restype = C.c_uint64
         L.orc_state_size.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
         L.orc_state_snapshot.argtypes = [C.c_void_p] * 8
@@ -293,6 +296,22 @@ class State:
         s, si = cols.struct(), ids.struct()
         lib().orc_state_merge_enriched(self._h, data.ctypes.data, rec_off.ctypes.data, C.byref(s), C.byref(si), total,
                                        seq_base, seq.ctypes.data)
+
+    def set_presence_now(self, now_ms):
+        """events folded from now on carry this timestamp as their device's lastInteractionDate (None: off)"""
+        lib().orc_state_set_presence_now(self._h, 0 if now_ms is None else int(now_ms) + 1)
+
+    def presence_scan(self, now_ms: int, interval_ms: int):
+        """-> (lastInteractionDate uint64[k], [device key bytes]) of the devices reported missing, marked as such"""
+        kb = C.c_uint64()
+        n = int(lib().orc_state_size(self._h, C.byref(kb)))
+        last = np.zeros(max(n, 1), np.uint64)
+        off = np.zeros(n + 1, np.uint64)
+        keys = np.zeros(max(int(kb.value), 1), np.uint8)
+        k = int(lib().orc_presence_scan(self._h, int(now_ms), int(interval_ms), n, last.ctypes.data, off.ctypes.data,
+                                        keys.ctypes.data))
+        raw = keys.tobytes()
+        return last[:k], [raw[int(off[i]): int(off[i + 1])] for i in range(k)]
 
     def snapshot(self) -> dict:
         kb = C.c_uint64()

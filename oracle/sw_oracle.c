@@ -734,6 +734,7 @@ typedef struct {
     double value;
 } st_entry;
 struct orc_state {
+    uint64_t presence_now1; /* 0 = presence not tracked; else the timestamp (ms) of the events being folded + 1 */
     st_entry *e;
     size_t n, cap;
     int64_t *table; /* open addressing -> index into e, -1 empty */
@@ -848,8 +849,59 @@ static void state_merge_any(orc_state *s, const uint8_t *bytes, const uint64_t *
         e->id_lo = ids ? ids->event_lo[r] : id_lo[r];
         e->date = rows->event_date[r];
         e->value = rows->v0[r];
+        if (s->presence_now1) {
+            /* every merged event: lastInteractionDate := now, presenceMissingDate := null
+             * (DeviceStateProcessingLogic.java:142-143).  The device's row: key = token, kind byte 0x7f, no name;
+             * seq holds lastInteractionDate, date holds presenceMissingDate (0 = null). */
+            kb[2] = 0x7f;
+            st_entry *d = st_get(s, kb, (uint32_t)(3 + tl));
+            if (d->seq <= s->presence_now1 - 1) { /* (a batch stamped earlier than one already folded changes nothing) */
+                d->seq = s->presence_now1 - 1;
+                d->date = 0;
+            }
+        }
     }
     free(kb);
+}
+void orc_state_set_presence_now(orc_state *s, uint64_t now_ms_plus1) { s->presence_now1 = now_ms_plus1; }
+/* DevicePresenceManager.PresenceChecker (DS/presence/DevicePresenceManager.java:139-167): device states with
+ * lastInteractionDate <= now - interval (query: MongoDeviceStateManagement.java:170-193, ascending by that date)
+ * for which SendOnceNotificationStrategy permits an event (presenceMissingDate == null,
+ * PresenceNotificationStrategies.java:24-31) get presenceMissingDate := now and are reported.  Returns the count;
+ * writes up to max_out rows (lastInteractionDate + the device's key bytes), ascending by (date, key). */
+static int pres_cmp(const void *a, const void *b) {
+    const st_entry *x = *(st_entry *const *)a, *y = *(st_entry *const *)b;
+    if (x->seq != y->seq) return x->seq < y->seq ? -1 : 1;
+    uint32_t ml = x->klen < y->klen ? x->klen : y->klen;
+    int c = memcmp(x->key, y->key, ml);
+    if (c) return c;
+    return (x->klen > y->klen) - (x->klen < y->klen);
+}
+uint64_t orc_presence_scan(orc_state *s, uint64_t now_ms, uint64_t interval_ms, uint64_t max_out, uint64_t *last_interaction,
+                           uint64_t *key_off, uint8_t *key_bytes) {
+    st_entry **hit = (st_entry **)malloc(sizeof(st_entry *) * (s->n ? s->n : 1));
+    uint64_t nh = 0;
+    const uint64_t cutoff = now_ms - interval_ms;
+    for (size_t i = 0; i < s->n; i++) {
+        st_entry *e = &s->e[i];
+        if (e->klen < 3 || e->key[2] != 0x7f) continue;
+        if (e->seq <= cutoff && e->date == 0) hit[nh++] = e;
+    }
+    qsort(hit, nh, sizeof(st_entry *), pres_cmp);
+    uint64_t off = 0;
+    for (uint64_t k = 0; k < nh; k++) {
+        hit[k]->date = (int64_t)now_ms;
+        if (k < max_out) {
+            last_interaction[k] = hit[k]->seq;
+            key_off[k] = off;
+            memcpy(key_bytes + off, hit[k]->key, hit[k]->klen);
+            off += hit[k]->klen;
+        }
+    }
+    if (nh <= max_out) key_off[nh] = off;
+    else key_off[max_out] = off;
+    free(hit);
+    return nh;
 }
 void orc_state_merge_seq(orc_state *s, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
                          uint32_t n_rows, uint64_t seq_base, const uint64_t *seq, const uint64_t *id_hi,

@@ -84,6 +84,10 @@ void orc_state_merge_seq(orc_state *, const uint8_t *bytes, const uint64_t *rec_
  * event id is the payload's own; seq as in orc_state_merge_seq */
 void orc_state_merge_enriched(orc_state *, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *rows,
                               const orc_event_ids *ids, uint32_t n_rows, uint64_t seq_base, const uint64_t *seq);
+/* presence: while now_ms_plus1 != 0 every folded event also touches its device's row (see sw_oracle.c) */
+void orc_state_set_presence_now(orc_state *, uint64_t now_ms_plus1);
+uint64_t orc_presence_scan(orc_state *, uint64_t now_ms, uint64_t interval_ms, uint64_t max_out, uint64_t *last_interaction,
+                           uint64_t *key_off, uint8_t *key_bytes);
 uint64_t orc_state_size(orc_state *, uint64_t *key_bytes);
 /* rows sorted by key bytes; key_off has n+1 entries */
 void orc_state_snapshot(orc_state *, uint64_t *seq, uint64_t *id_hi, uint64_t *id_lo,

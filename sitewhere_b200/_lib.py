@@ -93,6 +93,7 @@ SIGNATURES = {
     "swgpu_decode_merge_dev": (_I32, [_P, _I32, _P, _P, _U32, _U64, _P, _P, _P, _P]),
     "swgpu_merge_dev": (_I32, [_P, _P, _P, _U32, _COLS, _U32, _P, _U64, _P, _P]),
     "swgpu_state_size": (_I32, [_P, C.POINTER(_U64), C.POINTER(_U64)]),
+    "swgpu_presence_scan": (_I32, [_P, C.c_int64, C.c_int64, _U64, _U64, _P, _P, _P, C.POINTER(_U64), C.POINTER(_U64)]),
     "swgpu_state_snapshot": (_I32, [_P, _U64, _U64, _ROWS, C.POINTER(_U64)]),
     "swgpu_state_restore": (_I32, [_P, _ROWS, _U64]),
     "swgpu_state_clear": (_I32, [_P]),

@@ -360,6 +360,23 @@ class Context:
         self._check(self.lib.swgpu_state_size(self.h, C.byref(a), C.byref(b)))
         return int(a.value), int(b.value)
 
+    def presence_scan(self, now_ms: int, interval_ms: int, max_devices: int = None):
+        """swgpu_presence_scan -> (lastInteractionDate int64[k], [device key bytes], n_found)"""
+        if max_devices is None:
+            max_devices, kb = self.state_size()
+        else:
+            kb = max_devices * 64
+        last = np.zeros(max(max_devices, 1), np.int64)
+        off = np.zeros(max_devices + 1, np.uint64)
+        keys = np.zeros(max(kb, 1), np.uint8)
+        rep, found = C.c_uint64(), C.c_uint64()
+        rc = self.lib.swgpu_presence_scan(self.h, int(now_ms), int(interval_ms), max_devices, keys.shape[0], last.ctypes.data,
+                                          off.ctypes.data, keys.ctypes.data, C.byref(rep), C.byref(found))
+        self._check(rc, allow_capacity=True)
+        k = int(rep.value)
+        raw = keys.tobytes()
+        return last[:k], [raw[int(off[i]): int(off[i + 1])] for i in range(k)], int(found.value)
+
     def state_clear(self):
         self._check(self.lib.swgpu_state_clear(self.h))
 

@@ -159,6 +159,14 @@ extern "C" int32_t swgpu_set_option(swgpu_ctx *ctx, const char *name, int64_t va
         ctx->opt_zone_scan_sequential = value ? 1u : 0u;
         return SWGPU_OK;
     }
+    if (!strcmp(name, "state.presence_now_ms")) {
+        if (value < 0) {
+            SW_SET_ERR(ctx, "swgpu_set_option: state.presence_now_ms takes a time in ms since the epoch, or 0 to switch presence off");
+            return SWGPU_E_INVALID;
+        }
+        ctx->opt_presence_now1 = value ? (uint64_t)value + 1 : 0;
+        return SWGPU_OK;
+    }
     if (!strcmp(name, "json.fast_path")) {
         ctx->opt_json_fast = value ? 1u : 0u;
         return SWGPU_OK;

@@ -551,10 +551,10 @@ __device__ __forceinline__ void en_decode_tile(const EnArgs &a, const uint32_t t
                 const uint64_t seq1 = a.seq_base + ((uint64_t)(a.rec_base + rec0 + lane) << SWGPU_SEQ_RECORD_SHIFT) + 1;
                 if (staged) {
                     EnMgKey<SmemBytes> key{r.asg_hi, r.asg_lo, SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, SWGPU_SPAN_OFF(r.nspan), nl};
-                    mg_upsert(a.mt, &s_cnt[warp], h, 16u, nl, kindbyte, key, seq1, r.event_hi, r.event_lo, (uint64_t)r.date, r.v0);
+                    mg_upsert(a.mt, &s_cnt[warp], h, r.th, 16u, nl, kindbyte, key, seq1, r.event_hi, r.event_lo, (uint64_t)r.date, r.v0);
                 } else {
                     EnMgKey<GmemBytes> key{r.asg_hi, r.asg_lo, GmemBytes{a.bytes + r0}, SWGPU_SPAN_OFF(r.nspan), nl};
-                    mg_upsert(a.mt, &s_cnt[warp], h, 16u, nl, kindbyte, key, seq1, r.event_hi, r.event_lo, (uint64_t)r.date, r.v0);
+                    mg_upsert(a.mt, &s_cnt[warp], h, r.th, 16u, nl, kindbyte, key, seq1, r.event_hi, r.event_lo, (uint64_t)r.date, r.v0);
                 }
             }
         }

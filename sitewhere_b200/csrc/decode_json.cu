@@ -1291,10 +1291,10 @@ __global__ void __launch_bounds__(JS_THREADS) json_decode_merge_kernel(JsArgs a)
                 if (staged) {
                     MgKeyBytes<SmemBytes> key{SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, SWGPU_SPAN_OFF(r.tspan), tl,
                                               SWGPU_SPAN_OFF(r.nspan), nl};
-                    mg_upsert(a.mt, &s_cnt[warp], h, tl, nl, kindbyte, key, seq1, ihi, ilo, (uint64_t)r.date, r.v0);
+                    mg_upsert(a.mt, &s_cnt[warp], h, r.th, tl, nl, kindbyte, key, seq1, ihi, ilo, (uint64_t)r.date, r.v0);
                 } else {
                     MgKeyBytes<GmemBytes> key{GmemBytes{a.bytes + r0}, SWGPU_SPAN_OFF(r.tspan), tl, SWGPU_SPAN_OFF(r.nspan), nl};
-                    mg_upsert(a.mt, &s_cnt[warp], h, tl, nl, kindbyte, key, seq1, ihi, ilo, (uint64_t)r.date, r.v0);
+                    mg_upsert(a.mt, &s_cnt[warp], h, r.th, tl, nl, kindbyte, key, seq1, ihi, ilo, (uint64_t)r.date, r.v0);
                 }
             }
         }

@@ -320,7 +320,7 @@ __device__ __forceinline__ void pb_merge_rows(const PbArgs &a, MgLocalCnt *local
         }
         const uint64_t nh = kind == SWGPU_KIND_LOCATION ? 0ull : sw_hash64(bytes, noff, nlen);
         MgKeyBytes<B> key{bytes, o.hw_off, o.hw_len, noff, nl};
-        mg_upsert(a.mt, local, mg_mix(th, nh, kindbyte), o.hw_len, nl, kindbyte, key,
+        mg_upsert(a.mt, local, mg_mix(th, nh, kindbyte), th, o.hw_len, nl, kindbyte, key,
                   seq0 + (k < (1u << SWGPU_SEQ_RECORD_SHIFT) - 1 ? k : (1u << SWGPU_SEQ_RECORD_SHIFT) - 1), ihi, ilo,
                   (uint64_t)o.date, v0);
     }

@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(MG_THREADS) merge_upsert_kernel(MgArgs a) {
                 const uint64_t h = mg_mix(__ldg(a.token_hash + r),
                                           kind == SWGPU_KIND_LOCATION ? 0ull : __ldg(a.name_hash + r), kindbyte);
                 MgKeyGmem key{rec + SWGPU_SPAN_OFF(ts), rec + SWGPU_SPAN_OFF(ns), tl, nl};
-                mg_upsert(a.t, &s_cnt[warp], h, tl, nl, kindbyte, key, a.seq_base + r + 1, __ldg(a.id_hi + r),
+                mg_upsert(a.t, &s_cnt[warp], h, __ldg(a.token_hash + r), tl, nl, kindbyte, key, a.seq_base + r + 1, __ldg(a.id_hi + r),
                           __ldg(a.id_lo + r), (uint64_t)__ldg(a.event_date + r),
                           (uint64_t)__double_as_longlong(__ldg(a.v0 + r)));
             }
@@ -109,8 +109,7 @@ __global__ void __launch_bounds__(MG_THREADS) merge_fixup_kernel(MgTable t) {
         const MgFix f = t.fix[k];
         uint64_t *w = t.slots[f.slot].w;
         if (w[MG_W_BEST] != f.seq1) continue;  // a later event of this key won
-        *(ulonglong2 *)(w + MG_W_PAY) = make_ulonglong2(f.id_hi, f.id_lo);
-        *(ulonglong2 *)(w + MG_W_PAY + 2) = make_ulonglong2(f.date, f.value);
+        mg_store_payload(w, f.id_hi, f.id_lo, f.date, f.value);
     }
 }
 
@@ -225,6 +224,7 @@ extern "C" int32_t swgpu_state_reserve(swgpu_ctx *ctx, uint64_t max_keys, uint64
 int sw_state_prepare(swgpu_ctx *ctx, uint64_t new_keys, uint64_t rows, uint64_t seq_floor, MgTable *t) {
     SW_CUDA(ctx, cudaSetDevice(ctx->device));
     MgState *st = (MgState *)ctx->state;
+    if (ctx->opt_presence_now1) new_keys *= 2;  // every row may also add its device's presence row
     uint64_t ku = (st ? st->keys_upper : 0) + new_keys;
     if (!st || !st->arena || ku * 2 + 16 > st->cap) {
         if (st && st->ctr && st->slots) {
@@ -247,6 +247,7 @@ int sw_state_prepare(swgpu_ctx *ctx, uint64_t new_keys, uint64_t rows, uint64_t 
     t->fix = (MgFix *)st->fix.p;
     t->fix_cap = fix_cap;
     t->seq_floor = seq_floor;
+    t->presence_now1 = ctx->opt_presence_now1;
     SW_CUDA(ctx, cudaMemsetAsync(&st->ctr->n_fix, 0, sizeof(unsigned long long), ctx->stream));
     return SWGPU_OK;
 }
@@ -492,6 +493,123 @@ extern "C" int32_t swgpu_state_clear(swgpu_ctx *ctx) {
     return SWGPU_OK;
 }
 
+// ---- presence scan ------------------------------------------------------------------------------------------------------
+// DevicePresenceManager.PresenceChecker (service-device-state/.../presence/DevicePresenceManager.java:139-167): device
+// states with lastInteractionDate <= now - interval (MongoDeviceStateManagement.searchDeviceStates :170-193) for
+// which SendOnceNotificationStrategy permits an event (presenceMissingDate == null,
+// PresenceNotificationStrategies.java:24-31) are reported and get presenceMissingDate := now.  One streaming pass
+// over the table: sector 0 of every slot (tag, best, key header), the date word of the few that match.
+struct MgPresRow {
+    uint64_t last, key_pos;  // key_pos: byte offset | length << 40
+};
+__global__ void merge_presence_scan_kernel(MgSlot *slots, uint64_t cap, const uint64_t *arena, uint64_t cutoff1, uint64_t now_ms,
+                                           MgPresRow *rows, uint64_t max_rows, uint8_t *keys, uint64_t max_key_bytes,
+                                           unsigned long long *cursor /* [0] found, [1] key bytes, [2] reported */) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cap) return;
+    uint64_t *w = slots[i].w;
+    const ulonglong2 a0 = __ldg((const ulonglong2 *)w), a1 = __ldg((const ulonglong2 *)(w + 2));
+    const uint64_t tag = a0.x, best = a0.y, hdr = a1.x;
+    if (tag == 0 || tag == MG_TOMB || (uint32_t)((hdr >> 32) & 0xff) != MG_KIND_DEVICE) return;
+    if (best == 0 || best > cutoff1) return;      // interacted after the cut-off
+    if (w[MG_W_PAY + 2] != 0) return;             // already reported missing
+    atomicAdd(cursor, 1ull);
+    const uint32_t tl = (uint32_t)(hdr & 0xffff), kl = 3 + tl;
+    const unsigned long long k = atomicAdd(cursor + 2, 1ull);
+    if (k >= max_rows) {
+        atomicAdd(cursor + 2, (unsigned long long)-1ll);
+        return;  // no room in the caller's arrays: stays unreported, the next scan finds it again
+    }
+    const unsigned long long pos = atomicAdd(cursor + 1, (unsigned long long)kl);
+    if (pos + kl > max_key_bytes) {
+        atomicAdd(cursor + 1, (unsigned long long)(0ull - kl));
+        atomicAdd(cursor + 2, (unsigned long long)-1ll);
+        return;
+    }
+    w[MG_W_PAY + 2] = now_ms;  // presenceMissingDate
+    rows[k].last = best - 1;
+    rows[k].key_pos = pos | ((uint64_t)kl << 40);
+    uint8_t *pk = keys + pos;
+    pk[0] = (uint8_t)(tl & 0xff);
+    pk[1] = (uint8_t)(tl >> 8);
+    pk[2] = (uint8_t)MG_KIND_DEVICE;
+    const bool lng = (hdr & MG_HDR_LONG) != 0;
+    const uint64_t *aw = lng ? arena + w[MG_W_KEY0 + 1] : nullptr;
+    for (uint32_t b = 0; b < tl; b++) {
+        const uint32_t j = 1 + (b >> 3);
+        const uint64_t kwd = lng ? aw[j - 1] : (j < 6 ? w[MG_W_KEY0 + j] : w[MG_W_KEY6 + j - 6]);
+        pk[3 + b] = (uint8_t)(kwd >> (8 * (b & 7)));
+    }
+}
+
+extern "C" int32_t swgpu_presence_scan(swgpu_ctx *ctx, int64_t now_ms, int64_t interval_ms, uint64_t max_devices,
+                                       uint64_t max_key_bytes, int64_t *last_interaction, uint64_t *key_off, uint8_t *key_bytes,
+                                       uint64_t *n_reported, uint64_t *n_found) {
+    if (!ctx || !n_reported || now_ms <= 0 || interval_ms < 0 || (max_devices && (!last_interaction || !key_off || !key_bytes))) {
+        if (ctx) SW_SET_ERR(ctx, "swgpu_presence_scan: bad argument");
+        return SWGPU_E_INVALID;
+    }
+    *n_reported = 0;
+    if (n_found) *n_found = 0;
+    if (key_off) key_off[0] = 0;
+    MgState *st = (MgState *)ctx->state;
+    if (!st || !st->slots) return SWGPU_OK;
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    MgPresRow *d_rows = nullptr;
+    uint8_t *d_keys = nullptr;
+    unsigned long long *d_cur = nullptr, h_cur[3] = {0, 0, 0};
+    cudaError_t e = cudaMalloc(&d_rows, (max_devices + 1) * sizeof(MgPresRow));
+    if (e == cudaSuccess) e = cudaMalloc(&d_keys, max_key_bytes + 16);
+    if (e == cudaSuccess) e = cudaMalloc(&d_cur, 32);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d_cur, 0, 32, ctx->stream);
+    if (e == cudaSuccess) {
+        const uint64_t cutoff1 = now_ms > interval_ms ? (uint64_t)(now_ms - interval_ms) + 1 : 0;  // best <= cutoff + 1
+        merge_presence_scan_kernel<<<(unsigned)((st->cap + 255) / 256), 256, 0, ctx->stream>>>(
+            st->slots, st->cap, st->arena, cutoff1, (uint64_t)now_ms, d_rows, max_devices, d_keys, max_key_bytes, d_cur);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h_cur, d_cur, 24, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    std::vector<MgPresRow> rows(h_cur[2]);
+    std::vector<uint8_t> keys(h_cur[1] + 1);
+    if (e == cudaSuccess && h_cur[2]) {
+        e = cudaMemcpyAsync(rows.data(), d_rows, h_cur[2] * sizeof(MgPresRow), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(keys.data(), d_keys, h_cur[1], cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    }
+    if (d_rows) cudaFree(d_rows);
+    if (d_keys) cudaFree(d_keys);
+    if (d_cur) cudaFree(d_cur);
+    if (e != cudaSuccess) {
+        SW_SET_ERR(ctx, "swgpu_presence_scan failed: %s", cudaGetErrorString(e));
+        return e == cudaErrorMemoryAllocation ? SWGPU_E_NOMEM : SWGPU_E_CUDA;
+    }
+    // the reference's query sorts ascending by lastInteractionDate; ties by key bytes for a defined order
+    std::sort(rows.begin(), rows.end(), [&](const MgPresRow &x, const MgPresRow &y) {
+        if (x.last != y.last) return x.last < y.last;
+        const uint64_t xp = x.key_pos & ((1ull << 40) - 1), xl = x.key_pos >> 40, yp = y.key_pos & ((1ull << 40) - 1), yl = y.key_pos >> 40;
+        const int c = memcmp(keys.data() + xp, keys.data() + yp, (size_t)std::min(xl, yl));
+        return c ? c < 0 : xl < yl;
+    });
+    uint64_t off = 0;
+    for (uint64_t k = 0; k < rows.size(); k++) {
+        last_interaction[k] = (int64_t)rows[k].last;
+        key_off[k] = off;
+        const uint64_t pos = rows[k].key_pos & ((1ull << 40) - 1), kl = rows[k].key_pos >> 40;
+        memcpy(key_bytes + off, keys.data() + pos, kl);
+        off += kl;
+    }
+    if (key_off) key_off[rows.size()] = off;
+    *n_reported = rows.size();
+    if (n_found) *n_found = h_cur[0];
+    if (h_cur[0] > rows.size()) {
+        SW_SET_ERR(ctx, "swgpu_presence_scan: %llu devices are missing, %llu fit the arrays and were reported; scan again for the rest",
+                   h_cur[0], (unsigned long long)rows.size());
+        return SWGPU_E_CAPACITY;
+    }
+    return SWGPU_OK;
+}
+
 // ---- snapshot / restore: checkpoint operations, not the hot path ---------------------------------------------------
 // Snapshot: a kernel packs the live slots into dense rows and their keys, in the public form
 // token_len(2 LE) | kind byte | token | name, into one byte buffer; only those are copied to the host.
@@ -628,7 +746,7 @@ __global__ void __launch_bounds__(MG_THREADS) merge_restore_kernel(MgTable t, co
         const uint64_t th = sw_hash64(gb, 3, tl);
         const uint64_t nh = (kind == SWGPU_KIND_LOCATION || (kindbyte & 0x80)) ? 0ull : sw_hash64(gb, 3 + tl, nl);
         MgKeyPublic kr{key + 3, key + 3 + tl, tl, nl};
-        mg_upsert(t, &s_cnt[warp], mg_mix(th, nh, kindbyte), tl, nl, kindbyte, kr, seq[k] + 1, id_hi[k], id_lo[k],
+        mg_upsert(t, &s_cnt[warp], mg_mix(th, nh, kindbyte), th, tl, nl, kindbyte, kr, seq[k] + 1, id_hi[k], id_lo[k],
                   (uint64_t)date[k], (uint64_t)__double_as_longlong(value[k]));
     }
     __syncwarp();
@@ -659,6 +777,7 @@ extern "C" int32_t swgpu_state_restore(swgpu_ctx *ctx, const swgpu_state_rows *i
     MgTable t;
     if (int rc = sw_state_prepare(ctx, n_keys, n_keys, 0, &t)) return rc;
     t.seq_floor = ~0ull;  // keys are distinct: no row can follow another one of this launch
+    t.presence_now1 = 0;  // (presence rows are among the snapshot's keys)
     const uint64_t kb = in->key_off[n_keys];
     uint8_t *d = nullptr;
     const size_t col = (size_t)n_keys * 8, total = col * 5 + (size_t)(n_keys + 1) * 8 + kb + 64;

@@ -242,3 +242,68 @@ def test_merge_dev_reports_dropped_rows():
     snap_equal(ctx.state_snapshot(), st.snapshot())
     assert ctx.state_size()[0] == n      # the drop was reported once; nothing is pending now
     ctx.close()
+
+
+def test_presence_rows_and_scan(ctx):
+    """lastInteractionDate / presenceMissingDate per device and the presence scan, against the oracle: three batches
+    stamped at different times (unfused, fused protobuf, fused JSON), scans that report some devices, a device that
+    comes back, a scan with too small a result buffer"""
+    ctx.state_clear()
+    st = oracle.State()
+    t0 = 1_600_000_000_000
+    seq = 0
+    try:
+        # batch 1 (t0): devices 0..299, unfused merge
+        d1, o1, _ = S.pb_mixed(20_000, 300, seed=700)
+        ctx.set_option("state.presence_now_ms", t0)
+        st.set_presence_now(t0)
+        res = ctx.decode_pb(d1, o1)
+        oc, _, _, tot = oracle.decode_pb(d1, o1)
+        ids = np.arange(tot, dtype=np.uint64)
+        ctx.merge(d1, o1, res.cols, seq, ids, ids)
+        st.merge(d1, o1, oc, seq, ids, ids)
+        seq += tot
+        # batch 2 (t0 + 60 s): devices 0..99 only, fused
+        d2, o2, _ = S.pb_mixed(5_000, 100, seed=701)
+        ctx.set_option("state.presence_now_ms", t0 + 60_000)
+        st.set_presence_now(t0 + 60_000)
+        n2 = len(o2) - 1
+        ids2 = np.arange(n2, dtype=np.uint64)
+        rows = ctx.decode_merge("pb", d2, o2, seq, ids2, ids2)
+        oc2, _, _, tot2 = oracle.decode_pb(d2, o2)
+        assert rows == tot2
+        st.merge_by_record(d2, o2, oc2, tot2, seq, ids2, ids2)
+        seq += n2 << 12
+        snap_equal(ctx.state_snapshot(), st.snapshot())
+        # scan at t0 + 90 s with a 45 s interval: the devices last seen at t0 are missing
+        last, keys, found = ctx.presence_scan(t0 + 90_000, 45_000)
+        olast, okeys = st.presence_scan(t0 + 90_000, 45_000)
+        assert found == len(okeys) and 150 < found < 300
+        assert np.array_equal(last.astype(np.uint64), olast) and keys == okeys
+        assert all(k[2] == 0x7F for k in keys)
+        # the same scan again reports nothing (SendOnce); the snapshot shows the presenceMissingDate
+        last, keys, found = ctx.presence_scan(t0 + 91_000, 45_000)
+        assert found == 0 and st.presence_scan(t0 + 91_000, 45_000)[1] == []
+        snap_equal(ctx.state_snapshot(), st.snapshot())
+        # batch 3 (t0 + 120 s), JSON: some missing devices come back -> presenceMissingDate cleared
+        jrecs = [S.json_measurement(S.token_str(d), "fuel.level", "1.5", S.EVENT_DATE_BASE + d) for d in range(50, 250, 3)]
+        dj, oj = S.pack_records(jrecs)
+        ctx.set_option("state.presence_now_ms", t0 + 120_000)
+        st.set_presence_now(t0 + 120_000)
+        idj = np.arange(len(jrecs), dtype=np.uint64)
+        rows = ctx.decode_merge("json", dj, oj, seq, idj, idj)
+        ocj, _, _, totj = oracle.decode_json(dj, oj)
+        st.merge_by_record(dj, oj, ocj, totj, seq, idj, idj)
+        seq += len(jrecs) << 12
+        snap_equal(ctx.state_snapshot(), st.snapshot())
+        # a later scan with room for 10 devices only: 10 reported and marked, E_CAPACITY semantics, the rest next time
+        last, keys, found = ctx.presence_scan(t0 + 400_000, 100_000, max_devices=10)
+        assert len(keys) == 10 and found > 10
+        olast, okeys = st.presence_scan(t0 + 400_000, 100_000)
+        assert found == len(okeys)
+        last2, keys2, found2 = ctx.presence_scan(t0 + 400_000, 100_000)
+        assert found2 == found - 10 and sorted(keys + keys2) == sorted(okeys)
+        snap_equal(ctx.state_snapshot(), st.snapshot())
+    finally:
+        ctx.set_option("state.presence_now_ms", 0)
+        ctx.state_clear()

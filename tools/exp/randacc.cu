@@ -9,7 +9,13 @@ __device__ __forceinline__ uint64_t mix(uint64_t h) {
     h ^= h >> 33; h *= 0xff51afd7ed558ccdull; h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ull; h ^= h >> 33;
     return h;
 }
-template <int MODE>  // 0 read 64 B; 1 + atomicMax; 2 + 32-byte store; 3 atomicMax only (no read); 4 read 32 B only
+__device__ __forceinline__ void st256(uint64_t *p, uint64_t a, uint64_t b, uint64_t c, uint64_t d) {
+    asm volatile("st.global.v4.u64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(a), "l"(b), "l"(c), "l"(d) : "memory");
+}
+// 0 read 64 B; 1 + atomicMax; 2 + 32-byte store as two 16-byte stores; 3 atomicMax only (no read); 4 read 32 B only;
+// 5 = 2 with ONE 256-bit store (a full sector: no fill read); 6 = 5 with the payload in the sector next to `best`
+// (words 4..7: key words 2..5 would move to sector 2)... i.e. read sectors 0 and 2, atomic on 0, 256-bit store to 1
+template <int MODE>
 __global__ void __launch_bounds__(256) k(uint64_t *tab, uint64_t mask, uint64_t n, uint64_t seed, uint64_t *sink) {
     const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
     if (i >= n) return;
@@ -19,11 +25,12 @@ __global__ void __launch_bounds__(256) k(uint64_t *tab, uint64_t mask, uint64_t 
         ulonglong2 a0 = __ldcg((const ulonglong2 *)w), a1 = __ldcg((const ulonglong2 *)(w + 2));
         acc = a0.x ^ a0.y ^ a1.x ^ a1.y;
         if (MODE != 4) {
-            ulonglong2 a2 = __ldcg((const ulonglong2 *)(w + 4)), a3 = __ldcg((const ulonglong2 *)(w + 6));
+            const int o = MODE == 6 ? 8 : 4;
+            ulonglong2 a2 = __ldcg((const ulonglong2 *)(w + o)), a3 = __ldcg((const ulonglong2 *)(w + o + 2));
             acc ^= a2.x ^ a2.y ^ a3.x ^ a3.y;
         }
     }
-    if (MODE == 1 || MODE == 2 || MODE == 3) {
+    if (MODE == 1 || MODE == 2 || MODE == 3 || MODE == 5 || MODE == 6) {
         const unsigned long long old = atomicMax((unsigned long long *)(w + 1), (unsigned long long)(seed + i + (acc & 1)));
         acc ^= old;
     }
@@ -31,6 +38,8 @@ __global__ void __launch_bounds__(256) k(uint64_t *tab, uint64_t mask, uint64_t 
         *(ulonglong2 *)(w + 8) = make_ulonglong2(i, acc);
         *(ulonglong2 *)(w + 10) = make_ulonglong2(seed, i);
     }
+    if (MODE == 5) st256(w + 8, i, acc, seed, i);
+    if (MODE == 6) st256(w + 4, i, acc, seed, i);
     if (acc == 0x1234567) *sink = acc;
 }
 template <int MODE> float run(uint64_t *tab, uint64_t mask, uint64_t n, uint64_t *sink) {
@@ -48,13 +57,15 @@ template <int MODE> float run(uint64_t *tab, uint64_t mask, uint64_t n, uint64_t
 int main() {
     const uint64_t n = 10000000;
     uint64_t *sink; cudaMalloc(&sink, 8);
-    const char *names[] = {"read64", "read64+atomicMax", "read64+atomicMax+store32", "atomicMax only", "read32"};
+    const char *names[] = {"read64", "read64+atomicMax", "read64+atomicMax+store32 (2 x 16 B)", "atomicMax only", "read32",
+                           "read64+atomicMax+store32 (one 256-bit store)", "read sectors 0,2 + atomicMax + 256-bit store to sector 1"};
     for (uint64_t slots = 1ull << 20; slots <= (1ull << 26); slots <<= 2) {  // 128 MB .. 8 GB
         uint64_t *tab; if (cudaMalloc(&tab, slots * 128) != cudaSuccess) break;
         cudaMemset(tab, 0, slots * 128);
-        float t[5] = {run<0>(tab, slots - 1, n, sink), run<1>(tab, slots - 1, n, sink), run<2>(tab, slots - 1, n, sink),
-                      run<3>(tab, slots - 1, n, sink), run<4>(tab, slots - 1, n, sink)};
-        for (int m = 0; m < 5; m++)
+        float t[7] = {run<0>(tab, slots - 1, n, sink), run<1>(tab, slots - 1, n, sink), run<2>(tab, slots - 1, n, sink),
+                      run<3>(tab, slots - 1, n, sink), run<4>(tab, slots - 1, n, sink), run<5>(tab, slots - 1, n, sink),
+                      run<6>(tab, slots - 1, n, sink)};
+        for (int m = 0; m < 7; m++)
             printf("{\"table_MB\": %llu, \"variant\": \"%s\", \"ms_per_10M_rows\": %.4f, \"rows_per_s\": %.4e}\n",
                    (unsigned long long)(slots * 128 >> 20), names[m], t[m], n / (t[m] * 1e-3));
         cudaFree(tab);
