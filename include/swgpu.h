@@ -276,6 +276,22 @@ int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const uint8_t *by
                                uint32_t *first_row, uint32_t *out_rows, uint64_t max_pairs, uint64_t *pairs,
                                uint64_t *n_pairs, uint32_t chunk_records);
 
+/* Start-up sizing (no counterpart in the reference): allocates every device and pinned buffer that
+ * swgpu_decode_zone_test needs for batches of up to max_records records / max_bytes payload bytes, so that no
+ * cudaMalloc / cudaFree — which stall every stream of the device, other contexts' included — happens once batches
+ * are flowing.  (A batch whose rows or alerts outnumber its records still grows its buffers.)                    */
+int32_t swgpu_reserve_batch(swgpu_ctx *ctx, uint32_t max_records, uint64_t max_bytes);
+/* Asynchronous form of swgpu_decode_zone_test (no counterpart in the reference, whose decoders are called
+ * synchronously per payload): the call is queued on a worker thread owned by the context and *ticket identifies
+ * it; swgpu_wait(ticket) blocks until it is done and returns ITS status (outputs valid then; swgpu_last_error has
+ * the text).  Tickets complete in submission order.  Until every ticket has been waited for, the buffers passed in
+ * belong to the library and no other call may be made on the context.                                             */
+int32_t swgpu_submit_decode_zone_test(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off,
+                                      uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
+                                      uint32_t *first_row, uint32_t *out_rows, uint64_t max_pairs, uint64_t *pairs,
+                                      uint64_t *n_pairs, uint32_t chunk_records, uint64_t *ticket);
+int32_t swgpu_wait(swgpu_ctx *ctx, uint64_t ticket);
+
 /* Allocation-free form of swgpu_zone_test_dev.  It has no counterpart in the reference: it exists
  * for callers of this library that must not allocate device memory while a batch is in flight —
  * the rule-processing consumer thread when other contexts of the same process have work on the GPU

@@ -138,145 +138,148 @@ __device__ __forceinline__ void mg_flush_counts(const MgTable &t, MgLocalCnt *lo
         local->keys = local->bytes = 0;
     }
 }
+// One upsert.  DEVICE = true: the device's presence row (see mg_upsert): every writer stores the same values, so no
+// fix-up, and a row that finds the batch's timestamp already there has nothing to do.
+template <bool DEVICE, typename KeyRd>
+__device__ __forceinline__ void mg_upsert_one(const MgTable &t, MgLocalCnt *local, uint64_t h, uint32_t tl, uint32_t nl,
+                                              uint32_t kindbyte, const KeyRd &key, uint64_t seq1, uint64_t id_hi, uint64_t id_lo,
+                                              uint64_t date, uint64_t value) {
+    const uint32_t nw = mg_key_words(tl, nl);
+    const bool inl = nw <= MG_KEY_INLINE_WORDS;
+    const uint64_t hdr = mg_key_hdr(tl, nl, kindbyte) | (inl ? 0ull : MG_HDR_LONG);
+    // key words 0..5 in registers (requested before the table is probed: their loads and the slot's random,
+    // DRAM-latency load are in flight together); words 6..9 are read again on demand
+    uint64_t kw[6];
+    kw[0] = hdr;
+    bool haszero = false;  // a zero word cannot tell "not written yet" from "written": such keys take the ordered path
+#pragma unroll
+    for (uint32_t i = 1; i < 6; i++) {
+        kw[i] = (inl && i < nw) ? key.word(i) : 0ull;
+        haszero |= (inl && i < nw && kw[i] == 0ull);
+    }
+    if (inl)
+        for (uint32_t i = 6; i < nw; i++) haszero |= key.word(i) == 0ull;
+    const uint64_t want = (h & ~7ull) | 1ull;
+    uint64_t s = (h >> 3) & t.mask;
+    bool found = false, inserted = false, dropped = false;
+    // (the table is kept at most half full, so probe sequences are short; the bound only keeps a table that a
+    //  device-resident caller overfilled from spinning: such rows are counted in table_full)
+    const uint64_t max_probes = t.mask < MG_MAX_PROBES ? t.mask + 1 : MG_MAX_PROBES;
+    for (uint64_t probes = 0; probes < max_probes; probes++, s = (s + 1) & t.mask) {
+        uint64_t *w = t.slots[s].w;
+        // optimistic read of sectors 0-1: tag, best and key words 0..5 in one round trip
+        const ulonglong2 a0 = mg_ldcg2(w + 0), a1 = mg_ldcg2(w + 2), a2 = mg_ldcg2(w + 4), a3 = mg_ldcg2(w + 6);
+        uint64_t tag = a0.x;
+        if (tag == 0) {
+            const unsigned long long old = atomicCAS((unsigned long long *)w, 0ull, (unsigned long long)(want | MG_PENDING));
+            if (old == 0) {  // claimed: publish the key words, then clear the pending bit
+                bool ok = true;
+                if (inl) {
+                    *(ulonglong2 *)(w + 2) = make_ulonglong2(kw[0], kw[1]);
+                    *(ulonglong2 *)(w + 4) = make_ulonglong2(kw[2], kw[3]);
+                    *(ulonglong2 *)(w + 6) = make_ulonglong2(kw[4], kw[5]);
+                    for (uint32_t i = 6; i < nw; i++) w[MG_W_KEY6 + i - 6] = key.word(i);
+                } else {
+                    const unsigned long long off = atomicAdd(&t.ctr->arena_top, (unsigned long long)(nw - 1));
+                    if (off + (nw - 1) > t.arena_cap) {
+                        // no room for the key words: the reservation is handed back (an allocation that succeeds
+                        // lies wholly below the end of the arena, one that fails reaches beyond it, so they never
+                        // overlap), the words asked for are counted so that the host can grow the arena and replay
+                        // the batch, and the slot becomes a tombstone (it cannot be freed: other keys may already
+                        // have probed past it)
+                        atomicAdd(&t.ctr->arena_top, (unsigned long long)(0ull - (unsigned long long)(nw - 1)));
+                        atomicAdd(&t.ctr->arena_full, (unsigned long long)(nw - 1));
+                        ok = false;
+                    } else {
+                        for (uint32_t i = 1; i < nw; i++) t.arena[off + i - 1] = key.word(i);
+                        *(ulonglong2 *)(w + 2) = make_ulonglong2(hdr, (uint64_t)off);
+                        w[4] = nw;
+                    }
+                }
+                __threadfence();
+                mg_st_release_u64(w, ok ? want : MG_TOMB);
+                if (!ok) {
+                    dropped = true;
+                    break;
+                }
+                found = inserted = true;
+                break;
+            }
+            tag = old;  // somebody else claimed it first: is it our key?
+        }
+        if ((tag & ~MG_PENDING) != want) continue;  // another key (or a tombstone)
+        bool eq = false, settled = false;
+        if (tag == want && a0.x == want && inl && !haszero) {
+            // every word we hold is non-zero and a slot's key words only ever go from zero to their final
+            // value: if all of them compare equal, they are the published key, whatever the order in which
+            // the loads above were served
+            eq = a1.x == kw[0] && a1.y == kw[1] && a2.x == kw[2] && a2.y == kw[3] && a3.x == kw[4] && a3.y == kw[5];
+            for (uint32_t i = 6; eq && i < nw; i++) eq = __ldcg(w + MG_W_KEY6 + i - 6) == key.word(i);
+            settled = eq;  // a mismatch may be a stale read: look again below
+        }
+        if (!settled) {
+            // ordered re-read: wait for the claimer, then compare (acquire: the key words are visible)
+            tag = mg_ld_acquire_u64(w);
+            while (tag & MG_PENDING) tag = mg_ld_acquire_u64(w);
+            eq = tag == want && __ldcg(w + MG_W_KEY0) == hdr;
+            if (eq && inl) {
+                for (uint32_t i = 1; eq && i < nw; i++)
+                    eq = __ldcg(w + (i < 6 ? MG_W_KEY0 + i : MG_W_KEY6 + i - 6)) == key.word(i);
+            } else if (eq) {
+                const uint64_t off = __ldcg(w + MG_W_KEY0 + 1);
+                eq = __ldcg(w + MG_W_KEY0 + 2) == nw;
+                for (uint32_t i = 1; eq && i < nw; i++) eq = __ldcg(t.arena + off + i - 1) == key.word(i);
+            }
+        }
+        if (eq) {
+            found = true;
+            break;
+        }
+    }
+    if (inserted) {
+        // key counters: summed per warp in shared memory, flushed once per warp by mg_flush_counts
+        atomicAdd(&local->keys, 1u);
+        atomicAdd(&local->bytes, 3u + tl + nl);
+    }
+    if (!found) {
+        if (!dropped) atomicAdd(&t.ctr->table_full, 1ull);  // every slot probed
+        return;
+    }
+    uint64_t *w = t.slots[s].w;
+    const unsigned long long old = atomicMax((unsigned long long *)(w + MG_W_BEST), (unsigned long long)seq1);
+    if (old > seq1) return;                // a newer event is already there
+    if (DEVICE && old == seq1) return;     // the device row was touched by another row of this batch already
+    mg_store_payload(w, id_hi, id_lo, date, value);
+    if (!DEVICE && old > t.seq_floor && old != seq1) {  // the previous value was set by an older row of this launch
+        const unsigned long long k = atomicAdd(&t.ctr->n_fix, 1ull);
+        if (k < t.fix_cap) {
+            MgFix f;
+            f.slot = s;
+            f.seq1 = seq1;
+            f.id_hi = id_hi;
+            f.id_lo = id_lo;
+            f.date = date;
+            f.value = value;
+            t.fix[k] = f;
+        } else
+            atomicAdd(&t.ctr->fix_overflow, 1ull);
+    }
+}
+// the device row of a merged event, out of line: the hot path's registers are not shared with it
+template <typename KeyRd>
+__device__ __noinline__ void mg_touch_device(const MgTable &t, MgLocalCnt *local, uint64_t th, uint32_t tl, const KeyRd &key) {
+    mg_upsert_one<true>(t, local, mg_mix(th, 0ull, MG_KIND_DEVICE), tl, 0u, MG_KIND_DEVICE, key, t.presence_now1, 0ull, 0ull, 0ull,
+                        0ull);
+}
 // When the table tracks presence (t.presence_now1 != 0) every row also touches its device's row — key (token,
 // MG_KIND_DEVICE, no name): best := the batch's timestamp + 1 (lastInteractionDate), payload cleared
 // (presenceMissingDate := null), as DeviceStateProcessingLogic.processDeviceStateEvent does for every merged event
-// (DeviceStateProcessingLogic.java:142-143).  Same code, second pass of the loop below; every writer stores the same
-// values, so that pass needs no fix-up.
+// (DeviceStateProcessingLogic.java:142-143).
 template <typename KeyRd>
 __device__ __forceinline__ void mg_upsert(const MgTable &t, MgLocalCnt *local, uint64_t h, uint64_t th, uint32_t tl, uint32_t nl,
                                           uint32_t kindbyte, const KeyRd &key, uint64_t seq1, uint64_t id_hi, uint64_t id_lo,
                                           uint64_t date, uint64_t value) {
-    const int npass = t.presence_now1 ? 2 : 1;
-#pragma unroll 1
-    for (int pass = 0; pass < npass; pass++) {
-        if (pass) {  // the device row
-            nl = 0;
-            kindbyte = MG_KIND_DEVICE;
-            h = mg_mix(th, 0ull, MG_KIND_DEVICE);
-            seq1 = t.presence_now1;
-            id_hi = id_lo = date = value = 0ull;
-        }
-        const uint32_t nw = mg_key_words(tl, nl);
-        const bool inl = nw <= MG_KEY_INLINE_WORDS;
-        const uint64_t hdr = mg_key_hdr(tl, nl, kindbyte) | (inl ? 0ull : MG_HDR_LONG);
-        // key words 0..5 in registers (requested before the table is probed: their loads and the slot's random,
-        // DRAM-latency load are in flight together); words 6..9 are read again on demand
-        uint64_t kw[6];
-        kw[0] = hdr;
-        bool haszero = false;  // a zero word cannot tell "not written yet" from "written": such keys take the ordered path
-#pragma unroll
-        for (uint32_t i = 1; i < 6; i++) {
-            kw[i] = (inl && i < nw) ? key.word(i) : 0ull;
-            haszero |= (inl && i < nw && kw[i] == 0ull);
-        }
-        if (inl)
-            for (uint32_t i = 6; i < nw; i++) haszero |= key.word(i) == 0ull;
-        const uint64_t want = (h & ~7ull) | 1ull;
-        uint64_t s = (h >> 3) & t.mask;
-        bool found = false, inserted = false, dropped = false;
-        // (the table is kept at most half full, so probe sequences are short; the bound only keeps a table that a
-        //  device-resident caller overfilled from spinning: such rows are counted in table_full)
-        const uint64_t max_probes = t.mask < MG_MAX_PROBES ? t.mask + 1 : MG_MAX_PROBES;
-        for (uint64_t probes = 0; probes < max_probes; probes++, s = (s + 1) & t.mask) {
-            uint64_t *w = t.slots[s].w;
-            // optimistic read of sectors 0-1: tag, best and key words 0..5 in one round trip
-            const ulonglong2 a0 = mg_ldcg2(w + 0), a1 = mg_ldcg2(w + 2), a2 = mg_ldcg2(w + 4), a3 = mg_ldcg2(w + 6);
-            uint64_t tag = a0.x;
-            if (tag == 0) {
-                const unsigned long long old = atomicCAS((unsigned long long *)w, 0ull, (unsigned long long)(want | MG_PENDING));
-                if (old == 0) {  // claimed: publish the key words, then clear the pending bit
-                    bool ok = true;
-                    if (inl) {
-                        *(ulonglong2 *)(w + 2) = make_ulonglong2(kw[0], kw[1]);
-                        *(ulonglong2 *)(w + 4) = make_ulonglong2(kw[2], kw[3]);
-                        *(ulonglong2 *)(w + 6) = make_ulonglong2(kw[4], kw[5]);
-                        for (uint32_t i = 6; i < nw; i++) w[MG_W_KEY6 + i - 6] = key.word(i);
-                    } else {
-                        const unsigned long long off = atomicAdd(&t.ctr->arena_top, (unsigned long long)(nw - 1));
-                        if (off + (nw - 1) > t.arena_cap) {
-                            // no room for the key words: the reservation is handed back (an allocation that succeeds
-                            // lies wholly below the end of the arena, one that fails reaches beyond it, so they never
-                            // overlap), the words asked for are counted so that the host can grow the arena and replay
-                            // the batch, and the slot becomes a tombstone (it cannot be freed: other keys may already
-                            // have probed past it)
-                            atomicAdd(&t.ctr->arena_top, (unsigned long long)(0ull - (unsigned long long)(nw - 1)));
-                            atomicAdd(&t.ctr->arena_full, (unsigned long long)(nw - 1));
-                            ok = false;
-                        } else {
-                            for (uint32_t i = 1; i < nw; i++) t.arena[off + i - 1] = key.word(i);
-                            *(ulonglong2 *)(w + 2) = make_ulonglong2(hdr, (uint64_t)off);
-                            w[4] = nw;
-                        }
-                    }
-                    __threadfence();
-                    mg_st_release_u64(w, ok ? want : MG_TOMB);
-                    if (!ok) {
-                        dropped = true;
-                        break;
-                    }
-                    found = inserted = true;
-                    break;
-                }
-                tag = old;  // somebody else claimed it first: is it our key?
-            }
-            if ((tag & ~MG_PENDING) != want) continue;  // another key (or a tombstone)
-            bool eq = false, settled = false;
-            if (tag == want && a0.x == want && inl && !haszero) {
-                // every word we hold is non-zero and a slot's key words only ever go from zero to their final
-                // value: if all of them compare equal, they are the published key, whatever the order in which
-                // the loads above were served
-                eq = a1.x == kw[0] && a1.y == kw[1] && a2.x == kw[2] && a2.y == kw[3] && a3.x == kw[4] && a3.y == kw[5];
-                for (uint32_t i = 6; eq && i < nw; i++) eq = __ldcg(w + MG_W_KEY6 + i - 6) == key.word(i);
-                settled = eq;  // a mismatch may be a stale read: look again below
-            }
-            if (!settled) {
-                // ordered re-read: wait for the claimer, then compare (acquire: the key words are visible)
-                tag = mg_ld_acquire_u64(w);
-                while (tag & MG_PENDING) tag = mg_ld_acquire_u64(w);
-                eq = tag == want && __ldcg(w + MG_W_KEY0) == hdr;
-                if (eq && inl) {
-                    for (uint32_t i = 1; eq && i < nw; i++)
-                        eq = __ldcg(w + (i < 6 ? MG_W_KEY0 + i : MG_W_KEY6 + i - 6)) == key.word(i);
-                } else if (eq) {
-                    const uint64_t off = __ldcg(w + MG_W_KEY0 + 1);
-                    eq = __ldcg(w + MG_W_KEY0 + 2) == nw;
-                    for (uint32_t i = 1; eq && i < nw; i++) eq = __ldcg(t.arena + off + i - 1) == key.word(i);
-                }
-            }
-            if (eq) {
-                found = true;
-                break;
-            }
-        }
-        if (inserted) {
-            // key counters: summed per warp in shared memory, flushed once per warp by mg_flush_counts
-            atomicAdd(&local->keys, 1u);
-            atomicAdd(&local->bytes, 3u + tl + nl);
-        }
-        if (!found) {
-            if (!dropped) atomicAdd(&t.ctr->table_full, 1ull);  // every slot probed
-            continue;
-        }
-        uint64_t *w = t.slots[s].w;
-        const unsigned long long old = atomicMax((unsigned long long *)(w + MG_W_BEST), (unsigned long long)seq1);
-        if (old > seq1) continue;              // a newer event is already there
-        if (pass && old == seq1) continue;     // the device row was touched by another row of this batch already
-        mg_store_payload(w, id_hi, id_lo, date, value);
-        if (!pass && old > t.seq_floor && old != seq1) {  // the previous value was set by an older row of this launch
-            const unsigned long long k = atomicAdd(&t.ctr->n_fix, 1ull);
-            if (k < t.fix_cap) {
-                MgFix f;
-                f.slot = s;
-                f.seq1 = seq1;
-                f.id_hi = id_hi;
-                f.id_lo = id_lo;
-                f.date = date;
-                f.value = value;
-                t.fix[k] = f;
-            } else
-                atomicAdd(&t.ctr->fix_overflow, 1ull);
-        }
-    }
+    mg_upsert_one<false>(t, local, h, tl, nl, kindbyte, key, seq1, id_hi, id_lo, date, value);
+    if (t.presence_now1) mg_touch_device(t, local, th, tl, key);
 }
 #endif  // __CUDACC__

@@ -7,6 +7,12 @@
 // Replaces, for a batch: IDeviceEventDecoder.decode per payload (ES/spi/IDeviceEventDecoder.java:39) followed by
 // ZoneTestRuleProcessor.onLocation per decoded location (RP/processors/geospatial/ZoneTestRuleProcessor.java:47-63)
 // and, when asked, DeviceStateProcessingLogic.process (DS/processing/DeviceStateProcessingLogic.java:65-67).
+#include <condition_variable>
+#include <deque>
+#include <functional>
+#include <map>
+#include <thread>
+
 #include "swgpu_common.cuh"
 
 int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
@@ -46,12 +52,29 @@ struct Pipeline {
     // small-batch path: one staging block each way, host (pinned) and device
     swgpu_ctx::Buf sm_hin, sm_hout, sm_din, sm_dout;
     bool ready = false;
+    // swgpu_submit_decode_zone_test: one worker thread per context runs the queued calls in order
+    std::thread worker;
+    std::mutex qmu;
+    std::condition_variable qcv, dcv;
+    std::deque<std::pair<uint64_t, std::function<int()>>> queue;
+    std::map<uint64_t, int> done;
+    uint64_t next_ticket = 1;
+    bool stop = false;
 };
+static void pl_sync_streams(swgpu_ctx *ctx) {
+    Pipeline *p = (Pipeline *)ctx->pipeline;
+    cudaStreamSynchronize(ctx->stream);
+    if (p && p->s_in) cudaStreamSynchronize(p->s_in);
+    if (p && p->s_out) cudaStreamSynchronize(p->s_out);
+}
 
+static void pl_sync_streams(swgpu_ctx *ctx);
 static int pl_ensure_buf(swgpu_ctx *ctx, swgpu_ctx::Buf &b, size_t bytes) {
     if (bytes <= b.cap) return SWGPU_OK;
     if (b.p) {
-        SW_CUDA(ctx, cudaDeviceSynchronize());
+        // growth after start-up (swgpu_reserve_batch avoids it): wait for this context's three streams — not
+        // for the device — before the old buffer goes.  cudaFree itself still serialises with the other contexts.
+        pl_sync_streams(ctx);
         SW_CUDA(ctx, cudaFree(b.p));
         b.p = nullptr;
         b.cap = 0;
@@ -104,6 +127,14 @@ static int pl_get(swgpu_ctx *ctx, Pipeline **out) {
 void sw_pipeline_free(swgpu_ctx *ctx) {
     Pipeline *p = (Pipeline *)ctx->pipeline;
     if (!p) return;
+    if (p->worker.joinable()) {
+        {
+            std::lock_guard<std::mutex> lk(p->qmu);
+            p->stop = true;
+        }
+        p->qcv.notify_all();
+        p->worker.join();
+    }
     for (int i = 0; i < PL_SLOTS; i++) {
         PlSlot &s = p->slot[i];
         swgpu_ctx::Buf *bufs[] = {&s.bytes, &s.off, &s.cols, &s.status, &s.first, &s.pairs, &s.counts};
@@ -197,6 +228,79 @@ static int pl_small(swgpu_ctx *ctx, Pipeline *p, int32_t format, const uint8_t *
     return SWGPU_OK;
 }
 
+// Chunk size when the caller leaves it to us: about a dozen chunks per call.  Each chunk costs ~30 driver calls on the
+// calling thread (~0.1 ms), so many small chunks make the host the bottleneck; a few large ones leave the first upload
+// and the last download uncovered.  Measured on 10 M events: 64 K records per chunk 32.9 ms, 256 K 17.7 ms, 1 M
+// 15.3 ms, 2 M 16.2 ms.
+static uint32_t pl_chunk_records(uint32_t n) {
+    const uint64_t want = ((uint64_t)n / 12 + 65535) / 65536 * 65536;
+    return (uint32_t)(want < 131072 ? 131072 : want > 1048576 ? 1048576 : want);
+}
+
+// size the three ring slots for chunks of C records / chunk_bytes payload bytes / C alert pairs
+static int pl_size_slots(swgpu_ctx *ctx, Pipeline *p, uint32_t C, uint64_t chunk_bytes, int nslots) {
+    for (int i = 0; i < PL_SLOTS && i < nslots; i++) {
+        PlSlot &s = p->slot[i];
+        if (int rc = pl_ensure_buf(ctx, s.bytes, chunk_bytes + 64)) return rc;
+        if (int rc = pl_ensure_buf(ctx, s.off, (size_t)(C + 1) * 8)) return rc;
+        if (s.rows_cap < C) {
+            if (int rc = pl_ensure_buf(ctx, s.cols, (size_t)C * 8 * PL_NCOL)) return rc;
+            s.rows_cap = C;
+        }
+        if (int rc = pl_ensure_buf(ctx, s.status, (size_t)C + 16)) return rc;
+        if (int rc = pl_ensure_buf(ctx, s.first, (size_t)(C + 2) * 4)) return rc;
+        if (s.pairs_cap < C) {
+            if (int rc = pl_ensure_buf(ctx, s.pairs, (size_t)C * 8)) return rc;
+            s.pairs_cap = C;
+        }
+        if (int rc = pl_ensure_buf(ctx, s.counts, 64)) return rc;
+    }
+    return sw_ensure_scratch(ctx, SW_SCRATCH_HDR + ((size_t)C / 32 + 64) * 8);  // warp-tile scan states
+}
+
+// Allocate, at start-up, everything swgpu_decode_zone_test needs for batches of up to max_records records and
+// max_bytes payload bytes, so that no cudaMalloc / cudaFree (which stall every stream of the device, the other
+// contexts' too) happens once batches are flowing.  A batch that decodes to more rows than records (measurement
+// fan-out) or fires more alerts than records still grows its slot.
+extern "C" int32_t swgpu_reserve_batch(swgpu_ctx *ctx, uint32_t max_records, uint64_t max_bytes) {
+    if (!ctx) return SWGPU_E_INVALID;
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    Pipeline *p;
+    if (int rc = pl_get(ctx, &p)) return rc;
+    if (max_records == 0) return SWGPU_OK;
+    // the small-batch block (one staging block each way)
+    {
+        const uint32_t n = max_records < PL_SMALL_MAX ? max_records : PL_SMALL_MAX;
+        const uint64_t total = max_records <= PL_SMALL_MAX ? max_bytes : (max_bytes / max_records + 1) * n * 2;
+        const uint32_t rows_cap = n + 64;
+        const uint64_t pairs_cap = (uint64_t)n * 2 + 1024;
+        const size_t in_bytes = PL_ALIGN((size_t)(n + 1) * 8) + PL_ALIGN(total + 64);
+        const size_t out_bytes = 256 + PL_ALIGN((size_t)(n + 2) * 4) + PL_ALIGN((size_t)n + 16) +
+                                 PL_ALIGN((size_t)rows_cap * 8 * PL_NCOL) + PL_ALIGN(pairs_cap * 8);
+        if (int rc = sw_ensure_pinned(ctx, p->sm_hin, in_bytes)) return rc;
+        if (int rc = sw_ensure_pinned(ctx, p->sm_hout, out_bytes)) return rc;
+        if (int rc = sw_ensure(ctx, p->sm_din, in_bytes)) return rc;
+        if (int rc = sw_ensure(ctx, p->sm_dout, out_bytes)) return rc;
+        if (int rc = sw_ensure(ctx, ctx->d_zwork, ((size_t)rows_cap * 8 + 255) / 256 * 256 + (size_t)(rows_cap / 256 + 2) * 16 + 64))
+            return rc;
+    }
+    if (max_records > PL_SMALL_MAX) {
+        const uint32_t C = pl_chunk_records(max_records);
+        const uint32_t nchunks = (max_records + C - 1) / C;
+        // a chunk's payload: its share of the batch with a margin for uneven record sizes
+        const uint64_t chunk_bytes = nchunks <= 1 ? max_bytes : (uint64_t)((double)max_bytes / max_records * C * 1.25) + 65536;
+        if (int rc = pl_size_slots(ctx, p, C, chunk_bytes, PL_SLOTS)) return rc;
+        if (int rc = sw_ensure(ctx, ctx->d_zwork, ((size_t)C * 8 + 255) / 256 * 256 + (size_t)(C / 256 + 2) * 16 + 64)) return rc;
+        if ((size_t)nchunks + 1 > p->row_totals_cap) {
+            SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            if (p->row_totals) SW_CUDA(ctx, cudaFree(p->row_totals));
+            p->row_totals_cap = (size_t)nchunks + 64;
+            SW_CUDA(ctx, cudaMalloc((void **)&p->row_totals, sizeof(uint32_t) * p->row_totals_cap));
+        }
+    }
+    return SWGPU_OK;
+}
+
 extern "C" int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off,
                                           uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
                                           uint32_t *first_row, uint32_t *out_rows, uint64_t max_pairs, uint64_t *pairs,
@@ -225,15 +329,7 @@ extern "C" int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const 
         *out_rows = 0;  // did not fit the small block: the ring below re-runs it with exact sizes
         *n_pairs = 0;
     }
-    // Chunk size when the caller leaves it to us: about a dozen chunks per call.  Each chunk costs ~30 driver
-    // calls on this thread (~0.1 ms), so many small chunks make the host the bottleneck; a few large ones
-    // leave the first upload and the last download uncovered.  Measured on 10 M events: 64 K records per
-    // chunk 32.9 ms, 256 K 17.7 ms, 1 M 15.3 ms, 2 M 16.2 ms.
-    uint32_t C = chunk_records;
-    if (!C) {
-        const uint64_t want = ((uint64_t)n / 12 + 65535) / 65536 * 65536;
-        C = (uint32_t)(want < 131072 ? 131072 : want > 1048576 ? 1048576 : want);
-    }
+    const uint32_t C = chunk_records ? chunk_records : pl_chunk_records(n);
     const uint32_t nchunks = (n + C - 1) / C;
     uint64_t *const *hcol = (uint64_t *const *)out;
 
@@ -246,23 +342,7 @@ extern "C" int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const 
     }
     // a DeviceMeasurements payload can fan out; the row capacity per chunk starts at the record
     // count and a chunk that overflows it is re-run with the exact size (rare)
-    for (int i = 0; i < PL_SLOTS && i < (int)nchunks; i++) {
-        PlSlot &s = p->slot[i];
-        if (int rc = pl_ensure_buf(ctx, s.bytes, max_chunk_bytes + 64)) return rc;
-        if (int rc = pl_ensure_buf(ctx, s.off, (size_t)(C + 1) * 8)) return rc;
-        if (s.rows_cap < C) {
-            if (int rc = pl_ensure_buf(ctx, s.cols, (size_t)C * 8 * PL_NCOL)) return rc;
-            s.rows_cap = C;
-        }
-        if (int rc = pl_ensure_buf(ctx, s.status, (size_t)C + 16)) return rc;
-        if (int rc = pl_ensure_buf(ctx, s.first, (size_t)(C + 2) * 4)) return rc;
-        if (s.pairs_cap < C) {
-            if (int rc = pl_ensure_buf(ctx, s.pairs, (size_t)C * 8)) return rc;
-            s.pairs_cap = C;
-        }
-        if (int rc = pl_ensure_buf(ctx, s.counts, 64)) return rc;
-    }
-    if (int rc = sw_ensure_scratch(ctx, SW_SCRATCH_HDR + ((size_t)C / 32 + 64) * 8)) return rc;  // warp-tile scan states
+    if (int rc = pl_size_slots(ctx, p, C, max_chunk_bytes, (int)nchunks)) return rc;
     // running row totals: entry k = rows before chunk k (device), ring of nchunks+1
     {
         if ((size_t)nchunks + 1 > p->row_totals_cap) {
@@ -321,7 +401,7 @@ extern "C" int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const 
         const PlCounts cnt = p->mail[c % PL_SLOTS];
         if (cnt.rows > s.rows_cap || cnt.pairs > s.pairs_cap) {
             // fan-out or many alerts: grow this slot and re-run the chunk synchronously (rare)
-            SW_CUDA(ctx, cudaDeviceSynchronize());
+            pl_sync_streams(ctx);
             if (cnt.rows > s.rows_cap) {
                 if (int rc = pl_ensure_buf(ctx, s.cols, (size_t)cnt.rows * 8 * PL_NCOL)) return rc;
                 s.rows_cap = cnt.rows;
@@ -336,7 +416,7 @@ extern "C" int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const 
             const PlCounts c2 = p->mail[c % PL_SLOTS];
             if (c2.rows > s.rows_cap || c2.pairs > s.pairs_cap) {
                 // the alert count depended on rows that were cut off the first time: once more
-                SW_CUDA(ctx, cudaDeviceSynchronize());
+                pl_sync_streams(ctx);
                 if (c2.pairs > s.pairs_cap) {
                     if (int rc = pl_ensure_buf(ctx, s.pairs, (size_t)c2.pairs * 8)) return rc;
                     s.pairs_cap = c2.pairs;
@@ -393,4 +473,69 @@ extern "C" int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const 
         return SWGPU_E_CAPACITY;
     }
     return SWGPU_OK;
+}
+
+
+// ---- asynchronous form -------------------------------------------------------------------------------------------------
+// swgpu_submit_decode_zone_test queues the same call on the context's worker thread and returns a ticket at once;
+// swgpu_wait blocks until that call is done and returns its status (the outputs are valid then).  The chunked ring
+// is driven from the host (it needs each chunk's counts to size the downloads), so the asynchronous form runs it
+// on a thread the library owns instead of the caller's: the binding's consumer thread can poll Kafka or stage the
+// next batch meanwhile.  Tickets complete in submission order.  While tickets are pending no other call may be made
+// on the context (calls on one context are serial); the caller's buffers belong to the library until swgpu_wait.
+static void pl_worker(Pipeline *p) {
+    for (;;) {
+        std::pair<uint64_t, std::function<int()>> job;
+        {
+            std::unique_lock<std::mutex> lk(p->qmu);
+            p->qcv.wait(lk, [&] { return p->stop || !p->queue.empty(); });
+            if (p->queue.empty()) return;  // stop
+            job = std::move(p->queue.front());
+            p->queue.pop_front();
+        }
+        const int rc = job.second();
+        {
+            std::lock_guard<std::mutex> lk(p->qmu);
+            p->done[job.first] = rc;
+        }
+        p->dcv.notify_all();
+    }
+}
+
+extern "C" int32_t swgpu_submit_decode_zone_test(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off,
+                                                 uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
+                                                 uint32_t *first_row, uint32_t *out_rows, uint64_t max_pairs, uint64_t *pairs,
+                                                 uint64_t *n_pairs, uint32_t chunk_records, uint64_t *ticket) {
+    if (!ctx || !ticket || !out) {
+        if (ctx) SW_SET_ERR(ctx, "swgpu_submit_decode_zone_test: NULL argument");
+        return SWGPU_E_INVALID;
+    }
+    Pipeline *p;
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (int rc = pl_get(ctx, &p)) return rc;
+    const swgpu_decoded_cols cols = *out;  // the struct is copied: only the arrays must outlive the call
+    std::lock_guard<std::mutex> lk(p->qmu);
+    if (!p->worker.joinable()) p->worker = std::thread(pl_worker, p);
+    const uint64_t t = p->next_ticket++;
+    p->queue.emplace_back(t, [=]() {
+        return (int)swgpu_decode_zone_test(ctx, format, bytes, rec_off, n, max_rows, &cols, status, first_row, out_rows, max_pairs,
+                                           pairs, n_pairs, chunk_records);
+    });
+    *ticket = t;
+    p->qcv.notify_one();
+    return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_wait(swgpu_ctx *ctx, uint64_t ticket) {
+    if (!ctx) return SWGPU_E_INVALID;
+    Pipeline *p = (Pipeline *)ctx->pipeline;
+    if (!p || ticket == 0 || ticket >= p->next_ticket) {
+        SW_SET_ERR(ctx, "swgpu_wait: unknown ticket %llu", (unsigned long long)ticket);
+        return SWGPU_E_INVALID;
+    }
+    std::unique_lock<std::mutex> lk(p->qmu);
+    p->dcv.wait(lk, [&] { return p->done.count(ticket) != 0; });
+    const int rc = p->done[ticket];
+    p->done.erase(ticket);
+    return rc;
 }
