@@ -156,8 +156,9 @@ int32_t swgpu_sync(swgpu_ctx *ctx);
  *                           (DS/processing/DeviceStateProcessingLogic.java:142-143; the reference takes new Date(),
  *                           here the caller supplies the batch's time so that results are reproducible); 0 = off
  *                           (default).  Set it before each batch.  Costs one more table access per event.
- *   "json.fast_path"        0 = every JSON record takes the general structural pass instead of trying the
- *                           straight-line pass for plainly shaped requests first (default 1)
+ *   "json.fast_path"        0 = every JSON record takes the general structural pass; 1 (default) = a record in
+ *                           exactly the shape the reference's own serialiser writes is first tried against that
+ *                           template (same result, far fewer instructions)
  *   "zone.stats"            1 = zone tests also count their work (read it with swgpu_zone_stats)        */
 int32_t swgpu_set_option(swgpu_ctx *ctx, const char *name, int64_t value);
 /* Pinned host staging the Java side wraps as a direct ByteBuffer / MemorySegment.             */

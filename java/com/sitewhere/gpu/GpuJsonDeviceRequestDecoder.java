@@ -135,8 +135,15 @@ public class GpuJsonDeviceRequestDecoder extends TenantEngineLifecycleComponent 
 		request.setUpdateState(true);
 	    }
 	    if ((flags & F_HAS_METADATA) != 0) {
-		// a flat string map: parsed here from its span (no nesting by construction, see DESIGN.md)
-		request.setMetadata(JsonFlatMap.read(payload, r.metadataSpan()));
+		// the span is the text of the metadata object, validated by the library as a flat object of scalar
+		// values: Jackson reads it into the Map<String, String> exactly as the reference's treeToValue does
+		long ms = r.metadataSpan();
+		try {
+		    request.setMetadata(METADATA_MAPPER.readValue(payload, (int) (ms & 0xffffffffL), (int) (ms >>> 32),
+			    METADATA_TYPE));
+		} catch (java.io.IOException e) {
+		    throw new EventDecodeException(e);
+		}
 	    }
 	    if ((flags & F_HAS_DATE) != 0) {
 		request.setEventDate(new Date(r.eventDate()));
@@ -154,35 +161,12 @@ public class GpuJsonDeviceRequestDecoder extends TenantEngineLifecycleComponent 
 	return results;
     }
 
+    private static final com.fasterxml.jackson.databind.ObjectMapper METADATA_MAPPER = new com.fasterxml.jackson.databind.ObjectMapper();
+    private static final com.fasterxml.jackson.databind.JavaType METADATA_TYPE = METADATA_MAPPER.getTypeFactory()
+	    .constructMapType(java.util.HashMap.class, String.class, String.class);
+
     static String span(byte[] payload, long s) {
 	return new String(payload, (int) (s & 0xffffffffL), (int) (s >>> 32), StandardCharsets.UTF_8);
-    }
-
-    /** {"k":"v",...} with plain (escape-free) strings, as the kernel guarantees for a span it hands out. */
-    static final class JsonFlatMap {
-	static java.util.Map<String, String> read(byte[] payload, long s) {
-	    java.util.Map<String, String> m = new java.util.HashMap<>();
-	    int p = (int) (s & 0xffffffffL), end = p + (int) (s >>> 32);
-	    String key = null;
-	    while (p < end) {
-		if (payload[p] == '"') {
-		    int q = p + 1;
-		    while (payload[q] != '"') {
-			q++;
-		    }
-		    String str = new String(payload, p + 1, q - p - 1, StandardCharsets.UTF_8);
-		    if (key == null) {
-			key = str;
-		    } else {
-			m.put(key, str);
-			key = null;
-		    }
-		    p = q;
-		}
-		p++;
-	    }
-	    return m;
-	}
     }
 
     public void setDeviceOrdinal(int deviceOrdinal) {

@@ -35,14 +35,42 @@ public class GpuZoneTestRuleProcessor extends RuleProcessor {
     private List<ZoneTest> zoneTests = new ArrayList<ZoneTest>();
     private int deviceOrdinal = 0;
     private int maxBatch = 65536;
+    /** a location waits at most this long for company before the pending batch is tested */
+    private long lingerMicros = 2000;
     private SwGpu.Context ctx;
     private final List<IDeviceLocation> pending = new ArrayList<>();
+    private java.util.concurrent.ScheduledExecutorService lingerTimer;
 
     @Override
     public void start(ILifecycleProgressMonitor monitor) throws SiteWhereException {
 	super.start(monitor);
 	ctx = new SwGpu.Context(deviceOrdinal);
 	uploadZones();
+	// The stock host (KafkaRuleProcessorHost.java:144-153,221-224) calls onLocation once per event from its
+	// thread pool and nothing else, so the flush cannot depend on the host: a timer tests whatever is
+	// pending every lingerMicros (alerts are delayed by at most that), and a full batch flushes at once.
+	lingerTimer = java.util.concurrent.Executors.newSingleThreadScheduledExecutor(r -> {
+	    Thread t = new Thread(r, "gpu-zone-test-linger");
+	    t.setDaemon(true);
+	    return t;
+	});
+	lingerTimer.scheduleWithFixedDelay(() -> {
+	    try {
+		flush();
+	    } catch (Throwable e) {
+		getLogger().error("GPU zone test flush failed.", e);
+	    }
+	}, lingerMicros, lingerMicros, java.util.concurrent.TimeUnit.MICROSECONDS);
+    }
+
+    @Override
+    public void stop(ILifecycleProgressMonitor monitor) throws SiteWhereException {
+	if (lingerTimer != null) {
+	    lingerTimer.shutdownNow();
+	}
+	flush();
+	ctx.close();
+	super.stop(monitor);
     }
 
     /** Flatten every test's zone bounds (as GeoUtils.createPolygonForLocations reads them) and upload. */
@@ -87,7 +115,7 @@ public class GpuZoneTestRuleProcessor extends RuleProcessor {
 	}
     }
 
-    /** Called by the host when a poll batch ends (or on a timer): test all pending locations at once. */
+    /** Test all pending locations at once: called by the linger timer, and by onLocation when a batch is full. */
     public synchronized void flush() throws SiteWhereException {
 	int n = pending.size();
 	if (n == 0) {
@@ -134,5 +162,13 @@ public class GpuZoneTestRuleProcessor extends RuleProcessor {
 
     public void setDeviceOrdinal(int deviceOrdinal) {
 	this.deviceOrdinal = deviceOrdinal;
+    }
+
+    public void setLingerMicros(long lingerMicros) {
+	this.lingerMicros = lingerMicros;
+    }
+
+    public void setMaxBatch(int maxBatch) {
+	this.maxBatch = maxBatch;
     }
 }

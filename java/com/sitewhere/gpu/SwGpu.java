@@ -20,7 +20,7 @@ import com.sitewhere.spi.SiteWhereException;
 public final class SwGpu {
 
     public static final int ST_OK = 0, ST_DECODE_EXCEPTION = 1, ST_RUNTIME_EXCEPTION = 2, ST_PASSTHROUGH = 3;
-    public static final int FMT_PROTOBUF = 0, FMT_JSON = 1;
+    public static final int FMT_PROTOBUF = 0, FMT_JSON = 1, FMT_ENRICHED = 2;
     public static final int E_CAPACITY = -4;
     /** swgpu_decoded_cols: 13 pointers (9 mandatory, 4 optional). */
     public static final long COLS_BYTES = 13 * 8;
@@ -57,6 +57,16 @@ public final class SwGpu {
     static final MethodHandle STATE_SNAPSHOT = h("swgpu_state_snapshot",
 	    FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG, JAVA_LONG, ADDRESS, ADDRESS));
     static final MethodHandle STATE_RESTORE = h("swgpu_state_restore", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG));
+    static final MethodHandle SET_OPTION = h("swgpu_set_option", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG));
+    static final MethodHandle RESERVE_BATCH = h("swgpu_reserve_batch", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_LONG));
+    static final MethodHandle DECODE_ENRICHED = h("swgpu_decode_enriched", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS,
+	    ADDRESS, JAVA_INT, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
+    static final MethodHandle SUBMIT_DECODE_ZONE_TEST = h("swgpu_submit_decode_zone_test",
+	    FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS, ADDRESS,
+		    ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, JAVA_INT, ADDRESS));
+    static final MethodHandle WAIT = h("swgpu_wait", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG));
+    static final MethodHandle PRESENCE_SCAN = h("swgpu_presence_scan", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG,
+	    JAVA_LONG, JAVA_LONG, JAVA_LONG, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
     static final MethodHandle PARTITION = h("swgpu_partition", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_INT));
 
     /** One native context: one GPU, one calling thread. */

@@ -10,8 +10,9 @@
 // the four envelope keys and the fourteen request properties, the LAST occurrence's value token
 // (kind, span, escape flags).  After the pass the envelope rules and the bean rules are applied to
 // those slots, numbers go through dparse.cuh (Clinger / Eisel-Lemire / exact fallback), dates through
-// the StdDateFormat rules.  Rows are placed by the ordered single-pass scan.  HBM-bound by design;
-// what limits it today is instruction issue (byte-at-a-time scanning), see DESIGN.md.
+// the StdDateFormat rules.  Before that general pass, a record is tried against the exact text the reference's own
+// serialiser writes (json_template_record): same row, an order of magnitude fewer instructions.  Rows are placed by
+// the optimistic dense pass + ordered redo, as in the protobuf decoder.
 #include "dparse.cuh"
 #include "merge_table.cuh"
 #include "swgpu_common.cuh"
@@ -40,7 +41,7 @@ struct JsArgs {
     MgTable mt;
     const uint64_t *id_hi, *id_lo;
     uint64_t seq_base;
-    uint32_t fast;  // option "json.fast_path": try the fast structural pass first (default 1)
+    uint32_t fast;  // option "json.fast_path": try the template recogniser first (default 1)
 };
 
 enum { JK_NONE = 0, JK_OBJECT, JK_ARRAY, JK_STRING, JK_INT, JK_FLOAT, JK_TRUE, JK_FALSE, JK_NULL };
@@ -248,181 +249,6 @@ struct JsonScan {
             return -1;
         }
         return -1;
-    }
-
-    // ---- fast structural pass for the common shape ---------------------------------------------------------------
-    // A request as clients send it: a root object whose members are the four envelope keys (each at most once, any
-    // order), scalar values, "request" an object of known request properties with scalar values; strings are plain
-    // printable ASCII (no escape, no control character, no byte >= 0x80).  For such a record this fills `slots`
-    // exactly as run() does, in straight-line code: no nesting stack, keys taken from two 8-byte loads and matched
-    // as words, strings closed by an 8-byte scan.  ANYTHING else — an unknown or repeated key, a container value, an
-    // escape, odd white space, a grammar error — returns 3 and the caller takes run() from the start, so this
-    // path never decides an error.  Only for records staged in shared memory (8-byte reads may run past the
-    // record's end, into the tile's slack).
-    static __device__ __forceinline__ uint64_t stop_mask(uint64_t w) {  // 0x80 in every byte that ends plain string content
-        const uint64_t l = w & 0x7f7f7f7f7f7f7f7full;
-        const uint64_t q = l ^ 0x2222222222222222ull, bs = l ^ 0x5c5c5c5c5c5c5c5cull;
-        return (w | ~(l + 0x6060606060606060ull) | ~(q + 0x7f7f7f7f7f7f7f7full) | ~(bs + 0x7f7f7f7f7f7f7f7full)) &
-               0x8080808080808080ull;
-    }
-    static __device__ __forceinline__ uint64_t low_bytes(uint64_t w, uint32_t k) {  // the first k (< 8) bytes of w
-        return w & ((1ull << (8 * k)) - 1ull);
-    }
-    static constexpr __device__ uint64_t lit8(const char *lit, uint32_t l) {
-        uint64_t v = 0;
-        for (uint32_t k = 0; k < 8 && k < l; k++) v |= (uint64_t)(uint8_t)lit[k] << (8 * k);
-        return v;
-    }
-    // plain string body from pos (just after the opening quote): false = not plain / not closed inside the record
-    __device__ __forceinline__ bool fast_string(JSlot &s) {
-        const uint32_t start = pos;
-        for (;;) {
-            if (pos >= n) return false;
-            const uint64_t m = stop_mask(b.le64(pos));
-            if (m == 0) {
-                pos += 8;
-                continue;
-            }
-            pos += (uint32_t)(__ffsll((long long)m) - 1) >> 3;
-            break;
-        }
-        if (pos >= n || b.byte(pos) != '"') return false;
-        s.off = start;
-        s.len = pos - start;
-        s.info = JK_STRING;
-        pos++;
-        return true;
-    }
-    __device__ __forceinline__ bool fast_scalar(JSlot &s) {
-        if (pos >= n) return false;
-        const uint32_t c = b.byte(pos), off = pos;
-        if (c == '"') {
-            pos++;
-            return fast_string(s);
-        }
-        uint32_t info;
-        if (c == '-' || (c - '0') <= 9u) {
-            if (!scan_number(info)) return false;
-        } else if (c == 't') {
-            if (!scan_literal("true", 4)) return false;
-            info = JK_TRUE;
-        } else if (c == 'f') {
-            if (!scan_literal("false", 5)) return false;
-            info = JK_FALSE;
-        } else if (c == 'n') {
-            if (!scan_literal("null", 4)) return false;
-            info = JK_NULL;
-        } else
-            return false;
-        s.off = off;
-        s.len = pos - off;
-        s.info = info;
-        return true;
-    }
-    // key at pos (just after its opening quote): slot id, or -1; pos moves past the closing quote
-    __device__ __forceinline__ int fast_key(bool in_request) {
-        if (pos + 2 > n) return -1;
-        const uint64_t k0 = b.le64(pos), k1 = b.le64(pos + 8);
-        const uint64_t m0 = stop_mask(k0);
-        uint32_t kl;
-        if (m0)
-            kl = (uint32_t)(__ffsll((long long)m0) - 1) >> 3;
-        else {
-            const uint64_t m1 = stop_mask(k1);
-            if (!m1) return -1;  // longer than any key we know
-            kl = 8 + ((uint32_t)(__ffsll((long long)m1) - 1) >> 3);
-        }
-        if (pos + kl >= n) return -1;
-        if ((uint32_t)(((kl < 8 ? k0 : k1) >> (8 * (kl & 7))) & 0xff) != '"') return -1;  // stopped on something else
-        int slot = -1;
-        const uint64_t a = kl < 8 ? low_bytes(k0, kl) : k0, c = kl > 8 ? low_bytes(k1, kl - 8) : 0ull;
-        if (!in_request) {
-            switch (kl) {
-            case 4: if (a == lit8("type", 4)) slot = S_TYPE; break;
-            case 7: if (a == lit8("request", 7)) slot = S_REQUEST; break;
-            case 10: if (a == lit8("originat", 8) && c == lit8("or", 2)) slot = S_ORIG; break;
-            case 11: if (a == lit8("deviceTo", 8) && c == lit8("ken", 3)) slot = S_TOKEN; break;
-            }
-        } else {
-            switch (kl) {
-            case 4: slot = a == lit8("name", 4) ? S_NAME : a == lit8("type", 4) ? S_ATYPE : -1; break;
-            case 5: slot = a == lit8("value", 5) ? S_VALUE : a == lit8("level", 5) ? S_LEVEL : -1; break;
-            case 6: if (a == lit8("source", 6)) slot = S_SOURCE; break;
-            case 7: if (a == lit8("message", 7)) slot = S_MSG; break;
-            case 8: if (a == lit8("latitude", 8)) slot = S_LAT; break;  // ("metadata": an object, not for this path)
-            case 9:
-                if (c == lit8("e", 1))
-                    slot = a == lit8("eventDat", 8) ? S_EDATE : a == lit8("eventTyp", 8) ? S_ETYPE : a == lit8("longitud", 8) ? S_LON : -1;
-                else if (c == lit8("n", 1) && a == lit8("elevatio", 8))
-                    slot = S_ELEV;
-                break;
-            case 11:
-                if (a == lit8("updateSt", 8) && c == lit8("ate", 3)) slot = S_UPD;
-                else if (a == lit8("alternat", 8) && c == lit8("eId", 3)) slot = S_ALT;
-                break;
-            }
-        }
-        pos += kl + 1;
-        return slot;
-    }
-    __device__ int run_fast(JSlot *slots) {
-        esc_key = false;
-        req_unknown = false;
-        root_object = true;
-#pragma unroll
-        for (int k = 0; k < S_COUNT; k++) slots[k].info = JK_NONE;
-        skip_ws();
-        if (pos >= n || b.byte(pos) != '{') return 3;
-        pos++;
-        uint32_t seen = 0;
-        for (;;) {  // members of the root object
-            skip_ws();
-            if (pos >= n || b.byte(pos) != '"') return 3;
-            pos++;
-            const int slot = fast_key(false);
-            if (slot < 0 || ((seen >> slot) & 1u)) return 3;
-            seen |= 1u << slot;
-            skip_ws();
-            if (pos >= n || b.byte(pos) != ':') return 3;
-            pos++;
-            skip_ws();
-            if (pos >= n) return 3;
-            if (slot == S_REQUEST && b.byte(pos) == '{') {
-                const uint32_t obj = pos;
-                pos++;
-                for (;;) {  // members of the request object
-                    skip_ws();
-                    if (pos >= n || b.byte(pos) != '"') return 3;
-                    pos++;
-                    const int rs = fast_key(true);
-                    if (rs < 0 || ((seen >> rs) & 1u)) return 3;
-                    seen |= 1u << rs;
-                    skip_ws();
-                    if (pos >= n || b.byte(pos) != ':') return 3;
-                    pos++;
-                    skip_ws();
-                    if (!fast_scalar(slots[rs])) return 3;
-                    skip_ws();
-                    if (pos >= n) return 3;
-                    const uint32_t d = b.byte(pos);
-                    pos++;
-                    if (d == ',') continue;
-                    if (d == '}') break;
-                    return 3;
-                }
-                slots[S_REQUEST].off = obj;
-                slots[S_REQUEST].len = pos - obj;
-                slots[S_REQUEST].info = JK_OBJECT;
-            } else if (!fast_scalar(slots[slot]))
-                return 3;
-            skip_ws();
-            if (pos >= n) return 3;
-            const uint32_t d = b.byte(pos);
-            pos++;
-            if (d == ',') continue;
-            if (d == '}') return 0;
-            return 3;
-        }
     }
 
     // One structural pass over the first JSON value.  0 = ok, 1 = JsonParseException, 2 = nesting too deep.
@@ -904,12 +730,329 @@ struct JsRow {
     uint64_t v0, v1, v2;
 };
 
-// the fast structural pass reads 8 bytes at a time past the record's end: only where the record sits in a staged tile
-template <typename B> struct JsFastOk { static constexpr bool value = false; };
-template <> struct JsFastOk<SmemBytes> { static constexpr bool value = true; };
+// ---- template recogniser -------------------------------------------------------------------------------------------------
+// The request as the reference itself serialises it: DeviceRequest{deviceToken, originator, type, request} and the
+// request POJO written by a default Jackson ObjectMapper, properties in declaration order, compact, no escapes
+// (sitewhere-core-api/.../rest/model/device/communication/DeviceRequest.java:15-88,
+//  .../event/request/Device{Event,Measurement,Location,Alert}CreateRequest.java; dates per JsonDateSerializer.java:48-51):
+//   {"deviceToken":"T","originator":null,"type":"DeviceMeasurement","request":{"eventType":"Measurement",
+//    "eventDate":"yyyy-MM-ddTHH:mm:ss.SSSZ","updateState":B,"name":"N","value":X}}
+//   ... "type":"DeviceLocation","request":{"eventType":"Location", ... ,"latitude":X,"longitude":X,"elevation":X}}
+//   ... "type":"DeviceAlert","request":{"eventType":"Alert", ... ,"source":"S","level":"L","type":"A","message":"M"}}
+// A record of exactly this shape gives the same row through the general pass (json_decode_record below); this path
+// gets there in a few hundred instructions: the fixed text is compared four bytes at a time against constants, the
+// variable strings are closed by a four-byte scan that keeps their words for the hash, the date and the number are
+// converted while they are read.  Anything else — another key order, white space, an escape, a byte >= 0x80, an
+// optional property, a number outside the plain decimal form — returns false and the general pass decodes the
+// record from the start, so this path never decides an error.  Shared-memory records only (reads run up to seven
+// bytes past the record's end, into the tile's slack).
+struct JsWin {  // sequential little-endian 4-byte reads at any alignment
+    const uint32_t *wp;
+    uint32_t sh, cur;
+    __device__ __forceinline__ void seek(const uint8_t *p) {
+        const uintptr_t a = (uintptr_t)p;
+        wp = (const uint32_t *)(a & ~(uintptr_t)3);
+        sh = (uint32_t)(a & 3) * 8;
+        cur = *wp;
+    }
+    __device__ __forceinline__ uint32_t next() {
+        const uint32_t nx = *++wp;
+        const uint32_t v = __funnelshift_r(cur, nx, sh);
+        cur = nx;
+        return v;
+    }
+};
+static constexpr __host__ __device__ uint32_t js_lit32(const char *lit, int k, int n) {
+    uint32_t v = 0;
+    for (int j = 0; j < 4 && k + j < n; j++) v |= (uint32_t)(uint8_t)lit[k + j] << (8 * j);
+    return v;
+}
+// bytes [p, p+N) == lit ?  (N = sizeof(lit) - 1)
+template <int NP1>
+__device__ __forceinline__ bool js_expect(const uint8_t *p, const char (&lit)[NP1]) {
+    constexpr int N = NP1 - 1;
+    JsWin w;
+    w.seek(p);
+    uint32_t acc = 0;
+#pragma unroll
+    for (int k = 0; k + 4 <= N; k += 4) acc |= w.next() ^ js_lit32(lit, k, N);
+    if (N & 3) acc |= (w.next() ^ js_lit32(lit, N & ~3, N)) & ((1u << (8 * (N & 3))) - 1u);
+    return acc == 0;
+}
+__device__ __forceinline__ uint32_t js_stop32(uint32_t v) {  // 0x80 in every byte that ends plain string content
+    const uint32_t l = v & 0x7f7f7f7fu;
+    return (v | ~(l + 0x60606060u) | ~((l ^ 0x22222222u) + 0x7f7f7f7fu) | ~((l ^ 0x5c5c5c5cu) + 0x7f7f7f7fu)) & 0x80808080u;
+}
+// plain string body at p (just after the opening quote) of at most 4*W - 1 bytes: its words (for the hash) and length;
+// false = longer, not plain, or not closed
+template <int W>
+__device__ __forceinline__ bool js_plain_string(const uint8_t *p, uint32_t (&buf)[W], uint32_t &len) {
+    JsWin w;
+    w.seek(p);
+    bool done = false;
+    len = 0;
+#pragma unroll
+    for (int i = 0; i < W; i++) {
+        if (!done) {
+            const uint32_t v = w.next();
+            buf[i] = v;
+            const uint32_t m = js_stop32(v);
+            if (m) {
+                const uint32_t k = (uint32_t)(__ffs((int)m) - 1) >> 3;
+                if (((v >> (8 * k)) & 0xffu) != '"') return false;
+                len = 4 * i + k;
+                done = true;
+            }
+        } else
+            buf[i] = 0;
+    }
+    return done;
+}
+// sw_hash64 of the first len bytes held in buf (same word order as the byte-stream form)
+template <int W>
+__device__ __forceinline__ uint64_t js_hash_words(const uint32_t (&buf)[W], uint32_t len) {
+    const uint32_t m = 0x5bd1e995u;
+    uint32_t h = 0x9747b28cu ^ len, f = 0x811c9dc5u;
+    const uint32_t nw = len >> 2, rem = len & 3;
+    uint32_t tail = 0;
+#pragma unroll
+    for (int i = 0; i < W; i++) {
+        if ((uint32_t)i < nw) {
+            uint32_t k = buf[i];
+            f = sw_hash_hi_step(f, k);
+            k *= m;
+            k ^= k >> 24;
+            k *= m;
+            h *= m;
+            h ^= k;
+        } else if ((uint32_t)i == nw && rem)
+            tail = buf[i] & ((1u << (8 * rem)) - 1u);
+    }
+    if (rem) {
+        h ^= tail;
+        h *= m;
+    }
+    h ^= h >> 13;
+    h *= m;
+    h ^= h >> 15;
+    return ((uint64_t)sw_hash_hi_final(f, tail, len) << 32) | h;
+}
+// "yyyy-MM-ddTHH:mm:ss.SSSZ" at p -> ms since the epoch (StdDateFormat's lenient field arithmetic, as js_parse_date);
+// false = another form (the general pass handles those), or a year the general pass hands back
+__device__ __forceinline__ bool js_date24(const uint8_t *p, int64_t &ms) {
+    JsWin w;
+    w.seek(p);
+    uint32_t v[6];
+#pragma unroll
+    for (int i = 0; i < 6; i++) v[i] = w.next();
+    // separators: - at 4, 7; T at 10; : at 13, 16; . at 19; Z at 23
+    const bool sep = ((v[1] & 0xffu) == '-') && (((v[1] >> 24) & 0xffu) == '-') && (((v[2] >> 16) & 0xffu) == 'T') &&
+                     (((v[3] >> 8) & 0xffu) == ':') && ((v[4] & 0xffu) == ':') && (((v[4] >> 24) & 0xffu) == '.') &&
+                     (((v[5] >> 24) & 0xffu) == 'Z');
+    // digits everywhere else: byte - '0' <= 9 for each of the 17 digit positions
+    auto dg = [&](int pos) -> uint32_t { return ((v[pos >> 2] >> (8 * (pos & 3))) & 0xffu) - '0'; };
+    uint32_t bad = 0;
+    const int dpos[17] = {0, 1, 2, 3, 5, 6, 8, 9, 11, 12, 14, 15, 17, 18, 20, 21, 22};
+    uint32_t d[17];
+#pragma unroll
+    for (int i = 0; i < 17; i++) {
+        d[i] = dg(dpos[i]);
+        bad |= d[i] > 9u;
+    }
+    if (!sep || bad) return false;
+    const int year = (int)(d[0] * 1000 + d[1] * 100 + d[2] * 10 + d[3]);
+    if (year < 1583) return false;
+    ms = js_lenient_ms(year, (int)(d[4] * 10 + d[5]) - 1, (int)(d[6] * 10 + d[7]), (int)(d[8] * 10 + d[9]), (int)(d[10] * 10 + d[11]),
+                       (int)(d[12] * 10 + d[13]), (int)(d[14] * 100 + d[15] * 10 + d[16]));
+    return true;
+}
+// JSON number at b[pos..) in the plain decimal form  -?(0|[1-9][0-9]*)(\.[0-9]+)?  with at most 15 significant digits:
+// its double (one exact integer, one exact power of ten, one correctly rounded division: the value
+// Double.parseDouble gives) with Jackson's integer rule (an integer token that is zero is +0.0).  false = any
+// other form: the caller lets the general pass convert it.  `end` = first byte after the token.
+template <typename B>
+__device__ __forceinline__ bool js_plain_number(const B &b, uint32_t n, uint32_t pos, uint32_t &end, uint64_t &bits) {
+    const bool neg = pos < n && b.byte(pos) == '-';
+    uint32_t i = pos + (neg ? 1u : 0u);
+    if (i >= n) return false;
+    uint64_t w = 0;
+    uint32_t nd = 0, frac = 0;
+    uint32_t c = b.byte(i);
+    if (c == '0') {
+        i++;
+        if (i < n && (b.byte(i) - '0') <= 9u) return false;  // leading zero: a grammar error, not ours to report
+    } else if ((c - '1') <= 8u) {
+        while (i < n && (c = b.byte(i) - '0') <= 9u) {
+            w = w * 10 + c;
+            nd++;
+            i++;
+        }
+    } else
+        return false;
+    bool is_float = false;
+    if (i < n && b.byte(i) == '.') {
+        is_float = true;
+        i++;
+        const uint32_t f0 = i;
+        while (i < n && (c = b.byte(i) - '0') <= 9u) {
+            w = w * 10 + c;
+            nd += (w != 0);
+            i++;
+        }
+        frac = i - f0;
+        if (frac == 0) return false;
+    }
+    if (i < n && ((b.byte(i) | 0x20) == 'e')) return false;  // exponent form: general pass
+    if (nd > 15 || frac > 22) return false;
+    end = i;
+    if (w == 0) {
+        bits = (neg && is_float) ? 0x8000000000000000ull : 0ull;  // -0.0 keeps its sign, the integer -0 is +0.0
+        return true;
+    }
+    const double p10[] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
+                          1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+    double v = (double)w;
+    if (frac) v = __ddiv_rn(v, p10[frac]);
+    bits = (uint64_t)__double_as_longlong(v) | (neg ? 0x8000000000000000ull : 0ull);
+    return true;
+}
+
+template <typename B> struct JsTemplateOk { static constexpr bool value = false; };
+template <> struct JsTemplateOk<SmemBytes> { static constexpr bool value = true; };
+
+// advance over a literal, or leave the record to the general pass
+#define JS_LIT(lit) ((pos + (uint32_t)sizeof(lit) - 1 <= n && js_expect(s + pos, lit)) ? (pos += (uint32_t)sizeof(lit) - 1, true) : false)
+__device__ bool json_template_record(const SmemBytes &bytes, uint32_t n, uint32_t rec, JsRow &r) {
+    const uint8_t *s = bytes.s;
+    uint32_t pos = 0;
+    if (!JS_LIT("{\"deviceToken\":\"")) return false;
+    uint32_t tok[8], tl;
+    if (!js_plain_string(s + pos, tok, tl) || pos + tl >= n) return false;
+    const uint32_t tok_off = pos;
+    pos += tl;
+    if (!JS_LIT("\",\"originator\":null,\"type\":\"Device")) return false;
+    // the event type decides the rest
+    uint32_t kind;
+    if (JS_LIT("Measurement\",\"request\":{\"eventType\":\"Measurement\",\"eventDate\":\""))
+        kind = SWGPU_KIND_MEASUREMENT;
+    else if (JS_LIT("Location\",\"request\":{\"eventType\":\"Location\",\"eventDate\":\""))
+        kind = SWGPU_KIND_LOCATION;
+    else if (JS_LIT("Alert\",\"request\":{\"eventType\":\"Alert\",\"eventDate\":\""))
+        kind = SWGPU_KIND_ALERT;
+    else
+        return false;
+    if (pos + 24 > n) return false;
+    int64_t date;
+    if (!js_date24(s + pos, date)) return false;
+    pos += 24;
+    if (!JS_LIT("\",\"updateState\":")) return false;
+    uint32_t flags = SWGPU_F_HAS_DATE;
+    if (JS_LIT("false,\"")) {
+    } else if (JS_LIT("true,\"")) {
+        flags |= SWGPU_F_UPDATE_STATE;
+    } else
+        return false;
+    uint64_t v0 = 0, v1 = 0, v2 = 0, nh = 0, nspan = 0, mspan = 0;
+    uint32_t level = 0, source = 0;
+    if (kind == SWGPU_KIND_MEASUREMENT) {
+        if (!JS_LIT("name\":\"")) return false;
+        uint32_t nm[8], nl;
+        if (!js_plain_string(s + pos, nm, nl) || pos + nl >= n) return false;
+        nspan = sw_mk_span(pos, nl);
+        nh = js_hash_words(nm, nl);
+        pos += nl;
+        if (!JS_LIT("\",\"value\":")) return false;
+        uint32_t end;
+        if (!js_plain_number(bytes, n, pos, end, v0)) return false;
+        pos = end;
+        flags |= SWGPU_F_HAS_NAME | SWGPU_F_HAS_V0;
+    } else if (kind == SWGPU_KIND_LOCATION) {
+        uint32_t end;
+        if (!JS_LIT("latitude\":")) return false;
+        if (!js_plain_number(bytes, n, pos, end, v0)) return false;
+        pos = end;
+        if (!JS_LIT(",\"longitude\":")) return false;
+        if (!js_plain_number(bytes, n, pos, end, v1)) return false;
+        pos = end;
+        if (!JS_LIT(",\"elevation\":")) return false;
+        if (!js_plain_number(bytes, n, pos, end, v2)) return false;
+        pos = end;
+        flags |= SWGPU_F_HAS_V0 | SWGPU_F_HAS_V1 | SWGPU_F_HAS_V2;
+    } else {
+        if (!JS_LIT("source\":\"")) return false;
+        if (JS_LIT("Device\",\"level\":\""))
+            source = 0;
+        else if (JS_LIT("System\",\"level\":\""))
+            source = 1;
+        else
+            return false;
+        if (JS_LIT("Info\",\""))
+            level = 0;
+        else if (JS_LIT("Warning\",\""))
+            level = 1;
+        else if (JS_LIT("Error\",\""))
+            level = 2;
+        else if (JS_LIT("Critical\",\""))
+            level = 3;
+        else
+            return false;
+        if (!JS_LIT("type\":\"")) return false;
+        uint32_t nm[8], nl;
+        if (!js_plain_string(s + pos, nm, nl) || pos + nl >= n) return false;
+        nspan = sw_mk_span(pos, nl);
+        nh = js_hash_words(nm, nl);
+        pos += nl;
+        if (!JS_LIT("\",\"message\":\"")) return false;
+        // the message may be long: scan it four bytes at a time without keeping it
+        JsWin w;
+        w.seek(s + pos);
+        uint32_t ml = 0;
+        for (;;) {
+            if (pos + ml >= n) return false;
+            const uint32_t v = w.next(), m = js_stop32(v);
+            if (m) {
+                const uint32_t k = (uint32_t)(__ffs((int)m) - 1) >> 3;
+                if (((v >> (8 * k)) & 0xffu) != '"') return false;
+                ml += k;
+                break;
+            }
+            ml += 4;
+        }
+        if (pos + ml >= n) return false;
+        mspan = sw_mk_span(pos, ml);
+        pos += ml + 1;
+        flags |= SWGPU_F_HAS_NAME | SWGPU_F_HAS_MESSAGE;
+    }
+    // the two closing braces must end the record (what follows the first value is ignored by the reference too, but
+    // then this is not the serialiser's output: leave it to the general pass)
+    if (pos + 2 != n || s[pos] != '}' || s[pos + 1] != '}') return false;
+    r.status = SWGPU_ST_OK;
+    r.meta = sw_mk_meta(kind, flags, level, source, 1, kind, rec);
+    r.th = js_hash_words(tok, tl);
+    r.nh = nh;
+    r.tspan = sw_mk_span(tok_off, tl);
+    r.nspan = nspan;
+    r.ospan = 0;
+    r.mspan = mspan;
+    r.mdspan = 0;
+    r.aspan = 0;
+    r.date = date;
+    r.v0 = v0;
+    r.v1 = v1;
+    r.v2 = v2;
+    return true;
+}
+#undef JS_LIT
+template <typename B>
+__device__ __forceinline__ bool json_template_try(const B &, uint32_t, uint32_t, JsRow &) { return false; }
+template <>
+__device__ __forceinline__ bool json_template_try<SmemBytes>(const SmemBytes &b, uint32_t n, uint32_t rec, JsRow &r) {
+    return json_template_record(b, n, rec, r);
+}
 
 template <typename B>
-__device__ void json_decode_record(B bytes, uint32_t n, uint32_t rec, JsRow &r, bool FAST = true) {
+__device__ void json_decode_record(B bytes, uint32_t n, uint32_t rec, JsRow &r, bool try_template = true) {
+    if (try_template && json_template_try(bytes, n, rec, r)) return;
     r.status = SWGPU_ST_DECODE_EXCEPTION;
     r.meta = r.th = r.nh = r.tspan = r.nspan = r.ospan = r.mspan = r.mdspan = r.aspan = 0;
     r.date = 0;
@@ -928,12 +1071,7 @@ __device__ void json_decode_record(B bytes, uint32_t n, uint32_t rec, JsRow &r, 
     sc.b = bytes;
     sc.n = n;
     sc.pos = start;
-    int rc = 3;
-    if (FAST && JsFastOk<B>::value) rc = sc.run_fast(slots);
-    if (rc == 3) {
-        sc.pos = start;
-        rc = sc.run(slots);
-    }
+    const int rc = sc.run(slots);
     if (rc == 2) {
         r.status = SWGPU_ST_PASSTHROUGH;
         return;

@@ -134,9 +134,10 @@ def test_mirror_api(ctx):
 
 
 def test_fast_structural_pass_equals_general_pass(ctx):
-    """the straight-line pass for plainly shaped requests (option json.fast_path, default on) and the general
-    pass must give identical results: canonical records of the three event types in shuffled key order, with
-    white space, repeated / unknown keys, every known-answer vector, and mutated records"""
+    """the template recogniser for requests in the reference serialiser's own shape (option json.fast_path,
+    default on) and the general pass must give identical results: canonical records of the three event types
+    (taken by the template), the same in shuffled key order, with white space, repeated / unknown keys (not
+    taken), every known-answer vector, number and date variants inside the canonical text, and mutated records"""
     from tests.test_gpu_fuzz import _mutate, JSON_SPECIALS
     rnd = random.Random(12)
     rng = np.random.default_rng(12)
@@ -178,6 +179,18 @@ def test_fast_structural_pass_equals_general_pass(ctx):
             txt = txt.replace('"request"' + sep[1] + "{", '"request"' + sep[1] + '{"bogus":1,', 1)
         recs.append(txt.encode())
     recs += _mutate(rng, base[:2000], JSON_SPECIALS, 6000, max_mut=2)
+    # canonical text around every torture number / odd dates / long and odd strings
+    toks = [t for t in TORTURE] + ["-" + t for t in TORTURE if not t.startswith("-")] + ["0", "-0", "-0.0", "0.0", "1e5", "12345678901234567", "0.1234567890123456", "123456789012345.5", "1.0000000000000000000000001"]
+    for i, t in enumerate(toks):
+        recs.append(S.json_measurement(S.token_str(i % 50), "fuel.level", t, S.EVENT_DATE_BASE + i))
+        recs.append(S.json_location(S.token_str(i % 50), t, "-84.25", t, S.EVENT_DATE_BASE + i, update_state=bool(i & 1)))
+    for d in ("2018-13-45T25:61:61.999Z", "1582-01-01T00:00:00.000Z", "9999-12-31T23:59:59.999Z", "2018-06-01T12:00:00.000z", "2018-06-01 12:00:00.000Z"):
+        recs.append(S.json_measurement("tok", "n", "1.5", S.EVENT_DATE_BASE).replace(b"2018-06-01T12:00:00.000Z", d.encode()))
+    for tok in ("", "a", "x" * 31, "y" * 32, "z" * 40, "t\\u0041", "caf\u00e9", "tab\there"):
+        recs.append(S.json_measurement(tok, tok[:8], "2.5", S.EVENT_DATE_BASE))
+        recs.append(S.json_alert("dev", tok, "msg " + tok * 3, S.EVENT_DATE_BASE, level="Critical", source="System"))
+    recs.append(S.json_measurement("tok", "n", "1.5", S.EVENT_DATE_BASE) + b" ")
+    recs.append(S.json_measurement("tok", "n", "1.5", S.EVENT_DATE_BASE)[:-1])
     data, rec_off = S.pack_records(recs)
     fast = ctx.decode_json(data, rec_off)
     ctx.set_option("json.fast_path", 0)

@@ -130,3 +130,45 @@ def test_small_batch_path(ctx):
     assert n_rows == ototal
     for nm in names:
         assert np.array_equal(getattr(cols, nm)[:ototal].view(np.uint64), getattr(ocols, nm)[:ototal].view(np.uint64)), nm
+
+
+def test_reserve_batch_then_async_submit_and_wait():
+    """swgpu_reserve_batch sizes the buffers up front; swgpu_submit_decode_zone_test / swgpu_wait run the same
+    call on the context's worker thread: three batches queued at once, waited for in order, each equal to the oracle"""
+    import ctypes as C
+    import sitewhere_b200 as sw
+    from sitewhere_b200 import _lib as L
+    ctx = sw.Context(0)
+    try:
+        zones = S.star_zones(8)
+        ctx.set_zones(*zones)
+        assert ctx.lib.swgpu_reserve_batch(ctx.h, 300_000, 300_000 * 64) == 0
+        jobs = []
+        for k, n in enumerate((40_000, 300_000, 2_000)):                 # ring path, ring path, small-batch path
+            lon, lat = S.locations_for_zones(n, *zones[:3], seed=40 + k, boundary_rate=0.01)
+            data, rec_off, _ = S.pb_locations(n, 3000, lon, lat, seed=40 + k)
+            p_data = pinned_array((data.shape[0],), np.uint8)
+            p_data[:] = data
+            p_off = pinned_array((n + 1,), np.uint64)
+            p_off[:] = rec_off
+            cols = pinned_cols(n)
+            status = pinned_array((n,), np.uint8)
+            first = pinned_array((n + 1,), np.uint32)
+            pairs = pinned_array((n,), np.uint64)
+            out_rows, n_pairs, ticket = C.c_uint32(), C.c_uint64(), C.c_uint64()
+            s = cols.struct()
+            rc = ctx.lib.swgpu_submit_decode_zone_test(ctx.h, 0, p_data.ctypes.data, p_off.ctypes.data, n, n, C.byref(s),
+                                                       status.ctypes.data, first.ctypes.data, C.byref(out_rows), n,
+                                                       pairs.ctypes.data, C.byref(n_pairs), 0, C.byref(ticket))
+            assert rc == 0 and ticket.value == k + 1
+            jobs.append((ticket.value, data, rec_off, cols, status, first, pairs, out_rows, n_pairs, p_data, p_off, s))
+        for (t, data, rec_off, cols, status, first, pairs, out_rows, n_pairs, *_keep) in jobs:
+            assert ctx.lib.swgpu_wait(ctx.h, t) == 0
+            ocols, ostatus, ofirst, ototal = oracle.decode_pb(data, rec_off)
+            assert out_rows.value == ototal and np.array_equal(status, ostatus) and np.array_equal(first, ofirst)
+            assert_cols_equal(cols, ocols, ototal)
+            want, total = oracle.zone_test(*zones, ocols.v1[:ototal], ocols.v0[:ototal], meta=ocols.meta[:ototal])
+            assert n_pairs.value == total and np.array_equal(pairs[:total], want)
+        assert ctx.lib.swgpu_wait(ctx.h, 99) == L.E_INVALID
+    finally:
+        ctx.close()
