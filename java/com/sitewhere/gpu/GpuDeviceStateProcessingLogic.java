@@ -16,6 +16,12 @@
  * stock DeviceStateProcessingLogic, as do none of the others: a record the library rejects (status 1) is one the
  * reference would have logged and skipped (DeviceStateProcessingLogic.java:75-85,101-106).
  *
+ * Limit: the GPU table keeps, per (assignment, kind, name), the winner's event id, date and value, and per
+ * assignment the presence dates; deviceId / deviceTypeId / customerId / areaId / assetId of the state document
+ * (DeviceStateProcessingLogic.java:136-141) are not carried, so a state this shim CREATES holds the assignment id
+ * and the merged fields only (an existing document keeps its other fields: null never overwrites,
+ * DeviceStatePersistence.java:64-78).
+ *
  * NOT COMPILED in this repository (no JDK in the build container).
  */
 package com.sitewhere.gpu;
