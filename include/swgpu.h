@@ -159,6 +159,7 @@ int32_t swgpu_sync(swgpu_ctx *ctx);
  *   "json.fast_path"        0 = every JSON record takes the general structural pass; 1 (default) = a record in
  *                           exactly the shape the reference's own serialiser writes is first tried against that
  *                           template (same result, far fewer instructions)
+ *   "json.stats"            1 = JSON decodes count the records the template took (swgpu_json_stats)
  *   "zone.stats"            1 = zone tests also count their work (read it with swgpu_zone_stats)        */
 int32_t swgpu_set_option(swgpu_ctx *ctx, const char *name, int64_t value);
 /* Pinned host staging the Java side wraps as a direct ByteBuffer / MemorySegment.             */
@@ -254,6 +255,12 @@ int32_t swgpu_zone_test_dev(swgpu_ctx *ctx, const double *lon, const double *lat
  * out[2] = straddle tests (an edge whose ends lie on either side of the ray: the exact-sign determinant of
  * RayCrossingCounter.countSegment), out[3] = locations.  Waits for the context's stream.                  */
 int32_t swgpu_zone_stats(swgpu_ctx *ctx, uint64_t out[4]);
+
+/* Measurement aid: of the last swgpu_decode_json_dev that ran with option "json.stats" = 1 (and nothing
+ * else on the context since), out[0] = records the canonical-layout recogniser decoded (the rest went through
+ * the general parser; counted again by the ordered second pass when there was one), out[1] = non-zero when
+ * the ordered second pass ran.  Waits for the context's stream.                                            */
+int32_t swgpu_json_stats(swgpu_ctx *ctx, uint64_t out[2]);
 
 /* ---- fused host-buffer path ------------------------------------------------------------------------
  * Decode + zone test of one micro-batch held in HOST memory, in one call: what the Java binding's

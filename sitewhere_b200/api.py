@@ -269,6 +269,12 @@ class Context:
         self._check(self.lib.swgpu_zone_stats(self.h, out))
         return dict(cell_records=int(out[0]), edge_records=int(out[1]), straddle_tests=int(out[2]), locations=int(out[3]))
 
+    def json_stats(self) -> dict:
+        """swgpu_json_stats: recogniser hits of the last JSON decode run with option json.stats = 1."""
+        out = (C.c_uint64 * 2)()
+        self._check(self.lib.swgpu_json_stats(self.h, out))
+        return dict(template_records=int(out[0]), second_pass=int(out[1]))
+
     # ---- fused host-buffer path (chunked, overlapped) -------------------------------------------------
     def decode_zone_test(self, fmt: str, data, rec_off, cols: "HostCols" = None, status=None, first_row=None,
                          pairs=None, chunk_records: int = 0):

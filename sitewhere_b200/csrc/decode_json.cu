@@ -42,9 +42,11 @@ struct JsArgs {
     const uint64_t *id_hi, *id_lo;
     uint64_t seq_base;
     uint32_t fast;  // option "json.fast_path": try the template recogniser first (default 1)
+    uint32_t *hits; // option "json.stats": records the template recogniser took (NULL = not counted)
 };
 
 enum { JK_NONE = 0, JK_OBJECT, JK_ARRAY, JK_STRING, JK_INT, JK_FLOAT, JK_TRUE, JK_FALSE, JK_NULL };
+#define JS_ST_PENDING 0xffu  // internal record status between the template pass and the dense pass
 #define JI_ESCAPED 0x10u
 #define JI_NONASCII 0x20u
 #define JI_BADCHILD 0x40u  // metadata object holds a container value
@@ -917,12 +919,39 @@ __device__ __forceinline__ bool js_plain_number(const B &b, uint32_t n, uint32_t
     return true;
 }
 
+// Any other JSON number token (17 digits, exponent form ...): the general pass's grammar (JsonScan::scan_number) and
+// conversion (js_token_double).  Out of line: one lane in a hundred gets here.
+__device__ __noinline__ bool js_number_general(const uint8_t *s, uint32_t n, uint32_t pos, uint32_t *end, uint64_t *bits) {
+    JsonScan<SmemBytes> sc;
+    sc.b = SmemBytes{s};
+    sc.n = n;
+    sc.pos = pos;
+    uint32_t kind;
+    if (pos >= n || !sc.scan_number(kind)) return false;
+    JSlot t;
+    t.off = pos;
+    t.len = sc.pos - pos;
+    t.info = kind;
+    *bits = js_token_double(sc.b, t);
+    *end = sc.pos;
+    return true;
+}
+__device__ __forceinline__ bool js_number(const SmemBytes &b, uint32_t n, uint32_t pos, uint32_t &end, uint64_t &bits) {
+    if (js_plain_number(b, n, pos, end, bits)) return true;
+    uint32_t e = 0;
+    uint64_t v = 0;
+    if (!js_number_general(b.s, n, pos, &e, &v)) return false;
+    end = e;
+    bits = v;
+    return true;
+}
+
 template <typename B> struct JsTemplateOk { static constexpr bool value = false; };
 template <> struct JsTemplateOk<SmemBytes> { static constexpr bool value = true; };
 
 // advance over a literal, or leave the record to the general pass
 #define JS_LIT(lit) ((pos + (uint32_t)sizeof(lit) - 1 <= n && js_expect(s + pos, lit)) ? (pos += (uint32_t)sizeof(lit) - 1, true) : false)
-__device__ bool json_template_record(const SmemBytes &bytes, uint32_t n, uint32_t rec, JsRow &r) {
+__device__ __forceinline__ bool json_template_record(const SmemBytes &bytes, uint32_t n, uint32_t rec, JsRow &r) {
     const uint8_t *s = bytes.s;
     uint32_t pos = 0;
     if (!JS_LIT("{\"deviceToken\":\"")) return false;
@@ -963,19 +992,19 @@ __device__ bool json_template_record(const SmemBytes &bytes, uint32_t n, uint32_
         pos += nl;
         if (!JS_LIT("\",\"value\":")) return false;
         uint32_t end;
-        if (!js_plain_number(bytes, n, pos, end, v0)) return false;
+        if (!js_number(bytes, n, pos, end, v0)) return false;
         pos = end;
         flags |= SWGPU_F_HAS_NAME | SWGPU_F_HAS_V0;
     } else if (kind == SWGPU_KIND_LOCATION) {
         uint32_t end;
         if (!JS_LIT("latitude\":")) return false;
-        if (!js_plain_number(bytes, n, pos, end, v0)) return false;
+        if (!js_number(bytes, n, pos, end, v0)) return false;
         pos = end;
         if (!JS_LIT(",\"longitude\":")) return false;
-        if (!js_plain_number(bytes, n, pos, end, v1)) return false;
+        if (!js_number(bytes, n, pos, end, v1)) return false;
         pos = end;
         if (!JS_LIT(",\"elevation\":")) return false;
-        if (!js_plain_number(bytes, n, pos, end, v2)) return false;
+        if (!js_number(bytes, n, pos, end, v2)) return false;
         pos = end;
         flags |= SWGPU_F_HAS_V0 | SWGPU_F_HAS_V1 | SWGPU_F_HAS_V2;
     } else {
@@ -1050,9 +1079,13 @@ __device__ __forceinline__ bool json_template_try<SmemBytes>(const SmemBytes &b,
     return json_template_record(b, n, rec, r);
 }
 
-template <typename B>
-__device__ void json_decode_record(B bytes, uint32_t n, uint32_t rec, JsRow &r, bool try_template = true) {
-    if (try_template && json_template_try(bytes, n, rec, r)) return;
+template <typename B, bool TPL = true>
+__device__ void json_decode_record(B bytes, uint32_t n, uint32_t rec, JsRow &r, bool try_template = true,
+                                   uint32_t *template_hits = nullptr) {
+    if (TPL && try_template && json_template_try(bytes, n, rec, r)) {
+        if (template_hits) atomicAdd(template_hits, 1u);
+        return;
+    }
     r.status = SWGPU_ST_DECODE_EXCEPTION;
     r.meta = r.th = r.nh = r.tspan = r.nspan = r.ospan = r.mspan = r.mdspan = r.aspan = 0;
     r.date = 0;
@@ -1274,12 +1307,96 @@ __device__ void json_decode_record(B bytes, uint32_t n, uint32_t rec, JsRow &r, 
     r.status = SWGPU_ST_OK;
 }
 
+__device__ __forceinline__ void js_write_row(const JsArgs &a, const uint64_t row, const JsRow &r) {
+    a.cols.meta[row] = r.meta;
+    a.cols.token_hash[row] = r.th;
+    a.cols.name_hash[row] = r.nh;
+    a.cols.event_date[row] = r.date;
+    a.cols.v0[row] = __longlong_as_double((long long)r.v0);
+    a.cols.v1[row] = __longlong_as_double((long long)r.v1);
+    a.cols.v2[row] = __longlong_as_double((long long)r.v2);
+    a.cols.token_span[row] = r.tspan;
+    a.cols.name_span[row] = r.nspan;
+    if (a.cols.originator_span) a.cols.originator_span[row] = r.ospan;
+    if (a.cols.message_span) a.cols.message_span[row] = r.mspan;
+    if (a.cols.metadata_span) a.cols.metadata_span[row] = r.mdspan;
+    if (a.cols.alternate_id_span) a.cols.alternate_id_span[row] = r.aspan;
+}
+
 // one tile = JS_THREADS records, one per thread.  As in the protobuf decoder: each warp stages and decodes
 // its own 32 records (no block barrier for staging).
 template <bool DENSE>
 __device__ __forceinline__ void json_decode_tile(const JsArgs &a, const uint32_t tile, uint8_t *smem, uint64_t *s_warp) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint64_t rec0_64 = (uint64_t)tile * JS_THREADS + warp * 32;
+    const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
+    const uint32_t nrec = min(32u, a.n - rec0);
+    uint8_t *ws = smem + warp * (JS_WSTAGE + 32);
+    uint64_t r0 = 0, r1 = 0;
+    if (lane < nrec) {
+        r0 = a.rec_off[rec0 + lane];
+        r1 = a.rec_off[rec0 + lane + 1];
+    }
+    // after the template pass (json_template_kernel) the dense pass decodes only the records that one left
+    bool mine = lane < nrec;
+    if (DENSE && a.fast) {
+        mine = mine && a.status[rec0 + lane] == JS_ST_PENDING;
+        if (!__any_sync(SW_FULL, mine)) return;
+    }
+    const uint64_t b0 = __shfl_sync(SW_FULL, r0, 0);
+    const uint64_t b1 = __shfl_sync(SW_FULL, r1, nrec ? nrec - 1 : 0);
+    const uintptr_t addr = (uintptr_t)(a.bytes + b0);
+    const uint32_t lead = (uint32_t)(addr & 15);
+    const uint64_t span = (uint64_t)lead + (b1 - b0);
+    const bool staged = span <= JS_WSTAGE;
+    if (staged && nrec) {
+        const uint4 *src = (const uint4 *)(addr - lead);
+        uint4 *dst = (uint4 *)ws;
+        const uint32_t nvec = (uint32_t)((span + 15) >> 4);
+        for (uint32_t i = lane; i < nvec; i += 32) dst[i] = sw_ld_stream_u4(src + i);
+    }
+    __syncwarp();
+    JsRow r;
+    r.status = 0;
+    uint32_t count = 0;
+    if (mine) {
+        const uint64_t l64 = r1 - r0;
+        const uint32_t len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
+        if (staged)
+            json_decode_record<SmemBytes, !DENSE>(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, len, a.rec_base + rec0 + lane, r, a.fast != 0, a.hits);
+        else
+            json_decode_record<GmemBytes, !DENSE>(GmemBytes{a.bytes + r0}, len, a.rec_base + rec0 + lane, r, a.fast != 0, a.hits);
+        count = r.status == SWGPU_ST_OK ? 1u : 0u;
+    }
+    uint64_t tile_total = 0, row;
+    if (DENSE) {
+        row = (uint64_t)rec0 + lane;
+        if (mine && count != 1) atomicOr(a.not_dense, 1u);
+    } else {
+        row = sw_block_ordered_offset<JS_THREADS>(count, a.tile_state, tile, s_warp, &tile_total);
+    }
+    const uint64_t row_base = a.row_base ? (uint64_t)__ldg(a.row_base) : 0ull;
+    const uint32_t tid_rec = lane;  // record index within the tile
+    if (mine) {
+        a.status[rec0 + tid_rec] = (uint8_t)r.status;
+        a.first_row[rec0 + tid_rec] = (uint32_t)(row_base + row);
+        if (count && row < a.max_rows) js_write_row(a, row, r);
+    }
+    if ((uint64_t)tile * JS_THREADS + JS_THREADS >= a.n && tid == 0) {  // the tile holding the last record
+        const uint64_t total = DENSE ? (uint64_t)a.n : row + tile_total;
+        a.first_row[a.n] = (uint32_t)(row_base + total);
+        *a.out_rows = (uint32_t)total;
+        if (a.row_next) *a.row_next = (uint32_t)(row_base + total);
+    }
+}
+
+// Template pass (option "json.fast_path"): row index = record index as in the dense pass; a record in the
+// serialiser's layout is decoded here, every other one is marked JS_ST_PENDING for the dense pass that follows.
+// Nothing of the general parser is in this kernel: it stays small enough for the instruction cache.
+__global__ void __launch_bounds__(JS_THREADS) json_template_kernel(JsArgs a) {
+    extern __shared__ __align__(16) uint8_t smem[];  // JS_WARPS * (JS_WSTAGE + 32)
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint64_t rec0_64 = (uint64_t)blockIdx.x * JS_THREADS + warp * 32;
     const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
     const uint32_t nrec = min(32u, a.n - rec0);
     uint8_t *ws = smem + warp * (JS_WSTAGE + 32);
@@ -1301,51 +1418,24 @@ __device__ __forceinline__ void json_decode_tile(const JsArgs &a, const uint32_t
         for (uint32_t i = lane; i < nvec; i += 32) dst[i] = sw_ld_stream_u4(src + i);
     }
     __syncwarp();
-    JsRow r;
-    r.status = 0;
-    uint32_t count = 0;
-    if (lane < nrec) {
-        const uint64_t l64 = r1 - r0;
-        const uint32_t len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
-        if (staged)
-            json_decode_record(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, len, a.rec_base + rec0 + lane, r, a.fast != 0);
-        else
-            json_decode_record(GmemBytes{a.bytes + r0}, len, a.rec_base + rec0 + lane, r, a.fast != 0);
-        count = r.status == SWGPU_ST_OK ? 1u : 0u;
-    }
-    uint64_t tile_total = 0, row;
-    if (DENSE) {
-        row = (uint64_t)rec0 + lane;
-        if (lane < nrec && count != 1) atomicOr(a.not_dense, 1u);
-    } else {
-        row = sw_block_ordered_offset<JS_THREADS>(count, a.tile_state, tile, s_warp, &tile_total);
-    }
     const uint64_t row_base = a.row_base ? (uint64_t)__ldg(a.row_base) : 0ull;
-    const uint32_t tid_rec = lane;  // record index within the tile
+    bool hit = false;
     if (lane < nrec) {
-        a.status[rec0 + tid_rec] = (uint8_t)r.status;
-        a.first_row[rec0 + tid_rec] = (uint32_t)(row_base + row);
-        if (count && row < a.max_rows) {
-            a.cols.meta[row] = r.meta;
-            a.cols.token_hash[row] = r.th;
-            a.cols.name_hash[row] = r.nh;
-            a.cols.event_date[row] = r.date;
-            a.cols.v0[row] = __longlong_as_double((long long)r.v0);
-            a.cols.v1[row] = __longlong_as_double((long long)r.v1);
-            a.cols.v2[row] = __longlong_as_double((long long)r.v2);
-            a.cols.token_span[row] = r.tspan;
-            a.cols.name_span[row] = r.nspan;
-            if (a.cols.originator_span) a.cols.originator_span[row] = r.ospan;
-            if (a.cols.message_span) a.cols.message_span[row] = r.mspan;
-            if (a.cols.metadata_span) a.cols.metadata_span[row] = r.mdspan;
-            if (a.cols.alternate_id_span) a.cols.alternate_id_span[row] = r.aspan;
-        }
+        JsRow r;
+        if (staged) hit = json_template_record(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, (uint32_t)(r1 - r0), a.rec_base + rec0 + lane, r);
+        const uint64_t row = (uint64_t)rec0 + lane;
+        a.status[rec0 + lane] = hit ? (uint8_t)SWGPU_ST_OK : (uint8_t)JS_ST_PENDING;
+        a.first_row[rec0 + lane] = (uint32_t)(row_base + row);
+        if (hit && row < a.max_rows) js_write_row(a, row, r);
     }
-    if ((uint64_t)tile * JS_THREADS + JS_THREADS >= a.n && tid == 0) {  // the tile holding the last record
-        const uint64_t total = DENSE ? (uint64_t)a.n : row + tile_total;
-        a.first_row[a.n] = (uint32_t)(row_base + total);
-        *a.out_rows = (uint32_t)total;
-        if (a.row_next) *a.row_next = (uint32_t)(row_base + total);
+    if (a.hits) {
+        const uint32_t m = __ballot_sync(SW_FULL, hit);
+        if (lane == 0 && m) atomicAdd(a.hits, (uint32_t)__popc(m));
+    }
+    if ((uint64_t)blockIdx.x * JS_THREADS + JS_THREADS >= a.n && tid == 0) {  // the tile holding the last record
+        a.first_row[a.n] = (uint32_t)(row_base + a.n);
+        *a.out_rows = a.n;
+        if (a.row_next) *a.row_next = (uint32_t)(row_base + a.n);
     }
 }
 
@@ -1519,6 +1609,7 @@ int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *
     a.row_next = row_next;
     a.not_dense = (uint32_t *)ctx->scratch + 1;
     a.fast = ctx->opt_json_fast;
+    a.hits = ctx->opt_json_stats ? (uint32_t *)ctx->scratch + 2 : nullptr;
     const int smem = JS_WARPS * (JS_WSTAGE + 32);
     {
         // per device, once: the attribute is a property of the loaded function
@@ -1529,14 +1620,33 @@ int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *
         if (!done[d]) {
             SW_CUDA(ctx, cudaFuncSetAttribute(json_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
             SW_CUDA(ctx, cudaFuncSetAttribute(json_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            SW_CUDA(ctx, cudaFuncSetAttribute(json_template_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
             done[d] = true;
         }
+    }
+    if (a.fast) {
+        json_template_kernel<<<ntiles, JS_THREADS, smem, ctx->stream>>>(a);  // the serialiser's layout
+        SW_CUDA(ctx, cudaGetLastError());
     }
     json_decode_kernel<true><<<ntiles, JS_THREADS, smem, ctx->stream>>>(a);   // optimistic: rows = records
     SW_CUDA(ctx, cudaGetLastError());
     const uint32_t nredo = ntiles < (uint32_t)ctx->sm_count * 4u ? ntiles : (uint32_t)ctx->sm_count * 4u;
     json_decode_kernel<false><<<nredo, JS_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
     SW_CUDA(ctx, cudaGetLastError());
+    return SWGPU_OK;
+}
+
+// Records of the last JSON decode the template recogniser took (option "json.stats" = 1; synchronises the stream).
+extern "C" int32_t swgpu_json_stats(swgpu_ctx *ctx, uint64_t out[2]) {
+    if (!ctx || !out) return SWGPU_E_INVALID;
+    out[0] = out[1] = 0;
+    if (!ctx->scratch) return SWGPU_OK;
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint32_t w[3];
+    SW_CUDA(ctx, cudaMemcpyAsync(w, ctx->scratch, sizeof(w), cudaMemcpyDeviceToHost, ctx->stream));
+    SW_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    out[0] = w[2];
+    out[1] = w[1];
     return SWGPU_OK;
 }
 

@@ -30,4 +30,8 @@ with torch.cuda.stream(stream):
             ctx.decode_json_dev(d_bytes, d_off, n, cols, d_status, d_first, d_nrows)
         b.record(stream)
         torch.cuda.synchronize()
+        ctx.set_option("json.stats", 1)
+        ctx.decode_json_dev(d_bytes, d_off, n, cols, d_status, d_first, d_nrows)
+        print("  stats:", ctx.json_stats(), flush=True)
+        ctx.set_option("json.stats", 0)
         print("json.fast_path =", fast, ": %.4f ms per %d records" % (a.elapsed_time(b) / 5, n), int(d_nrows.item()), flush=True)
