@@ -19,6 +19,7 @@
 
 #define JS_THREADS 128
 #define JS_WARPS (JS_THREADS / 32)
+#define JS_AHEAD 4096         // template pass: warp tiles between an L2 prefetch and its use (about one wave of resident warps)
 #define JS_WSTAGE (8 * 1024)  // bytes staged per warp tile: 32 records of up to 256 B on average (more CTAs per SM than 12 KiB)
 #define JS_MAX_DEPTH 256
 
@@ -42,6 +43,7 @@ struct JsArgs {
     const uint64_t *id_hi, *id_lo;
     uint64_t seq_base;
     uint32_t fast;  // option "json.fast_path": try the template recogniser first (default 1)
+    uint32_t *pending;  // template pass -> dense pass: non-zero when the template pass left records
     uint32_t *hits; // option "json.stats": records the template recogniser took (NULL = not counted)
 };
 
@@ -785,52 +787,44 @@ __device__ __forceinline__ uint32_t js_stop32(uint32_t v) {  // 0x80 in every by
     const uint32_t l = v & 0x7f7f7f7fu;
     return (v | ~(l + 0x60606060u) | ~((l ^ 0x22222222u) + 0x7f7f7f7fu) | ~((l ^ 0x5c5c5c5cu) + 0x7f7f7f7fu)) & 0x80808080u;
 }
-// plain string body at p (just after the opening quote) of at most 4*W - 1 bytes: its words (for the hash) and length;
-// false = longer, not plain, or not closed
+// plain string body at p (just after the opening quote) of at most 4*W - 1 bytes: its length; false = longer, not
+// plain, or not closed
 template <int W>
-__device__ __forceinline__ bool js_plain_string(const uint8_t *p, uint32_t (&buf)[W], uint32_t &len) {
+__device__ __forceinline__ bool js_plain_string(const uint8_t *p, uint32_t &len) {
     JsWin w;
     w.seek(p);
-    bool done = false;
-    len = 0;
-#pragma unroll
-    for (int i = 0; i < W; i++) {
-        if (!done) {
-            const uint32_t v = w.next();
-            buf[i] = v;
-            const uint32_t m = js_stop32(v);
-            if (m) {
-                const uint32_t k = (uint32_t)(__ffs((int)m) - 1) >> 3;
-                if (((v >> (8 * k)) & 0xffu) != '"') return false;
-                len = 4 * i + k;
-                done = true;
-            }
-        } else
-            buf[i] = 0;
+#pragma unroll 1
+    for (uint32_t i = 0; i < (uint32_t)W; i++) {
+        const uint32_t v = w.next();
+        const uint32_t m = js_stop32(v);
+        if (m) {
+            const uint32_t k = (uint32_t)(__ffs((int)m) - 1) >> 3;
+            len = 4 * i + k;
+            return ((v >> (8 * k)) & 0xffu) == '"';
+        }
     }
-    return done;
+    return false;
 }
-// sw_hash64 of the first len bytes held in buf (same word order as the byte-stream form)
-template <int W>
-__device__ __forceinline__ uint64_t js_hash_words(const uint32_t (&buf)[W], uint32_t len) {
+// sw_hash64 of the len bytes at p (same word order as the byte-stream form); reads up to 3 bytes past them
+__device__ __forceinline__ uint64_t js_hash_at(const uint8_t *p, uint32_t len) {
     const uint32_t m = 0x5bd1e995u;
     uint32_t h = 0x9747b28cu ^ len, f = 0x811c9dc5u;
     const uint32_t nw = len >> 2, rem = len & 3;
-    uint32_t tail = 0;
-#pragma unroll
-    for (int i = 0; i < W; i++) {
-        if ((uint32_t)i < nw) {
-            uint32_t k = buf[i];
-            f = sw_hash_hi_step(f, k);
-            k *= m;
-            k ^= k >> 24;
-            k *= m;
-            h *= m;
-            h ^= k;
-        } else if ((uint32_t)i == nw && rem)
-            tail = buf[i] & ((1u << (8 * rem)) - 1u);
+    JsWin w;
+    w.seek(p);
+#pragma unroll 1
+    for (uint32_t i = 0; i < nw; i++) {
+        uint32_t k = w.next();
+        f = sw_hash_hi_step(f, k);
+        k *= m;
+        k ^= k >> 24;
+        k *= m;
+        h *= m;
+        h ^= k;
     }
+    uint32_t tail = 0;
     if (rem) {
+        tail = w.next() & ((1u << (8 * rem)) - 1u);
         h ^= tail;
         h *= m;
     }
@@ -868,10 +862,20 @@ __device__ __forceinline__ bool js_date24(const uint8_t *p, int64_t &ms) {
                        (int)(d[12] * 10 + d[13]), (int)(d[14] * 100 + d[15] * 10 + d[16]));
     return true;
 }
-// JSON number at b[pos..) in the plain decimal form  -?(0|[1-9][0-9]*)(\.[0-9]+)?  with at most 15 significant digits:
-// its double (one exact integer, one exact power of ten, one correctly rounded division: the value
-// Double.parseDouble gives) with Jackson's integer rule (an integer token that is zero is +0.0).  false = any
-// other form: the caller lets the general pass convert it.  `end` = first byte after the token.
+// JSON number at b[pos..) in the plain decimal form  -?(0|[1-9][0-9]*)(\.[0-9]+)?  with at most 19 significant digits
+// (all of them fit one 64-bit integer w, so the value is exactly w / 10^frac): up to 2^53 and 10^22 one exact
+// integer, one exact power of ten and one correctly rounded division give the double Double.parseDouble gives;
+// beyond that the same Eisel-Lemire step as the general conversion (sw_parse_double_bits) when it can decide.
+// Jackson's integer rule: an integer token that is zero is +0.0.  false = any other form, or undecided: the caller
+// takes the general conversion.  `end` = first byte after the token.
+__constant__ double js_p10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                  1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+__device__ __noinline__ bool js_eisel(uint64_t w, int q, uint64_t *bits) {
+    uint64_t v = 0;
+    const bool ok = sw_eisel_lemire(w, (int64_t)q, v);
+    *bits = v;
+    return ok;
+}
 template <typename B>
 __device__ __forceinline__ bool js_plain_number(const B &b, uint32_t n, uint32_t pos, uint32_t &end, uint64_t &bits) {
     const bool neg = pos < n && b.byte(pos) == '-';
@@ -904,18 +908,23 @@ __device__ __forceinline__ bool js_plain_number(const B &b, uint32_t n, uint32_t
         frac = i - f0;
         if (frac == 0) return false;
     }
-    if (i < n && ((b.byte(i) | 0x20) == 'e')) return false;  // exponent form: general pass
-    if (nd > 15 || frac > 22) return false;
+    if (i < n && ((b.byte(i) | 0x20) == 'e')) return false;  // exponent form: general conversion
+    if (nd > 19 || frac > 300) return false;                  // (w may have wrapped)
     end = i;
+    const uint64_t sign = neg ? 0x8000000000000000ull : 0ull;
     if (w == 0) {
-        bits = (neg && is_float) ? 0x8000000000000000ull : 0ull;  // -0.0 keeps its sign, the integer -0 is +0.0
+        bits = is_float ? sign : 0ull;  // -0.0 keeps its sign, the integer -0 is +0.0
         return true;
     }
-    const double p10[] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
-                          1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
-    double v = (double)w;
-    if (frac) v = __ddiv_rn(v, p10[frac]);
-    bits = (uint64_t)__double_as_longlong(v) | (neg ? 0x8000000000000000ull : 0ull);
+    if (w <= (1ull << 53) && frac <= 22) {
+        double v = (double)w;
+        if (frac) v = __ddiv_rn(v, js_p10[frac]);
+        bits = (uint64_t)__double_as_longlong(v) | sign;
+        return true;
+    }
+    uint64_t v;
+    if (!js_eisel(w, -(int)frac, &v)) return false;
+    bits = v | sign;
     return true;
 }
 
@@ -955,8 +964,8 @@ __device__ __forceinline__ bool json_template_record(const SmemBytes &bytes, uin
     const uint8_t *s = bytes.s;
     uint32_t pos = 0;
     if (!JS_LIT("{\"deviceToken\":\"")) return false;
-    uint32_t tok[8], tl;
-    if (!js_plain_string(s + pos, tok, tl) || pos + tl >= n) return false;
+    uint32_t tl;
+    if (!js_plain_string<8>(s + pos, tl) || pos + tl >= n) return false;
     const uint32_t tok_off = pos;
     pos += tl;
     if (!JS_LIT("\",\"originator\":null,\"type\":\"Device")) return false;
@@ -985,10 +994,10 @@ __device__ __forceinline__ bool json_template_record(const SmemBytes &bytes, uin
     uint32_t level = 0, source = 0;
     if (kind == SWGPU_KIND_MEASUREMENT) {
         if (!JS_LIT("name\":\"")) return false;
-        uint32_t nm[8], nl;
-        if (!js_plain_string(s + pos, nm, nl) || pos + nl >= n) return false;
+        uint32_t nl;
+        if (!js_plain_string<8>(s + pos, nl) || pos + nl >= n) return false;
         nspan = sw_mk_span(pos, nl);
-        nh = js_hash_words(nm, nl);
+        nh = js_hash_at(s + pos, nl);
         pos += nl;
         if (!JS_LIT("\",\"value\":")) return false;
         uint32_t end;
@@ -1026,10 +1035,10 @@ __device__ __forceinline__ bool json_template_record(const SmemBytes &bytes, uin
         else
             return false;
         if (!JS_LIT("type\":\"")) return false;
-        uint32_t nm[8], nl;
-        if (!js_plain_string(s + pos, nm, nl) || pos + nl >= n) return false;
+        uint32_t nl;
+        if (!js_plain_string<8>(s + pos, nl) || pos + nl >= n) return false;
         nspan = sw_mk_span(pos, nl);
-        nh = js_hash_words(nm, nl);
+        nh = js_hash_at(s + pos, nl);
         pos += nl;
         if (!JS_LIT("\",\"message\":\"")) return false;
         // the message may be long: scan it four bytes at a time without keeping it
@@ -1057,7 +1066,7 @@ __device__ __forceinline__ bool json_template_record(const SmemBytes &bytes, uin
     if (pos + 2 != n || s[pos] != '}' || s[pos + 1] != '}') return false;
     r.status = SWGPU_ST_OK;
     r.meta = sw_mk_meta(kind, flags, level, source, 1, kind, rec);
-    r.th = js_hash_words(tok, tl);
+    r.th = js_hash_at(s + tok_off, tl);
     r.nh = nh;
     r.tspan = sw_mk_span(tok_off, tl);
     r.nspan = nspan;
@@ -1077,6 +1086,10 @@ __device__ __forceinline__ bool json_template_try(const B &, uint32_t, uint32_t,
 template <>
 __device__ __forceinline__ bool json_template_try<SmemBytes>(const SmemBytes &b, uint32_t n, uint32_t rec, JsRow &r) {
     return json_template_record(b, n, rec, r);
+}
+template <>  // (the caller asks for the template only for a record staged in shared memory)
+__device__ __forceinline__ bool json_template_try<AnyBytes>(const AnyBytes &b, uint32_t n, uint32_t rec, JsRow &r) {
+    return json_template_record(SmemBytes{b.s}, n, rec, r);
 }
 
 template <typename B, bool TPL = true>
@@ -1343,6 +1356,7 @@ __device__ __forceinline__ void json_decode_tile(const JsArgs &a, const uint32_t
         mine = mine && a.status[rec0 + lane] == JS_ST_PENDING;
         if (!__any_sync(SW_FULL, mine)) return;
     }
+    __syncwarp();  // (the dense pass walks tiles in a loop: every lane is done with the previous tile's bytes)
     const uint64_t b0 = __shfl_sync(SW_FULL, r0, 0);
     const uint64_t b1 = __shfl_sync(SW_FULL, r1, nrec ? nrec - 1 : 0);
     const uintptr_t addr = (uintptr_t)(a.bytes + b0);
@@ -1362,10 +1376,9 @@ __device__ __forceinline__ void json_decode_tile(const JsArgs &a, const uint32_t
     if (mine) {
         const uint64_t l64 = r1 - r0;
         const uint32_t len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
-        if (staged)
-            json_decode_record<SmemBytes, !DENSE>(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, len, a.rec_base + rec0 + lane, r, a.fast != 0, a.hits);
-        else
-            json_decode_record<GmemBytes, !DENSE>(GmemBytes{a.bytes + r0}, len, a.rec_base + rec0 + lane, r, a.fast != 0, a.hits);
+        // one copy of the parser for staged and unstaged records (generic loads): half the code of two
+        const uint8_t *rp = staged ? ws + lead + (uint32_t)(r0 - b0) : a.bytes + r0;
+        json_decode_record<AnyBytes, !DENSE>(AnyBytes{rp}, len, a.rec_base + rec0 + lane, r, a.fast != 0 && staged, a.hits);
         count = r.status == SWGPU_ST_OK ? 1u : 0u;
     }
     uint64_t tile_total = 0, row;
@@ -1394,9 +1407,9 @@ __device__ __forceinline__ void json_decode_tile(const JsArgs &a, const uint32_t
 // serialiser's layout is decoded here, every other one is marked JS_ST_PENDING for the dense pass that follows.
 // Nothing of the general parser is in this kernel: it stays small enough for the instruction cache.
 __global__ void __launch_bounds__(JS_THREADS) json_template_kernel(JsArgs a) {
-    extern __shared__ __align__(16) uint8_t smem[];  // JS_WARPS * (JS_WSTAGE + 32)
+    extern __shared__ __align__(16) uint8_t smem[];  // (JS_WSTAGE + 32) per warp of the CTA
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint64_t rec0_64 = (uint64_t)blockIdx.x * JS_THREADS + warp * 32;
+    const uint64_t rec0_64 = (uint64_t)blockIdx.x * blockDim.x + warp * 32;
     const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
     const uint32_t nrec = min(32u, a.n - rec0);
     uint8_t *ws = smem + warp * (JS_WSTAGE + 32);
@@ -1404,6 +1417,14 @@ __global__ void __launch_bounds__(JS_THREADS) json_template_kernel(JsArgs a) {
     if (lane < nrec) {
         r0 = a.rec_off[rec0 + lane];
         r1 = a.rec_off[rec0 + lane + 1];
+    }
+    // the bytes of the warp tile JS_AHEAD tiles further on are asked into L2 now (one bulk prefetch by lane 0 at
+    // the end of this tile), so that the warp that gets there finds its offsets and its records in L2
+    uint64_t p0 = 0, p1 = 0;
+    const uint64_t prec = rec0_64 + (uint64_t)JS_AHEAD * 32;
+    if (lane == 0 && prec < a.n) {
+        p0 = a.rec_off[prec];
+        p1 = a.rec_off[prec + 32 <= a.n ? prec + 32 : a.n];
     }
     const uint64_t b0 = __shfl_sync(SW_FULL, r0, 0);
     const uint64_t b1 = __shfl_sync(SW_FULL, r1, nrec ? nrec - 1 : 0);
@@ -1418,6 +1439,13 @@ __global__ void __launch_bounds__(JS_THREADS) json_template_kernel(JsArgs a) {
         for (uint32_t i = lane; i < nvec; i += 32) dst[i] = sw_ld_stream_u4(src + i);
     }
     __syncwarp();
+    if (lane == 0 && p1 > p0) {
+        const uintptr_t pa = (uintptr_t)(a.bytes + p0);
+        const uint64_t pspan = (pa & 15) + (p1 - p0);
+        if (pspan <= JS_WSTAGE)
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pa & ~(uintptr_t)15),
+                         "r"((uint32_t)((pspan + 15) & ~15ull)) : "memory");
+    }
     const uint64_t row_base = a.row_base ? (uint64_t)__ldg(a.row_base) : 0ull;
     bool hit = false;
     if (lane < nrec) {
@@ -1428,11 +1456,12 @@ __global__ void __launch_bounds__(JS_THREADS) json_template_kernel(JsArgs a) {
         a.first_row[rec0 + lane] = (uint32_t)(row_base + row);
         if (hit && row < a.max_rows) js_write_row(a, row, r);
     }
-    if (a.hits) {
-        const uint32_t m = __ballot_sync(SW_FULL, hit);
-        if (lane == 0 && m) atomicAdd(a.hits, (uint32_t)__popc(m));
+    const uint32_t hm = __ballot_sync(SW_FULL, hit);
+    if (lane == 0) {
+        if (a.hits && hm) atomicAdd(a.hits, (uint32_t)__popc(hm));
+        if ((uint32_t)__popc(hm) != nrec) atomicOr(a.pending, 1u);  // the dense pass has records to decode
     }
-    if ((uint64_t)blockIdx.x * JS_THREADS + JS_THREADS >= a.n && tid == 0) {  // the tile holding the last record
+    if ((uint64_t)blockIdx.x * blockDim.x + blockDim.x >= a.n && tid == 0) {  // the tile holding the last record
         a.first_row[a.n] = (uint32_t)(row_base + a.n);
         *a.out_rows = a.n;
         if (a.row_next) *a.row_next = (uint32_t)(row_base + a.n);
@@ -1449,7 +1478,9 @@ __global__ void __launch_bounds__(JS_THREADS) json_decode_kernel(JsArgs a) {
     __shared__ uint64_t s_warp[JS_THREADS / 32 + 2];
     __shared__ uint32_t s_tile;
     if (DENSE) {
-        json_decode_tile<true>(a, blockIdx.x, smem, s_warp);
+        if (a.fast && __ldg(a.pending) == 0) return;  // the template pass took every record
+        for (uint32_t tile = blockIdx.x; tile < (a.n + JS_THREADS - 1) / JS_THREADS; tile += gridDim.x)
+            json_decode_tile<true>(a, tile, smem, s_warp);
         return;
     }
     if (__ldg(a.not_dense) == 0) return;
@@ -1500,10 +1531,8 @@ __global__ void __launch_bounds__(JS_THREADS) json_decode_merge_kernel(JsArgs a)
         const uint64_t l64 = r1 - r0;
         const uint32_t len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
         JsRow r;
-        if (staged)
-            json_decode_record(SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, len, a.rec_base + rec, r, a.fast != 0);
-        else
-            json_decode_record(GmemBytes{a.bytes + r0}, len, a.rec_base + rec, r, a.fast != 0);
+        const uint8_t *rp = staged ? ws + lead + (uint32_t)(r0 - b0) : a.bytes + r0;
+        json_decode_record(AnyBytes{rp}, len, a.rec_base + rec, r, a.fast != 0 && staged);
         a.status[rec] = (uint8_t)r.status;
         count = r.status == SWGPU_ST_OK ? 1u : 0u;
         const uint32_t kind = SWGPU_META_KIND(r.meta), fl = SWGPU_META_FLAGS(r.meta);
@@ -1609,6 +1638,7 @@ int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *
     a.row_next = row_next;
     a.not_dense = (uint32_t *)ctx->scratch + 1;
     a.fast = ctx->opt_json_fast;
+    a.pending = (uint32_t *)ctx->scratch + 3;
     a.hits = ctx->opt_json_stats ? (uint32_t *)ctx->scratch + 2 : nullptr;
     const int smem = JS_WARPS * (JS_WSTAGE + 32);
     {
@@ -1625,12 +1655,15 @@ int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *
         }
     }
     if (a.fast) {
-        json_template_kernel<<<ntiles, JS_THREADS, smem, ctx->stream>>>(a);  // the serialiser's layout
+        // one warp per CTA: a CTA's shared memory goes back the moment its 32 records are done (measured: 27 resident
+        // warps per SM against 17 with four-warp CTAs, 0.114 -> 0.105 ms per 1 M records)
+        json_template_kernel<<<(n + 31) / 32, 32, JS_WSTAGE + 32, ctx->stream>>>(a);  // the serialiser's layout
         SW_CUDA(ctx, cudaGetLastError());
     }
-    json_decode_kernel<true><<<ntiles, JS_THREADS, smem, ctx->stream>>>(a);   // optimistic: rows = records
-    SW_CUDA(ctx, cudaGetLastError());
     const uint32_t nredo = ntiles < (uint32_t)ctx->sm_count * 4u ? ntiles : (uint32_t)ctx->sm_count * 4u;
+    // after the template pass the dense pass usually has little or nothing to do: a few CTAs per SM walk the tiles
+    json_decode_kernel<true><<<a.fast ? nredo : ntiles, JS_THREADS, smem, ctx->stream>>>(a);  // optimistic: rows = records
+    SW_CUDA(ctx, cudaGetLastError());
     json_decode_kernel<false><<<nredo, JS_THREADS, smem, ctx->stream>>>(a);  // exact redo iff not dense
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;

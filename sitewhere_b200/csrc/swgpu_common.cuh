@@ -262,6 +262,20 @@ struct SmemBytes {
         return ((uint64_t)hi << 32) | lo;
     }
 };
+// either of the two behind one type (generic addressing), where one copy of a large parser matters more than
+// LDS against LD: le64 reads the aligned words that hold the eight bytes, never one that holds none of them
+struct AnyBytes {
+    const uint8_t *s;
+    __device__ __forceinline__ uint32_t byte(uint32_t i) const { return s[i]; }
+    __device__ __forceinline__ uint64_t le64(uint32_t i) const {
+        const uintptr_t a = (uintptr_t)(s + i);
+        const uint32_t *w = (const uint32_t *)(a & ~(uintptr_t)3);
+        const uint32_t sh = (uint32_t)(a & 3) * 8;
+        const uint32_t w0 = w[0], w1 = w[1], w2 = sh ? w[2] : 0u;
+        const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
+        return ((uint64_t)hi << 32) | lo;
+    }
+};
 struct GmemBytes {
     const uint8_t *s;
     __device__ __forceinline__ uint32_t byte(uint32_t i) const { return __ldg(s + i); }
