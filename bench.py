@@ -539,7 +539,7 @@ def run_decode_zone(args, env, workload):
     # B_dec = payload + 8 per record (offsets) + 64 per decoded row
     bytes_s8d = total_bytes + 8 * n + 64 * n_rows
     bytes_moved = total_bytes + 8 * (n + 1) + 72 * n_rows + n + 4 * (n + 1)   # nine 8-byte columns + status + first_row
-    kname = "json_decode_kernel<dense>" if fmt == "json" else "pb_decode_dense_kernel<false>"
+    kname = "json_template_kernel" if fmt == "json" else "pb_decode_dense_kernel<false>"
     ach = bytes_s8d / (ms_dec * 1e-3) / 1e9
     tr = profile_traffic(kname, n)
     ms_step = ms_all / args.steps
@@ -551,15 +551,16 @@ def run_decode_zone(args, env, workload):
                          % (total_bytes / 1e6, 72 * n / 1e6),
                    "sharding": "Kafka murmur2(deviceToken) % n_gpus; zone table NCCL-broadcast once"},
         "e2e": e2e,
-        # per step: decode dense pass, ordered pass (returns at once on a dense batch), zone count, scan, emit
-        "gpu_launches": 5 * args.steps,
+        # per step: (JSON: template pass,) decode dense pass, ordered pass (returns at once on a dense batch), zone
+        # count, scan, emit
+        "gpu_launches": (6 if fmt == "json" else 5) * args.steps,
         "roofline": {"bound": "hbm", "kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                      "traffic": tr["dram_bytes"] if tr else None, "traffic_source": tr, "peak_source": peak_src,
                      "algorithmic_bytes": bytes_s8d,
                      "algorithmic_bytes_rule": "SURVEY.md §8(d): payload + 8/record + 64/row",
                      "bytes_moved_expected": bytes_moved, "duration_ms": ms_dec,
                      "duration": "mean over the timed steps, CUDA events around the decode stage on the launch stream "
-                                 "(dense kernel + the ordered pass that returns at once + one small memset)",
+                                 "(JSON: template pass + dense pass over what it left; protobuf: dense pass; + the ordered pass that returns at once + one small memset)",
                      "step_frac_hbm": (bytes_s8d + 24 * n_rows + 8 * n_pairs) / (ms_step * 1e-3) / 1e9 / peak},
         "kernels": {"decode": {"ms": ms_dec, "events_per_s": n / (ms_dec * 1e-3)}, "zone_test": zb},
     }

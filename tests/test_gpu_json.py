@@ -192,12 +192,18 @@ def test_fast_structural_pass_equals_general_pass(ctx):
     recs.append(S.json_measurement("tok", "n", "1.5", S.EVENT_DATE_BASE) + b" ")
     recs.append(S.json_measurement("tok", "n", "1.5", S.EVENT_DATE_BASE)[:-1])
     data, rec_off = S.pack_records(recs)
+    ctx.set_option("json.stats", 1)
     fast = ctx.decode_json(data, rec_off)
+    st_fast = ctx.json_stats()
     ctx.set_option("json.fast_path", 0)
     try:
         slow = ctx.decode_json(data, rec_off)
+        st_slow = ctx.json_stats()
     finally:
         ctx.set_option("json.fast_path", 1)
+        ctx.set_option("json.stats", 0)
+    # the template really took the canonical records (and none with the option off)
+    assert st_fast["template_records"] >= 6000 and st_slow["template_records"] == 0
     assert fast.n_rows == slow.n_rows and np.array_equal(fast.status, slow.status)
     assert np.array_equal(fast.first_row, slow.first_row)
     from tests.helpers import assert_cols_equal
