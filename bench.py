@@ -466,7 +466,13 @@ def run_decode_zone(args, env, workload):
     def run_zone():
         ctx.zone_test_dev(cols.v1, cols.v0, cols.meta, n, d_nrows, d_pairs, d_npairs)
 
+    # the timed step is ONE device-buffer call, swgpu_decode_zone_test_dev (decode, then the zone test on the columns)
     def step(timed):
+        ctx.decode_zone_test_dev(fmt, d_bytes, d_off, n, cols, d_status, d_first, d_nrows, d_pairs, d_npairs)
+
+    # the same work as two calls (swgpu_decode_*_dev, then swgpu_zone_test_dev on the decoded columns), timed per
+    # stage AFTER the timed region: what each stage costs on its own
+    def step_two_calls(timed):
         if timed:
             begin()
         decode(d_bytes, d_off, n, cols, d_status, d_first, d_nrows)
@@ -481,6 +487,10 @@ def run_decode_zone(args, env, workload):
         n_rows, n_pairs = int(d_nrows.item()), int(d_npairs.item())
         assert n_rows == n, (n_rows, n)
         assert int(d_status.max().item()) == 0
+        for k in range(args.warmup + args.steps):
+            step_two_calls(k >= args.warmup)
+        torch.cuda.synchronize()
+        assert (int(d_nrows.item()), int(d_npairs.item())) == (n_rows, n_pairs)
         ms_dec, ms_zone = mean_ms()
         zb = zone_block(ctx, run_zone, ms_zone, n_rows) if env.rank == 0 else None
     ms_all = max_over_ranks(env, ms)

@@ -284,6 +284,16 @@ int32_t swgpu_decode_zone_test(swgpu_ctx *ctx, int32_t format, const uint8_t *by
                                uint32_t *first_row, uint32_t *out_rows, uint64_t max_pairs, uint64_t *pairs,
                                uint64_t *n_pairs, uint32_t chunk_records);
 
+/* The same two steps on DEVICE buffers, asynchronous on the context's stream, in one call:
+ * swgpu_decode_{pb,json,enriched}_dev followed by swgpu_zone_test_dev(lon = out->v1, lat = out->v0, meta =
+ * out->meta, n = max_rows, n_rows_dev = out_rows_dev), with the same outputs
+ * (RP/kafka/KafkaRuleProcessorHost.java:144-153 hands each decoded location to
+ * ZoneTestRuleProcessor.onLocation).  All nine mandatory columns of `out` are required.                   */
+int32_t swgpu_decode_zone_test_dev(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off,
+                                   uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
+                                   uint32_t *first_row, uint32_t *out_rows_dev, uint64_t max_pairs, uint64_t *pairs,
+                                   uint64_t *n_pairs_dev);
+
 /* Start-up sizing (no counterpart in the reference): allocates every device and pinned buffer that
  * swgpu_decode_zone_test needs for batches of up to max_records records / max_bytes payload bytes, so that no
  * cudaMalloc / cudaFree — which stall every stream of the device, other contexts' included — happens once batches

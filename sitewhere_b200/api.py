@@ -263,6 +263,14 @@ class Context:
             n_rows_t.data_ptr() if n_rows_t is not None else None, pairs_t.numel(), pairs_t.data_ptr(),
             n_pairs_t.data_ptr()))
 
+    def decode_zone_test_dev(self, fmt, bytes_t, off_t, n, cols, status_t, first_row_t, n_rows_t, pairs_t, n_pairs_t):
+        """swgpu_decode_zone_test_dev: decode + zone test on device buffers, one call"""
+        s = cols.struct()
+        self._check(self.lib.swgpu_decode_zone_test_dev(
+            self.h, L.FMT[fmt] if isinstance(fmt, str) else int(fmt), bytes_t.data_ptr(), off_t.data_ptr(), int(n),
+            cols.capacity, C.byref(s), status_t.data_ptr(), first_row_t.data_ptr(), n_rows_t.data_ptr(), pairs_t.numel(),
+            pairs_t.data_ptr(), n_pairs_t.data_ptr()))
+
     def zone_stats(self) -> dict:
         """swgpu_zone_stats: work counters of the last zone test run with option zone.stats = 1."""
         out = (C.c_uint64 * 4)()

@@ -414,8 +414,8 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_ordered_kernel(PbArgs a)
 // of its shared-memory slice (one TMA bulk copy per tile, completion on an mbarrier) and the offsets of the tile after that
 // already requested, so the two serial round trips at the head of a tile (offsets, then payload: half of
 // the stall samples of the one-tile-per-warp kernel) are paid once per warp instead of once per tile.
-#ifndef PB_MERGE_MIN_CTAS
-#define PB_MERGE_MIN_CTAS 3  // fused decode + merge: resident CTAs per SM asked of the compiler (random table accesses want warps in flight)
+#ifndef PB_MIN_CTAS
+#define PB_MIN_CTAS 3  // resident CTAs per SM asked of the compiler (at most 80 registers): 3 CTAs for the plain pass as before, and the fused merge's random table accesses want warps in flight (128 registers and 2 CTAs without it: 1.63 against 1.54 ms per 10 M events)
 #endif
 #define PD_TILES 4
 #define PD_STAGE 3072  // bytes staged per warp tile (32 records of up to 96 B on average); larger tiles read global memory
@@ -493,7 +493,7 @@ __device__ __forceinline__ bool pd_issue(const PbArgs &a, uint32_t wt, uint32_t 
 // MERGE = false: rows -> columns (swgpu_decode_pb[_dev]).  MERGE = true: rows -> device-state table
 // (swgpu_decode_merge[_dev]): no columns, no first_row, no ordered redo; *out_rows counts the decoded rows.
 template <bool MERGE>
-__global__ void __launch_bounds__(PB_THREADS, MERGE ? PB_MERGE_MIN_CTAS : 1) pb_decode_dense_kernel(PbArgs a) {
+__global__ void __launch_bounds__(PB_THREADS, PB_MIN_CTAS) pb_decode_dense_kernel(PbArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];  // PB_WARPS * 2 * (PD_STAGE + 32)
     __shared__ __align__(8) uint64_t s_bar[PB_WARPS][2];
     __shared__ MgLocalCnt s_cnt[PB_WARPS];

@@ -172,3 +172,79 @@ def test_reserve_batch_then_async_submit_and_wait():
         assert ctx.lib.swgpu_wait(ctx.h, 99) == L.E_INVALID
     finally:
         ctx.close()
+
+
+def _dev_decode_zone(ctx, fmt, data, rec_off, cap_rows=None, cap_pairs=1 << 20):
+    """swgpu_decode_zone_test_dev on device buffers -> (per-column dict, status, first_row, n_rows, pairs)"""
+    import torch
+    import sitewhere_b200 as sw
+    from sitewhere_b200 import _lib as L
+    dev = torch.device("cuda", 0)
+    n = rec_off.shape[0] - 1
+    cap = cap_rows or max(n, 1)
+    st = torch.cuda.current_stream(dev)
+    c2 = sw.Context(0, stream=st.cuda_stream)
+    try:
+        d_bytes = torch.zeros(data.shape[0] + 64, dtype=torch.uint8, device=dev)
+        d_bytes[: data.shape[0]].copy_(torch.from_numpy(data))
+        d_off = torch.from_numpy(rec_off.view(np.int64)).to(dev)
+        cols = sw.DeviceCols(cap, dev, optional=True)
+        d_status = torch.zeros(max(n, 1), dtype=torch.uint8, device=dev)
+        d_first = torch.zeros(n + 1, dtype=torch.int32, device=dev)
+        d_rows = torch.zeros(1, dtype=torch.int32, device=dev)
+        d_pairs = torch.zeros(cap_pairs, dtype=torch.int64, device=dev)
+        d_np = torch.zeros(1, dtype=torch.int64, device=dev)
+        return c2, d_bytes, d_off, n, cols, d_status, d_first, d_rows, d_pairs, d_np
+    except Exception:
+        c2.close()
+        raise
+
+
+@pytest.mark.parametrize("shape", ["dense_locations", "mixed_with_failures", "outside_conditions", "json"])
+def test_decode_zone_test_dev_equals_oracle(ctx, shape):
+    """the device-buffer form against the oracle: a dense batch, a batch with failed records and measurement
+    fan-out (the ordered pass takes over), Outside conditions, and JSON"""
+    import torch
+    fmt = "json" if shape == "json" else "pb"
+    zones = S.star_zones(8, cond_mode="alternate") if shape == "outside_conditions" else S.star_zones(16)
+    if shape == "dense_locations" or shape == "outside_conditions":
+        lon, lat = S.locations_for_zones(30_001, *zones[:3], seed=21, boundary_rate=0.02)
+        data, rec_off, _ = S.pb_locations(30_001, 2000, lon, lat, seed=21)
+    elif shape == "mixed_with_failures":
+        good, goff, _ = S.pb_mixed(9000, 300, seed=22, zones=zones)
+        raw = good.tobytes()
+        recs = [raw[int(goff[i]): int(goff[i + 1])] for i in range(9000)]
+        cs = pb_cases.cases()
+        rng = np.random.default_rng(5)
+        for k in range(300):
+            recs.insert(int(rng.integers(0, len(recs))), cs[k % len(cs)][1])
+        recs.insert(500, S.pb_measurements_record("fan", [("m%03d" % k, float(k)) for k in range(40)], date=5))
+        data, rec_off = S.pack_records(recs)
+    else:
+        lon, lat = S.locations_for_zones(5000, *zones[:3], seed=23, boundary_rate=0.02)
+        recs = [S.json_location(S.token_str(i % 100), repr(float(lat[i])), repr(float(lon[i])), "1.5", S.EVENT_DATE_BASE + i)
+                for i in range(5000)]
+        data, rec_off = S.pack_records(recs)
+    ocols, ostatus, ofirst, ototal = getattr(oracle, "decode_pb" if fmt == "pb" else "decode_json")(data, rec_off)
+    want, total = oracle.zone_test(*zones, ocols.v1[:ototal], ocols.v0[:ototal], meta=ocols.meta[:ototal])
+    n = rec_off.shape[0] - 1
+    c2, d_bytes, d_off, n, cols, d_status, d_first, d_rows, d_pairs, d_np = _dev_decode_zone(
+        ctx, fmt, data, rec_off, cap_rows=max(ototal, n) + 7, cap_pairs=max(total, 1) + 5)
+    try:
+        c2.set_zones(*zones)
+        for _ in range(2):   # twice: the work area and flags are reused
+            c2.decode_zone_test_dev(fmt, d_bytes, d_off, n, cols, d_status, d_first, d_rows, d_pairs, d_np)
+        torch.cuda.synchronize()
+        assert int(d_rows.item()) == ototal
+        assert np.array_equal(d_status.cpu().numpy()[:n], ostatus)
+        assert np.array_equal(d_first.cpu().numpy().view(np.uint32), ofirst)
+        for name in ("meta", "token_hash", "name_hash", "event_date", "token_span", "name_span"):
+            assert np.array_equal(getattr(cols, name).cpu().numpy()[:ototal].view(np.uint64),
+                                  np.asarray(getattr(ocols, name)[:ototal]).view(np.uint64)), name
+        for name in ("v0", "v1", "v2"):
+            assert np.array_equal(getattr(cols, name).cpu().numpy()[:ototal].view(np.uint64),
+                                  np.asarray(getattr(ocols, name)[:ototal]).view(np.uint64)), name
+        assert int(d_np.item()) == total
+        assert np.array_equal(d_pairs.cpu().numpy()[:total].view(np.uint64), want)
+    finally:
+        c2.close()
