@@ -100,6 +100,24 @@ def profile_traffic(kernel: str, units: int):
     return None
 
 
+def random_access_ceiling(ms_fused: float, ms_unfused_merge: float, rows: int):
+    """The merge's table accesses are random sectors, not a stream: tools/exp/randacc.cu measures that access pattern
+    alone (random 64-byte read + atomicMax + one 256-bit store per row, the merge's own instructions; profiles/r02g_randacc.jsonl, largest table).
+    Returns the measured ceiling and how close the kernels are to it; None without the file."""
+    try:
+        best = None
+        for l in open(os.path.join(ROOT, "profiles", "r02d_randacc.jsonl")):
+            e = json.loads(l)
+            if e.get("variant") == "read64+atomicMax+store32 (one 256-bit store)" and (best is None or e["table_MB"] > best["table_MB"]):
+                best = e
+        ms = best["ms_per_10M_rows"] * rows / 1e7
+        return {"source": "profiles/r02g_randacc.jsonl (tools/exp/randacc.cu, %d MB table)" % best["table_MB"],
+                "ms_per_batch": ms, "frac_unfused_merge": ms / ms_unfused_merge, "frac_fused_decode_merge": ms / ms_fused,
+                "note": "fractions = ceiling time / kernel time; the fused kernel also decodes the payload in that time"}
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
@@ -706,7 +724,8 @@ def run_c3(args, env):
                      "bytes_moved_rule": "payload + offsets + 16 B ids + status + table: 64 B read, 64 B of dirty sectors per row",
                      "duration_ms": ms_step / nb,
                      "duration": "timed step / batches: the step is nothing but this kernel and its fix-up pass",
-                     "merge_only_frac_hbm_unfused": 73 * per / (ms_mrg * 1e-3) / 1e9 / peak},
+                     "merge_only_frac_hbm_unfused": 73 * per / (ms_mrg * 1e-3) / 1e9 / peak,
+                     "random_access_ceiling": random_access_ceiling(ms_step / nb, ms_mrg, per)},
         "kernels": {"fused_decode_merge": {"ms_per_batch": ms_step / nb, "events_per_s": per / (ms_step / nb * 1e-3)},
                     "unfused_decode_to_columns": {"ms_per_batch": ms_dec},
                     "unfused_merge_from_columns": {"ms_per_batch": ms_mrg, "rows_per_s": per / (ms_mrg * 1e-3),
