@@ -262,6 +262,31 @@ int32_t swgpu_zone_stats(swgpu_ctx *ctx, uint64_t out[4]);
  * the ordered second pass ran.  Waits for the context's stream.                                            */
 int32_t swgpu_json_stats(swgpu_ctx *ctx, uint64_t out[2]);
 
+/* ---- outbound payload -------------------------------------------------
+ * The GInboundEventPayload every decoded request is forwarded as, built on the device from the decoded rows.
+ * Replaces, per decoded request, EventSourcesManager.handleDecodedEvent's
+ * EventModelMarshaler.buildInboundEventPayloadMessage(payload) (ES/EventSourcesManager.java:152-166;
+ * sitewhere-grpc-event-management/.../EventModelMarshaler.java:93-115, EventModelConverter.java:1878-1887,
+ * 1621-1653, 399-406, 623-632, 770-784, 196-211).  `rows` are the columns of swgpu_decode_{pb,json}_dev over
+ * the same `bytes` / `rec_off` (strings are read through the spans; the four optional span columns may be NULL =
+ * no such property in any row), `format` says which decoder produced them (SWGPU_FMT_PROTOBUF: a row without
+ * event date gets `now_ms`, as ProtobufDeviceEventDecoder substitutes new Date(); SWGPU_FMT_JSON: it stays null
+ * -> 0).  Output: the records back to back in row order in `out`, out_off[n_rows + 1] (row r is
+ * out[out_off[r] .. out_off[r+1])), *out_bytes_dev = total length, and per row enc_status:                  */
+#define SWGPU_ENC_OK 0       /* bytes written                                                               */
+#define SWGPU_ENC_THROWS 1   /* the reference throws here (NullPointerException from a builder setter or an
+                              * unboxing, ClassCastException from an eventType that is not the request's):
+                              * nothing is sent for this request                                             */
+#define SWGPU_ENC_HANDBACK 3 /* the bytes depend on Java-side state (metadata map order, escaped / coerced /
+                              * non-ASCII strings): the caller builds this one with the stock marshaler      */
+#define SWGPU_ENC_NOTHING 4  /* the request is null: handleDecodedEvent sends nothing                        */
+/* A 256-row tile whose bytes do not fit `out_cap` is not written (out_off and *out_bytes_dev are still exact:
+ * call again with room).  source_id: at most 256 bytes, host memory.  Asynchronous on the context's stream. */
+int32_t swgpu_encode_inbound_dev(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off,
+                                 const swgpu_decoded_cols *rows, uint32_t n_rows, const uint32_t *n_rows_dev,
+                                 const uint8_t *source_id, uint32_t source_id_len, int64_t now_ms, uint8_t *out,
+                                 uint64_t out_cap, uint64_t *out_off, uint8_t *enc_status, uint64_t *out_bytes_dev);
+
 /* ---- fused host-buffer path ------------------------------------------------------------------------
  * Decode + zone test of one micro-batch held in HOST memory, in one call: what the Java binding's
  * micro-batcher issues per batch.  Replaces IDeviceEventDecoder.decode per payload

@@ -121,6 +121,9 @@ def lib() -> C.CDLL:
         L.orc_state_size.restype = C.c_uint64
         L.orc_state_size.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
         L.orc_state_snapshot.argtypes = [C.c_void_p] * 8
+        L.orc_encode_inbound.restype = C.c_uint64
+        L.orc_encode_inbound.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.POINTER(_ColsStruct), C.c_uint32, C.c_void_p,
+                                         C.c_uint32, C.c_int64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -185,6 +188,23 @@ def decode_enriched(data, rec_off, max_rows=None):
                                       C.byref(si), status.ctypes.data, first_row.ctypes.data)
     cols.n = min(int(total), max_rows)
     return cols, ids, status[:n], first_row, int(total)
+
+
+def encode_inbound(fmt: str, data, rec_off, cols: "Cols", n_rows: int, source_id: bytes, now_ms: int, out_cap=None):
+    """the GInboundEventPayload bytes each decoded row is forwarded as -> (out bytes, out_off[n_rows + 1], enc_status)"""
+    data = _u8(data)
+    rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
+    if out_cap is None:
+        out_cap = int(data.shape[0]) * 2 + (64 + len(source_id)) * max(n_rows, 1)
+    out = np.zeros(max(out_cap, 1), dtype=np.uint8)
+    out_off = np.zeros(n_rows + 1, dtype=np.uint64)
+    st = np.zeros(max(n_rows, 1), dtype=np.uint8)
+    src = np.frombuffer(source_id, dtype=np.uint8) if source_id else np.zeros(1, np.uint8)
+    s = cols.struct()
+    total = lib().orc_encode_inbound({"pb": 0, "json": 1}[fmt], data.ctypes.data if data.size else None, rec_off.ctypes.data,
+                                     C.byref(s), n_rows, src.ctypes.data, len(source_id), int(now_ms), out.ctypes.data,
+                                     out_cap, out_off.ctypes.data, st.ctypes.data)
+    return out[: min(int(total), out_cap)], out_off, st[:n_rows]
 
 
 def json_number_to_double(tok: str):

@@ -93,6 +93,11 @@ uint64_t orc_state_size(orc_state *, uint64_t *key_bytes);
 void orc_state_snapshot(orc_state *, uint64_t *seq, uint64_t *id_hi, uint64_t *id_lo,
                         int64_t *event_date, double *value, uint64_t *key_off, uint8_t *key_bytes);
 
+/* the GInboundEventPayload a decoded row is forwarded as (sw_oracle_encode.c) */
+uint64_t orc_encode_inbound(int format, const uint8_t *bytes, const uint64_t *rec_off, const orc_cols *c, uint32_t n_rows,
+                            const uint8_t *source_id, uint32_t source_len, int64_t now_ms, uint8_t *out, uint64_t out_cap,
+                            uint64_t *out_off, uint8_t *enc_status);
+
 #ifdef __cplusplus
 }
 #endif

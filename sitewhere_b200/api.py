@@ -271,6 +271,16 @@ class Context:
             cols.capacity, C.byref(s), status_t.data_ptr(), first_row_t.data_ptr(), n_rows_t.data_ptr(), pairs_t.numel(),
             pairs_t.data_ptr(), n_pairs_t.data_ptr()))
 
+    def encode_inbound_dev(self, fmt, bytes_t, off_t, cols, n_rows, n_rows_t, source_id: bytes, now_ms, out_t, out_off_t,
+                           enc_status_t, out_bytes_t):
+        """swgpu_encode_inbound_dev: the GInboundEventPayload bytes of every decoded row, back to back in `out_t`"""
+        s = cols.struct()
+        src = (C.c_uint8 * max(len(source_id), 1)).from_buffer_copy(source_id or b"\0")
+        self._check(self.lib.swgpu_encode_inbound_dev(
+            self.h, L.FMT[fmt], bytes_t.data_ptr(), off_t.data_ptr(), C.byref(s), int(n_rows),
+            n_rows_t.data_ptr() if n_rows_t is not None else None, src, len(source_id), int(now_ms), out_t.data_ptr(),
+            out_t.numel(), out_off_t.data_ptr(), enc_status_t.data_ptr(), out_bytes_t.data_ptr()))
+
     def zone_stats(self) -> dict:
         """swgpu_zone_stats: work counters of the last zone test run with option zone.stats = 1."""
         out = (C.c_uint64 * 4)()

@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libswgpu.so")
-SOURCES = ["ctx.cu", "decode_pb.cu", "decode_json.cu", "decode_enriched.cu", "zone.cu", "merge.cu", "pipeline.cu"]
+SOURCES = ["ctx.cu", "decode_pb.cu", "decode_json.cu", "decode_enriched.cu", "zone.cu", "merge.cu", "encode.cu", "pipeline.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "--expt-relaxed-constexpr", "--extended-lambda",

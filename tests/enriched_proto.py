@@ -84,11 +84,35 @@ def classes():
                                 ("deviceMetadata", 5, F.TYPE_MESSAGE, ""), ("assignmentStatus", 6, F.TYPE_ENUM, "GDeviceAssignmentStatus"),
                                 ("assignmentMetadata", 7, F.TYPE_MESSAGE, "")], maps=("deviceMetadata", "assignmentMetadata"))
     msg("GEnrichedEventPayload", [("context", 1, F.TYPE_MESSAGE, "GDeviceEventContext"), ("event", 2, F.TYPE_MESSAGE, "GAnyDeviceEvent")])
+    # the outbound side (device-event-model.proto:34-42,45-49,66-72,75-80,111-120,307-312; sitewhere-common.proto GOptionalBoolean)
+    msg("GOptionalBoolean", [("value", 1, F.TYPE_BOOL, "")])
+    msg("GDeviceEventCreateRequest", [("alternateId", 1, F.TYPE_MESSAGE, "GOptionalString"),
+                                      ("customerToken", 2, F.TYPE_MESSAGE, "GOptionalString"),
+                                      ("areaToken", 3, F.TYPE_MESSAGE, "GOptionalString"),
+                                      ("assetToken", 4, F.TYPE_MESSAGE, "GOptionalString"), ("eventDate", 5, F.TYPE_UINT64, ""),
+                                      ("updateState", 6, F.TYPE_MESSAGE, "GOptionalBoolean"), ("metadata", 7, F.TYPE_MESSAGE, "")],
+        maps=("metadata",))
+    msg("GDeviceMeasurementCreateRequest", [("name", 1, F.TYPE_STRING, ""), ("value", 2, F.TYPE_DOUBLE, ""),
+                                            ("event", 3, F.TYPE_MESSAGE, "GDeviceEventCreateRequest")])
+    msg("GDeviceAlertCreateRequest", [("source", 1, F.TYPE_ENUM, "GAlertSource"), ("level", 2, F.TYPE_ENUM, "GAlertLevel"),
+                                      ("type", 3, F.TYPE_STRING, ""), ("alertMessage", 4, F.TYPE_STRING, ""),
+                                      ("event", 5, F.TYPE_MESSAGE, "GDeviceEventCreateRequest")])
+    msg("GDeviceLocationCreateRequest", [("latitude", 1, F.TYPE_MESSAGE, "GOptionalDouble"),
+                                         ("longitude", 2, F.TYPE_MESSAGE, "GOptionalDouble"),
+                                         ("elevation", 3, F.TYPE_MESSAGE, "GOptionalDouble"),
+                                         ("event", 4, F.TYPE_MESSAGE, "GDeviceEventCreateRequest")])
+    msg("GAnyDeviceEventCreateRequest", [("measurement", 1, F.TYPE_MESSAGE, "GDeviceMeasurementCreateRequest"),
+                                         ("alert", 2, F.TYPE_MESSAGE, "GDeviceAlertCreateRequest"),
+                                         ("location", 3, F.TYPE_MESSAGE, "GDeviceLocationCreateRequest")], oneof="event")
+    msg("GInboundEventPayload", [("sourceId", 1, F.TYPE_STRING, ""), ("deviceToken", 2, F.TYPE_STRING, ""),
+                                 ("originator", 3, F.TYPE_MESSAGE, "GOptionalString"),
+                                 ("event", 4, F.TYPE_MESSAGE, "GAnyDeviceEventCreateRequest")])
     pool = descriptor_pool.DescriptorPool()
     pool.Add(fdp)
     get = lambda n: message_factory.GetMessageClass(pool.FindMessageTypeByName("com.sitewhere.grpc.model." + n))
     return {n: get(n) for n in ("GEnrichedEventPayload", "GAnyDeviceEvent", "GDeviceEvent", "GDeviceMeasurement", "GDeviceAlert",
-                                "GDeviceLocation", "GDeviceEventContext", "GUUID", "GOptionalDouble", "GOptionalString")}
+                                "GDeviceLocation", "GDeviceEventContext", "GUUID", "GOptionalDouble", "GOptionalString",
+                                "GInboundEventPayload", "GOptionalBoolean")}
 
 
 NAMES = ["fuel.level", "engine.temp", "oil.psi", "rpm.avg", "speed.kmh", "battery.v", "", "température"]
