@@ -511,6 +511,38 @@ def run_decode_zone(args, env, workload):
         assert (int(d_nrows.item()), int(d_npairs.item())) == (n_rows, n_pairs)
         ms_dec, ms_zone = mean_ms()
         zb = zone_block(ctx, run_zone, ms_zone, n_rows) if env.rank == 0 else None
+        # SURVEY.md §8 row N2 (not part of the timed step): the outbound GInboundEventPayload of every row, built on
+        # the device from the columns just decoded
+        enc = None
+        if env.rank == 0:
+            src = b"bench-source"
+            d_eoff = torch.empty(n + 1, dtype=torch.int64, device=dev)
+            d_est = torch.empty(n, dtype=torch.uint8, device=dev)
+            d_etot = torch.zeros(1, dtype=torch.int64, device=dev)
+            d_eout = torch.empty(int(total_bytes) + (48 + len(src)) * n, dtype=torch.uint8, device=dev)
+
+            def run_enc():
+                ctx.encode_inbound_dev(fmt, d_bytes, d_off, cols, n, d_nrows, src, 1_700_000_000_000, d_eout, d_eoff, d_est,
+                                       d_etot)
+            for _ in range(3):
+                run_enc()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(args.steps):
+                run_enc()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            ms_enc = e0.elapsed_time(e1) / args.steps
+            out_b = int(d_etot.item())
+            assert out_b <= d_eout.numel() and int(d_est.max().item()) == 0
+            # bytes moved: the columns it reads (meta, date, three values, two spans), the strings through the spans
+            # (token + name), sizes written and read back, offsets, status, and the records written
+            moved = 56 * n + out_b + 4 * 2 * n + 8 * n + n + 32 * n
+            enc = {"ms": ms_enc, "events_per_s": n / (ms_enc * 1e-3), "out_bytes": out_b,
+                   "out_bytes_per_event": out_b / n, "approx_bytes_moved": moved,
+                   "approx_frac_hbm": moved / (ms_enc * 1e-3) / 1e9 / measured_peaks()[0],
+                   "launches": "encode_size_kernel, encode_scan_kernel, encode_emit_kernel"}
+            del d_eout
     ms_all = max_over_ranks(env, ms)
     value = n * env.world * args.steps / (ms_all * 1e-3)
 
@@ -590,7 +622,8 @@ def run_decode_zone(args, env, workload):
                      "duration": "mean over the timed steps, CUDA events around the decode stage on the launch stream "
                                  "(JSON: template pass + dense pass over what it left; protobuf: dense pass; + the ordered pass that returns at once + one small memset)",
                      "step_frac_hbm": (bytes_s8d + 24 * n_rows + 8 * n_pairs) / (ms_step * 1e-3) / 1e9 / peak},
-        "kernels": {"decode": {"ms": ms_dec, "events_per_s": n / (ms_dec * 1e-3)}, "zone_test": zb},
+        "kernels": {"decode": {"ms": ms_dec, "events_per_s": n / (ms_dec * 1e-3)}, "zone_test": zb,
+                    "encode_inbound_payload (N2, outside the timed step)": enc},
     }
     return line, zones, (data, rec_off)
 

@@ -16,6 +16,7 @@
 // request), or when its bytes depend on Java-side state and the host shim has to build it (metadata map: HashMap
 // order; strings with JSON escapes, coerced from other tokens, or holding a byte >= 0x80).
 #include "swgpu_common.cuh"
+#include "tile_scan.cuh"
 
 #define EC_THREADS 256
 #define EC_STAGE (48 * 1024)  // a tile whose records fit is assembled in shared memory and copied out coalesced
@@ -52,13 +53,40 @@ __device__ __forceinline__ uint32_t ec_vl(uint64_t v) {  // bytes of a varint
     return v < 0x80 ? 1u : (uint32_t)(70 - __clzll((long long)v)) / 7u;
 }
 __device__ __forceinline__ uint32_t ec_str(uint32_t len) { return len ? 1u + ec_vl(len) + len : 0u; }
+// the aligned 32-bit words that hold s[0..n): word k of the stream, already shifted so that byte 0 is s[4k]
+struct EcWords {
+    const uint32_t *w;
+    uint32_t sh, nw, cur, k;
+    __device__ __forceinline__ void open(const uint8_t *s, uint32_t n) {
+        const uintptr_t a = (uintptr_t)s;
+        w = (const uint32_t *)(a & ~(uintptr_t)3);
+        sh = (uint32_t)(a & 3) * 8;
+        nw = ((uint32_t)(a & 3) + n + 3) >> 2;  // aligned words with at least one byte of the string
+        k = 0;
+        cur = n ? __ldg(w) : 0u;
+    }
+    __device__ __forceinline__ uint32_t next() {  // (a word past the last one that holds a byte of s is never read)
+        k++;
+        const uint32_t nx = k < nw ? __ldg(w + k) : 0u;
+        const uint32_t v = __funnelshift_r(cur, nx, sh);
+        cur = nx;
+        return v;
+    }
+};
 __device__ __forceinline__ bool ec_ascii(const uint8_t *s, uint32_t n) {
+    EcWords ws;
+    ws.open(s, n);
     uint32_t acc = 0;
-    for (uint32_t i = 0; i < n; i++) acc |= __ldg(s + i);
-    return acc < 0x80;
+    for (uint32_t i = 0; i < n; i += 4) {
+        const uint32_t v = ws.next();
+        acc |= n - i >= 4 ? v : v & ((1u << (8 * (n - i))) - 1u);
+    }
+    return (acc & 0x80808080u) == 0;
 }
 
-// loads row i and decides its status (see the header); lengths of the parts it will not write are zeroed
+// loads row i and decides its status (see the header); lengths of the parts it will not write are zeroed.
+// CHECK = false: the row is known to be SWGPU_ENC_OK (the emit pass): the strings are not scanned again
+template <bool CHECK>
 __device__ __forceinline__ uint32_t ec_load(const EcArgs &a, uint32_t i, EcRow &r) {
     const uint64_t m = __ldg(a.cols.meta + i);
     r.kind = SWGPU_META_KIND(m);
@@ -92,6 +120,7 @@ __device__ __forceinline__ uint32_t ec_load(const EcArgs &a, uint32_t i, EcRow &
     if (r.kind != SWGPU_KIND_ALERT) r.msg_len = 0;
     if (!(r.flags & SWGPU_F_HAS_ORIGINATOR)) r.orig_len = 0;
     if (!(r.flags & SWGPU_F_HAS_ALT_ID)) r.alt_len = 0;
+    if (!CHECK) return SWGPU_ENC_OK;
     if ((r.flags & (SWGPU_F_HAS_METADATA | SWGPU_F_STR_ESCAPED | SWGPU_F_NAME_COERCED)) || !ec_ascii(r.tok, r.tok_len) ||
         !ec_ascii(r.name, r.name_len) || !ec_ascii(r.msg, r.msg_len) || !ec_ascii(r.orig, r.orig_len) ||
         !ec_ascii(r.alt, r.alt_len))
@@ -137,11 +166,25 @@ struct EcWr {  // byte writer (generic address: shared-memory stage or global me
 #pragma unroll
         for (int k = 0; k < 8; k++) *p++ = (uint8_t)(u >> (8 * k));
     }
-    __device__ __forceinline__ void str(uint32_t tag, const uint8_t *s, uint32_t len) {  // global source
+    __device__ __forceinline__ void str(uint32_t tag, const uint8_t *s, uint32_t len) {  // global source, 4 bytes per load
         if (!len) return;
         b(tag);
         varint(len);
-        for (uint32_t i = 0; i < len; i++) *p++ = __ldg(s + i);
+        EcWords ws;
+        ws.open(s, len);
+        uint32_t i = 0;
+        for (; i + 4 <= len; i += 4) {
+            const uint32_t v = ws.next();
+            p[0] = (uint8_t)v;
+            p[1] = (uint8_t)(v >> 8);
+            p[2] = (uint8_t)(v >> 16);
+            p[3] = (uint8_t)(v >> 24);
+            p += 4;
+        }
+        if (i < len) {
+            uint32_t v = ws.next();
+            for (; i < len; i++, v >>= 8) *p++ = (uint8_t)v;
+        }
     }
     __device__ __forceinline__ void str_param(uint32_t tag, const uint8_t *s, uint32_t len) {  // kernel-parameter source
         if (!len) return;
@@ -233,50 +276,13 @@ __global__ void __launch_bounds__(EC_THREADS) encode_size_kernel(EcArgs a) {
     uint32_t len = 0;
     if (i < n_live) {
         EcRow r;
-        const uint32_t st = ec_load(a, i, r);
+        const uint32_t st = ec_load<true>(a, i, r);
         a.enc_status[i] = (uint8_t)st;
         if (st == SWGPU_ENC_OK) len = ec_lens(a, r).total;
     }
     if (i < a.n) a.lens[i] = len;
     const uint32_t tot = ec_block_sum(len, s_part);
     if (threadIdx.x == 0) a.tile_tot[blockIdx.x] = tot;
-}
-
-// one CTA: exclusive scan of the tile totals
-__global__ void __launch_bounds__(1024) encode_scan_kernel(const uint64_t *tot, uint64_t *base, uint32_t ntiles, uint64_t *total) {
-    __shared__ uint64_t s_w[32];
-    __shared__ uint64_t s_carry;
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) s_carry = 0;
-    __syncthreads();
-    for (uint32_t t0 = 0; t0 < ntiles; t0 += 1024) {
-        const uint32_t t = t0 + threadIdx.x;
-        const uint64_t v = t < ntiles ? tot[t] : 0;
-        uint64_t inc = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint64_t u = __shfl_up_sync(SW_FULL, inc, o);
-            if (lane >= (uint32_t)o) inc += u;
-        }
-        if (lane == 31) s_w[warp] = inc;
-        __syncthreads();
-        if (warp == 0) {
-            uint64_t x = s_w[lane], y = x;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint64_t u = __shfl_up_sync(SW_FULL, y, o);
-                if (lane >= (uint32_t)o) y += u;
-            }
-            s_w[lane] = y - x;  // exclusive prefix of the warp sums
-        }
-        __syncthreads();
-        const uint64_t carry = s_carry;
-        if (t < ntiles) base[t] = carry + s_w[warp] + inc - v;
-        __syncthreads();
-        if (threadIdx.x == 1023) s_carry = carry + s_w[warp] + inc;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) *total = s_carry;
 }
 
 __global__ void __launch_bounds__(EC_THREADS) encode_emit_kernel(EcArgs a) {
@@ -314,7 +320,7 @@ __global__ void __launch_bounds__(EC_THREADS) encode_emit_kernel(EcArgs a) {
     const bool staged = head + tile_len <= EC_STAGE;
     if (len && i < n_live) {
         EcRow r;
-        ec_load(a, i, r);
+        ec_load<false>(a, i, r);
         const EcLens l = ec_lens(a, r);
         ec_write(a, r, l, staged ? stage + head + excl : a.out + pos);
     }
@@ -389,7 +395,11 @@ extern "C" int32_t swgpu_encode_inbound_dev(swgpu_ctx *ctx, int32_t format, cons
     }
     encode_size_kernel<<<ntiles, EC_THREADS, 0, ctx->stream>>>(a);
     SW_CUDA(ctx, cudaGetLastError());
-    encode_scan_kernel<<<1, 1024, 0, ctx->stream>>>(a.tile_tot, a.tile_base, ntiles, out_bytes_dev);
+    if (ntiles <= ZS_MC_MAX_TILES)
+        zone_scan_mc_kernel<<<(ntiles + ZS_THREADS - 1) / ZS_THREADS, ZS_THREADS, 0, ctx->stream>>>(a.tile_tot, a.tile_base, ntiles,
+                                                                                                  out_bytes_dev);
+    else
+        zone_scan_kernel<<<1, ZS_THREADS, 0, ctx->stream>>>(a.tile_tot, a.tile_base, ntiles, out_bytes_dev);
     SW_CUDA(ctx, cudaGetLastError());
     encode_emit_kernel<<<ntiles, EC_THREADS, EC_STAGE + 32, ctx->stream>>>(a);
     SW_CUDA(ctx, cudaGetLastError());
