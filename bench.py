@@ -50,13 +50,17 @@ WORKLOADS = {
     "c3": dict(metric="events/sec decode+merge",
                name="C3: 100M mixed measurement/location/alert protobuf events, 1M device tokens, decode + device-state merge",
                events=100_000_000),
+    "n1": dict(metric="events/sec decode+zone-test",
+               name="N1 (SURVEY.md section 8f): 10M GEnrichedEventPayload location records off the inbound-enriched-events topic, "
+                    "enriched decode + zone test vs 1,024 concave 64-vertex zones; decode + device-state merge beside it",
+               events=10_000_000),
     "c5": dict(metric="events/sec decode+zone-test (64 KB micro-batch stream)",
                name="C5: 64 KB micro-batch stream of protobuf DeviceLocation events, 10M devices, 65,536 concave 64-vertex zones",
                events=2_000_000),
 }
 C3_BATCH = 10_000_000
 C5_POLL_BYTES = 65_536
-CPU_SAMPLE = {"c1": 300_000, "c2": 2_000_000, "c3": 4_000_000, "c5": 24_000}
+CPU_SAMPLE = {"c1": 300_000, "c2": 2_000_000, "c3": 4_000_000, "c5": 24_000, "n1": 2_000_000}
 
 
 def measured_peaks():
@@ -183,6 +187,13 @@ def gen_locations(n, zones, n_devices, rank, world, seed):
     return data, rec_off
 
 
+def gen_n1(n, zones, rank):
+    from sitewhere_b200 import synth as S
+    lon, lat = S.locations_for_zones(n, *zones[:3], seed=S.SEED_BASE + 9 + 1000 * rank)
+    data, rec_off, _ = S.enriched_locations(n, N_DEVICES, lon, lat, seed=S.SEED_BASE + 9 + 1000 * rank)
+    return data, rec_off
+
+
 def gen_c1(n, rank):
     """n JSON measurement requests; the generator's Python loop is slow, so 250 K distinct payloads are tiled"""
     from sitewhere_b200 import synth as S
@@ -209,6 +220,8 @@ def build_inputs(workload, n, rank, world):
         return zones, gen_c1(n, rank)
     if workload == "c2":
         return zones, gen_locations(n, zones, N_DEVICES, rank, world, S.SEED_BASE + 1)
+    if workload == "n1":
+        return zones, gen_n1(n, zones, rank)
     if workload == "c5":
         return zones, gen_locations(n, zones, 10_000_000, rank, world, S.SEED_BASE + 4)
     nb = max(1, (n + C3_BATCH - 1) // C3_BATCH)
@@ -233,7 +246,11 @@ def cpu_decode_zone(fmt, zones, data, rec_off, threads):
     """The oracle's decode + index-free zone loop, records split over `threads` host threads (ctypes drops the GIL)."""
     import oracle
     oracle.lib()
-    dec = oracle.decode_json if fmt == "json" else oracle.decode_pb
+    def dec(chunk, off, max_rows):
+        if fmt == "enriched":
+            cols, ids, status, first_row, total = oracle.decode_enriched(chunk, off, max_rows=max_rows)
+            return cols, status, first_row, total
+        return (oracle.decode_json if fmt == "json" else oracle.decode_pb)(chunk, off, max_rows=max_rows)
 
     def work(a, b):
         if a == b:
@@ -272,7 +289,7 @@ def cpu_leg(workload, zones, rank_inputs, cores, sample):
         return sample, t, f"first {sample} events of batch 0: decode + sequential fold, one state per thread"
     data, rec_off = rank_inputs
     sample = min(sample, rec_off.shape[0] - 1)
-    fmt = "json" if workload == "c1" else "pb"
+    fmt = "json" if workload == "c1" else "enriched" if workload == "n1" else "pb"
     t = cpu_decode_zone(fmt, zones, data[: int(rec_off[sample])], rec_off[: sample + 1], cores)
     return sample, t, f"first {sample} events of the same input: decode + index-free zone loop over {len(zones[3])} zones"
 
@@ -460,7 +477,7 @@ def zone_block(ctx, run_zone, ms_zone, n_loc):
 def run_decode_zone(args, env, workload):
     torch, sw, ctx, dev, stream = env.torch, env.sw, env.ctx, env.dev, env.stream
     from sitewhere_b200.api import pinned_array, pinned_cols
-    fmt = "json" if workload == "c1" else "pb"
+    fmt = "json" if workload == "c1" else "enriched" if workload == "n1" else "pb"
     zones, (data, rec_off) = build_inputs(workload, args.events, env.rank, env.world)
     n = rec_off.shape[0] - 1
     if env.rank == 0:
@@ -478,7 +495,7 @@ def run_decode_zone(args, env, workload):
     d_pairs = torch.empty(max_pairs, dtype=torch.int64, device=dev)
     d_npairs = torch.zeros(1, dtype=torch.int64, device=dev)
     torch.cuda.synchronize()
-    decode = ctx.decode_json_dev if fmt == "json" else ctx.decode_pb_dev
+    decode = {"json": ctx.decode_json_dev, "enriched": ctx.decode_enriched_dev, "pb": ctx.decode_pb_dev}[fmt]
     begin, mark, mean_ms = stage_timer(torch, stream, 2)
 
     def run_zone():
@@ -514,7 +531,32 @@ def run_decode_zone(args, env, workload):
         # SURVEY.md §8 row N2 (not part of the timed step): the outbound GInboundEventPayload of every row, built on
         # the device from the columns just decoded
         enc = None
-        if env.rank == 0:
+        mrg = None
+        if env.rank == 0 and fmt == "enriched":
+            # the device-state consumer's side of the same topic: decode + merge in one kernel, presence rows kept
+            ctx.state_clear()
+            ctx.state_reserve(4 * N_DEVICES, 1 << 20)
+            seqn = [0]
+
+            def run_mrg():
+                ctx.set_option("state.presence_now_ms", 1_700_000_000_000 + seqn[0])
+                ctx.decode_merge_dev("enriched", d_bytes, d_off, n, seqn[0], None, None, d_status, d_nrows)
+                seqn[0] += n << 12
+            for _ in range(3):
+                run_mrg()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(args.steps):
+                run_mrg()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            ms_m = e0.elapsed_time(e1) / args.steps
+            keys, _kb = ctx.state_size()
+            ctx.set_option("state.presence_now_ms", 0)
+            mrg = {"ms": ms_m, "events_per_s": n / (ms_m * 1e-3), "state_keys": keys,
+                   "what": "swgpu_decode_merge_dev(SWGPU_FMT_ENRICHED) with state.presence_now_ms set: one kernel parses the "
+                           "payload, folds the location and touches the device's presence row"}
+        if env.rank == 0 and fmt != "enriched":
             src = b"bench-source"
             d_eoff = torch.empty(n + 1, dtype=torch.int64, device=dev)
             d_est = torch.empty(n, dtype=torch.uint8, device=dev)
@@ -599,7 +641,7 @@ def run_decode_zone(args, env, workload):
     # B_dec = payload + 8 per record (offsets) + 64 per decoded row
     bytes_s8d = total_bytes + 8 * n + 64 * n_rows
     bytes_moved = total_bytes + 8 * (n + 1) + 72 * n_rows + n + 4 * (n + 1)   # nine 8-byte columns + status + first_row
-    kname = "json_template_kernel" if fmt == "json" else "pb_decode_dense_kernel<false>"
+    kname = {"json": "json_template_kernel", "enriched": "enriched_decode_kernel<dense>", "pb": "pb_decode_dense_kernel<false>"}[fmt]
     ach = bytes_s8d / (ms_dec * 1e-3) / 1e9
     tr = profile_traffic(kname, n)
     ms_step = ms_all / args.steps
@@ -623,7 +665,8 @@ def run_decode_zone(args, env, workload):
                                  "(JSON: template pass + dense pass over what it left; protobuf: dense pass; + the ordered pass that returns at once + one small memset)",
                      "step_frac_hbm": (bytes_s8d + 24 * n_rows + 8 * n_pairs) / (ms_step * 1e-3) / 1e9 / peak},
         "kernels": {"decode": {"ms": ms_dec, "events_per_s": n / (ms_dec * 1e-3)}, "zone_test": zb,
-                    "encode_inbound_payload (N2, outside the timed step)": enc},
+                    "encode_inbound_payload (N2, outside the timed step)": enc,
+                    "decode_merge_with_presence (outside the timed step)": mrg},
     }
     return line, zones, (data, rec_off)
 
@@ -948,7 +991,7 @@ def run_ours(args):
     env.barrier = barrier
 
     w = WORKLOADS[args.workload]
-    if args.workload in ("c1", "c2"):
+    if args.workload in ("c1", "c2", "n1"):
         res = run_decode_zone(args, env, args.workload)
     elif args.workload == "c3":
         res = run_c3(args, env)

@@ -159,6 +159,8 @@ int32_t swgpu_sync(swgpu_ctx *ctx);
  *   "json.fast_path"        0 = every JSON record takes the general structural pass; 1 (default) = a record in
  *                           exactly the shape the reference's own serialiser writes is first tried against that
  *                           template (same result, far fewer instructions)
+ *   "enriched.fast_path"    0 = every enriched record takes the general proto3 parser; 1 (default) = a payload in
+ *                           the serialiser's own field order is read in one forward pass first (same result)
  *   "json.stats"            1 = JSON decodes count the records the template took (swgpu_json_stats)
  *   "zone.stats"            1 = zone tests also count their work (read it with swgpu_zone_stats)        */
 int32_t swgpu_set_option(swgpu_ctx *ctx, const char *name, int64_t value);

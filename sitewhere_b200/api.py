@@ -237,6 +237,13 @@ class Context:
                                                    cols.capacity, C.byref(s), status_t.data_ptr(),
                                                    first_row_t.data_ptr(), n_rows_t.data_ptr()))
 
+    def decode_enriched_dev(self, bytes_t, off_t, n, cols: DeviceCols, status_t, first_row_t, n_rows_t, ids_struct=None):
+        """swgpu_decode_enriched_dev (ids_struct: an EventIdsStruct of device pointers, or None = ids not wanted)"""
+        s = cols.struct()
+        self._check(self.lib.swgpu_decode_enriched_dev(self.h, bytes_t.data_ptr(), off_t.data_ptr(), int(n), cols.capacity,
+                                                       C.byref(s), C.byref(ids_struct) if ids_struct is not None else None,
+                                                       status_t.data_ptr(), first_row_t.data_ptr(), n_rows_t.data_ptr()))
+
     # ---- zone test ----------------------------------------------------------------------------------
     def zone_test(self, lon, lat, meta=None, max_pairs=None):
         lon = np.ascontiguousarray(lon, dtype=np.float64)

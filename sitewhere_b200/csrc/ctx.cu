@@ -171,6 +171,10 @@ extern "C" int32_t swgpu_set_option(swgpu_ctx *ctx, const char *name, int64_t va
         ctx->opt_json_fast = value ? 1u : 0u;
         return SWGPU_OK;
     }
+    if (!strcmp(name, "enriched.fast_path")) {
+        ctx->opt_enriched_fast = value ? 1u : 0u;
+        return SWGPU_OK;
+    }
     if (!strcmp(name, "json.stats")) {
         ctx->opt_json_stats = value ? 1u : 0u;
         return SWGPU_OK;

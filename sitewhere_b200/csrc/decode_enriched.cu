@@ -50,7 +50,10 @@ struct EnArgs {
     uint32_t *not_dense;
     MgTable mt;  // fused decode + merge
     uint64_t seq_base;
+    uint32_t fast;      // option "enriched.fast_path": the forward-pass kernel ran first, this pass takes what it left
+    uint32_t *pending;  // forward pass -> general pass: non-zero when records were left
 };
+#define EN_ST_PENDING 0xffu  // internal record status between the two passes
 
 // ---- message values (defaults: all zero) and their proto3 merge ----------------------------------------------------
 struct EnUuid {
@@ -409,34 +412,9 @@ struct EnKeyBytes {
     __device__ __forceinline__ uint64_t le64(uint32_t i) const { return i == 0 ? msb : lsb; }  // (only offsets 0 and 8 are asked for)
 };
 
+// what the converter makes of a parsed payload (EventModelConverter.asApiEnrichedEventPayload): enum checks, flags, row
 template <typename B>
-__device__ void en_decode_record(B bytes, uint32_t total, uint32_t rec, EnRow &row) {
-    memset(&row, 0, sizeof row);
-    EnParser<B> p;
-    p.r.b = bytes;
-    p.r.pos = 0;
-    p.r.end = total;
-    p.r.limit = total;  // parseFrom(byte[]): the array's length is the outermost limit
-    p.r.err = false;
-    p.r.last_tag = 0;
-    EnAny ev;
-    memset(&ev, 0, sizeof ev);
-    uint32_t asg_status = 0;
-    while (!p.r.err) {
-        const uint32_t tag = p.r.read_tag();
-        if (p.r.err || tag == 0) break;
-        if (tag == 10)
-            p.context(asg_status);
-        else if (tag == 18)
-            p.any(ev);
-        else if (!p.r.unknown(tag))
-            break;
-    }
-    if (!p.r.err && p.r.last_tag != 0) p.r.err = true;
-    if (p.r.err) {
-        row.status = SWGPU_ST_DECODE_EXCEPTION;
-        return;
-    }
+__device__ __forceinline__ void en_finish(const B &bytes, uint32_t rec, const EnAny &ev, uint32_t asg_status, EnRow &row) {
     if (ev.ocase == 4) {
         row.status = SWGPU_ST_PASSTHROUGH;
         return;
@@ -480,6 +458,239 @@ __device__ void en_decode_record(B bytes, uint32_t total, uint32_t rec, EnRow &r
     row.dev_lo = ev.ev.device.lsb;
 }
 
+template <typename B>
+__device__ void en_decode_record(B bytes, uint32_t total, uint32_t rec, EnRow &row) {
+    memset(&row, 0, sizeof row);
+    EnParser<B> p;
+    p.r.b = bytes;
+    p.r.pos = 0;
+    p.r.end = total;
+    p.r.limit = total;  // parseFrom(byte[]): the array's length is the outermost limit
+    p.r.err = false;
+    p.r.last_tag = 0;
+    EnAny ev;
+    memset(&ev, 0, sizeof ev);
+    uint32_t asg_status = 0;
+    while (!p.r.err) {
+        const uint32_t tag = p.r.read_tag();
+        if (p.r.err || tag == 0) break;
+        if (tag == 10)
+            p.context(asg_status);
+        else if (tag == 18)
+            p.any(ev);
+        else if (!p.r.unknown(tag))
+            break;
+    }
+    if (!p.r.err && p.r.last_tag != 0) p.r.err = true;
+    if (p.r.err) {
+        row.status = SWGPU_ST_DECODE_EXCEPTION;
+        return;
+    }
+    en_finish(bytes, rec, ev, asg_status, row);
+}
+
+// ---- the serialiser's own layout ---------------------------------------------------------------------------------
+// protobuf-java writes a message's known fields in field-number order, each once (map entries one after another), and
+// proto3 3.3.0 keeps no unknown fields: every payload the reference itself produces can be read in ONE forward pass with
+// no merge bookkeeping.  en_fast_parse accepts exactly that — the expected tags in ascending order, lengths of at most
+// two bytes, single-byte enum values, strings without a byte >= 0x80 — and fills the same EnAny the general parser
+// fills (a field that occurs once is taken as parsed there too); anything else returns false and the general parser
+// decodes the record from the start, so this path never decides an error.  Shared-memory records only.
+struct EnFast {
+    const uint8_t *s;
+    uint32_t p, end;
+    bool bad;
+    __device__ __forceinline__ bool at(uint32_t tag) const { return p < end && s[p] == tag; }
+    // the length after a tag at p (one or two bytes); p moves to the body
+    __device__ __forceinline__ uint32_t len() {
+        uint32_t l = p + 1 < end ? s[p + 1] : 0x80u;
+        p += 2;
+        if (l & 0x80) {
+            const uint32_t h = p < end ? s[p] : 0x80u;
+            p++;
+            if (h & 0x80) bad = true;
+            l = (l & 0x7f) | (h << 7);
+        }
+        if (p + l > end) bad = true;
+        return l;
+    }
+    __device__ __forceinline__ uint64_t le64(uint32_t o) const { return SmemBytes{s}.le64(o); }
+    __device__ __forceinline__ void ascii(uint32_t off, uint32_t l) {
+        uint32_t acc = 0;
+        for (uint32_t i = 0; i < l; i++) acc |= s[off + i];
+        if (acc & 0x80) bad = true;
+    }
+    // GUUID {fixed64 msb = 1; fixed64 lsb = 2}
+    __device__ __forceinline__ void uuid(uint32_t tag, EnUuid &u) {
+        if (!at(tag)) return;
+        const uint32_t l = len();
+        if (bad) return;
+        u.has = 1;
+        uint32_t q = p;
+        if (q < p + l && s[q] == 0x09 && q + 9 <= p + l) {
+            u.msb = le64(q + 1);
+            q += 9;
+        }
+        if (q < p + l && s[q] == 0x11 && q + 9 <= p + l) {
+            u.lsb = le64(q + 1);
+            q += 9;
+        }
+        if (q != p + l) bad = true;
+        p += l;
+    }
+    __device__ __forceinline__ void str(uint32_t tag, uint32_t &off, uint32_t &l) {
+        if (!at(tag)) return;
+        l = len();
+        if (bad) return;
+        off = p;
+        ascii(off, l);
+        p += l;
+    }
+    // GOptionalString {string value = 1}
+    __device__ __forceinline__ void opt_str(uint32_t tag, EnStr &t) {
+        if (!at(tag)) return;
+        const uint32_t l = len();
+        if (bad) return;
+        const uint32_t e = p + l;
+        t.has = 1;
+        EnFast in{s, p, e, false};
+        in.str(0x0A, t.off, t.len);
+        if (in.bad || in.p != e) bad = true;
+        p = e;
+    }
+    // GOptionalDouble {double value = 1}
+    __device__ __forceinline__ void opt_dbl(uint32_t tag, EnDbl &t) {
+        if (!at(tag)) return;
+        const uint32_t l = len();
+        if (bad) return;
+        t.has = 1;
+        if (l == 9 && s[p] == 0x09)
+            t.bits = le64(p + 1);
+        else if (l != 0)
+            bad = true;
+        p += l;
+    }
+    // map<string,string> entries of one field, one after another; returns how many
+    __device__ __forceinline__ uint32_t map(uint32_t tag, uint32_t &first_pos) {
+        uint32_t cnt = 0;
+        while (!bad && at(tag)) {
+            if (!cnt) first_pos = p;
+            cnt++;
+            const uint32_t l = len();
+            if (bad) break;
+            const uint32_t e = p + l;
+            EnFast in{s, p, e, false};
+            uint32_t o, n;
+            in.str(0x0A, o, n);
+            in.str(0x12, o, n);
+            if (in.bad || in.p != e) bad = true;
+            p = e;
+        }
+        return cnt;
+    }
+    __device__ __forceinline__ void enum1(uint32_t tag, uint32_t &v) {  // single-byte varint
+        if (!at(tag)) return;
+        if (p + 1 >= end || (s[p + 1] & 0x80)) {
+            bad = true;
+            return;
+        }
+        v = s[p + 1];
+        p += 2;
+    }
+    __device__ __forceinline__ void varint(uint32_t tag, uint64_t &v) {
+        if (!at(tag)) return;
+        p++;
+        uint64_t r = 0;
+        for (uint32_t k = 0; k < 10; k++) {
+            if (p >= end) break;
+            const uint32_t b = s[p++];
+            r |= (uint64_t)(b & 0x7f) << (7 * k);
+            if (!(b & 0x80)) {
+                v = r;
+                return;
+            }
+        }
+        bad = true;
+    }
+    // GDeviceEvent
+    __device__ __forceinline__ void event(uint32_t tag, EnEvent &t) {
+        if (!at(tag)) return;
+        const uint32_t l = len();
+        if (bad) return;
+        const uint32_t e = p + l;
+        EnFast in{s, p, e, false};
+        t.has = 1;
+        in.uuid(0x0A, t.id);
+        in.opt_str(0x12, t.alt);
+        in.enum1(0x18, t.etype);
+        in.uuid(0x22, t.device);
+        in.uuid(0x2A, t.assignment);
+        EnUuid drop{0u, 0ull, 0ull};
+        in.uuid(0x32, drop);
+        in.uuid(0x3A, drop);
+        in.uuid(0x42, drop);
+        in.varint(0x48, t.date);
+        uint64_t received = 0;
+        in.varint(0x50, received);
+        t.md_count = in.map(0x5A, t.md_first);
+        if (in.bad || in.p != e) bad = true;
+        p = e;
+    }
+};
+__device__ __forceinline__ bool en_fast_parse(const uint8_t *s, uint32_t total, EnAny &ev, uint32_t &asg_status) {
+    EnFast f{s, 0u, total, false};
+    if (f.at(0x0A)) {  // GDeviceEventContext
+        const uint32_t l = f.len();
+        if (f.bad) return false;
+        const uint32_t e = f.p + l;
+        EnFast c{s, f.p, e, false};
+        EnUuid drop{0u, 0ull, 0ull};
+        EnStr st{0u, 0u, 0u};
+        uint32_t first;
+        c.uuid(0x0A, drop);
+        c.uuid(0x12, drop);
+        c.uuid(0x1A, drop);
+        c.opt_str(0x22, st);
+        c.map(0x2A, first);
+        c.enum1(0x30, asg_status);
+        c.map(0x3A, first);
+        if (c.bad || c.p != e) return false;
+        f.p = e;
+    }
+    if (f.at(0x12)) {  // GAnyDeviceEvent: one member
+        const uint32_t l = f.len();
+        if (f.bad || f.p + l != total || l == 0) return false;
+        const uint32_t which = s[f.p] == 0x0A ? 1u : s[f.p] == 0x12 ? 2u : s[f.p] == 0x1A ? 3u : 0u;
+        if (!which) return false;  // (another event type, an unknown field: the general parser says what it is)
+        const uint32_t lm = f.len();
+        if (f.bad || f.p + lm != total) return false;
+        EnFast m{s, f.p, total, false};
+        ev.ocase = which;
+        if (which == 1) {
+            m.str(0x0A, ev.name_off, ev.name_len);
+            if (m.at(0x11) && m.p + 9 <= m.end) {
+                ev.value_bits = m.le64(m.p + 1);
+                m.p += 9;
+            }
+            m.event(0x1A, ev.ev);
+        } else if (which == 2) {
+            m.enum1(0x08, ev.source);
+            m.enum1(0x10, ev.level);
+            m.str(0x1A, ev.name_off, ev.name_len);
+            m.str(0x22, ev.msg_off, ev.msg_len);
+            m.event(0x2A, ev.ev);
+        } else {
+            m.opt_dbl(0x0A, ev.lat);
+            m.opt_dbl(0x12, ev.lon);
+            m.opt_dbl(0x1A, ev.elev);
+            m.event(0x22, ev.ev);
+        }
+        if (m.bad || m.p != total) return false;
+        f.p = total;
+    }
+    return f.p == total;
+}
+
 // key words of an enriched row: the assignment id's two words, then the name from the payload
 template <typename B>
 struct EnMgKey {
@@ -497,6 +708,45 @@ struct EnMgKey {
     }
 };
 
+__device__ __forceinline__ void en_write_row(const EnArgs &a, const uint64_t row, const EnRow &r) {
+    a.cols.meta[row] = r.meta;
+    a.cols.token_hash[row] = r.th;
+    a.cols.name_hash[row] = r.nh;
+    a.cols.event_date[row] = r.date;
+    a.cols.v0[row] = __longlong_as_double((long long)r.v0);
+    a.cols.v1[row] = __longlong_as_double((long long)r.v1);
+    a.cols.v2[row] = __longlong_as_double((long long)r.v2);
+    a.cols.token_span[row] = 0;
+    a.cols.name_span[row] = r.nspan;
+    if (a.cols.originator_span) a.cols.originator_span[row] = 0;
+    if (a.cols.message_span) a.cols.message_span[row] = r.mspan;
+    if (a.cols.metadata_span) a.cols.metadata_span[row] = r.mdspan;
+    if (a.cols.alternate_id_span) a.cols.alternate_id_span[row] = r.aspan;
+    if (a.ids.event_hi) {
+        a.ids.event_hi[row] = r.event_hi;
+        a.ids.event_lo[row] = r.event_lo;
+        a.ids.assignment_hi[row] = r.asg_hi;
+        a.ids.assignment_lo[row] = r.asg_lo;
+        a.ids.device_hi[row] = r.dev_hi;
+        a.ids.device_lo[row] = r.dev_lo;
+    }
+}
+// one decoded row into the device-state table (fused decode + merge); key = assignment id + name
+template <typename B>
+__device__ __forceinline__ void en_merge_row(const EnArgs &a, MgLocalCnt *cnt, const B &rec_bytes, const EnRow &r, uint32_t rec) {
+    const uint32_t kind = SWGPU_META_KIND(r.meta), fl = SWGPU_META_FLAGS(r.meta);
+    const uint32_t nl = kind == SWGPU_KIND_LOCATION ? 0u : SWGPU_SPAN_LEN(r.nspan);
+    if (nl > 0xffffu) {
+        atomicAdd(&a.mt.ctr->key_too_long, 1ull);
+        return;
+    }
+    const uint32_t kindbyte = mg_kindbyte(kind, fl);
+    const uint64_t h = mg_mix(r.th, kind == SWGPU_KIND_LOCATION ? 0ull : r.nh, kindbyte);
+    const uint64_t seq1 = a.seq_base + ((uint64_t)(a.rec_base + rec) << SWGPU_SEQ_RECORD_SHIFT) + 1;
+    EnMgKey<B> key{r.asg_hi, r.asg_lo, rec_bytes, SWGPU_SPAN_OFF(r.nspan), nl};
+    mg_upsert(a.mt, cnt, h, r.th, 16u, nl, kindbyte, key, seq1, r.event_hi, r.event_lo, (uint64_t)r.date, r.v0);
+}
+
 // MODE 0: optimistic pass, row index = record index (raises *not_dense when a record yields no row)
 // MODE 1: ordered redo (ticketed tiles + look-back), returns at once unless *not_dense
 // MODE 2: fused decode + merge (newest records first; no columns)
@@ -513,6 +763,13 @@ __device__ __forceinline__ void en_decode_tile(const EnArgs &a, const uint32_t t
         r0 = a.rec_off[rec0 + lane];
         r1 = a.rec_off[rec0 + lane + 1];
     }
+    // after the forward pass (enriched_fast_kernel) modes 0 and 2 decode only the records that one left
+    bool mine = lane < nrec;
+    if (MODE != 1 && a.fast) {
+        mine = mine && a.status[rec0 + lane] == EN_ST_PENDING;
+        if (!__any_sync(SW_FULL, mine)) return;
+    }
+    __syncwarp();  // (modes 0 and 2 walk tiles in a loop: every lane is done with the previous tile's bytes)
     const uint64_t b0 = __shfl_sync(SW_FULL, r0, 0);
     const uint64_t b1 = __shfl_sync(SW_FULL, r1, nrec ? nrec - 1 : 0);
     const uintptr_t addr = (uintptr_t)(a.bytes + b0);
@@ -529,7 +786,7 @@ __device__ __forceinline__ void en_decode_tile(const EnArgs &a, const uint32_t t
     EnRow r;
     r.status = 0;
     uint32_t count = 0;
-    if (lane < nrec) {
+    if (mine) {
         const uint64_t l64 = r1 - r0;
         const uint32_t len = l64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)l64;
         if (staged)
@@ -541,22 +798,10 @@ __device__ __forceinline__ void en_decode_tile(const EnArgs &a, const uint32_t t
     }
     if (MODE == 2) {
         if (count) {
-            const uint32_t kind = SWGPU_META_KIND(r.meta), fl = SWGPU_META_FLAGS(r.meta);
-            const uint32_t nl = kind == SWGPU_KIND_LOCATION ? 0u : SWGPU_SPAN_LEN(r.nspan);
-            if (nl > 0xffffu) {
-                atomicAdd(&a.mt.ctr->key_too_long, 1ull);
-            } else {
-                const uint32_t kindbyte = mg_kindbyte(kind, fl);
-                const uint64_t h = mg_mix(r.th, kind == SWGPU_KIND_LOCATION ? 0ull : r.nh, kindbyte);
-                const uint64_t seq1 = a.seq_base + ((uint64_t)(a.rec_base + rec0 + lane) << SWGPU_SEQ_RECORD_SHIFT) + 1;
-                if (staged) {
-                    EnMgKey<SmemBytes> key{r.asg_hi, r.asg_lo, SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, SWGPU_SPAN_OFF(r.nspan), nl};
-                    mg_upsert(a.mt, &s_cnt[warp], h, r.th, 16u, nl, kindbyte, key, seq1, r.event_hi, r.event_lo, (uint64_t)r.date, r.v0);
-                } else {
-                    EnMgKey<GmemBytes> key{r.asg_hi, r.asg_lo, GmemBytes{a.bytes + r0}, SWGPU_SPAN_OFF(r.nspan), nl};
-                    mg_upsert(a.mt, &s_cnt[warp], h, r.th, 16u, nl, kindbyte, key, seq1, r.event_hi, r.event_lo, (uint64_t)r.date, r.v0);
-                }
-            }
+            if (staged)
+                en_merge_row(a, &s_cnt[warp], SmemBytes{ws + lead + (uint32_t)(r0 - b0)}, r, rec0 + lane);
+            else
+                en_merge_row(a, &s_cnt[warp], GmemBytes{a.bytes + r0}, r, rec0 + lane);
         }
         __syncwarp();
         count = __reduce_add_sync(SW_FULL, count);
@@ -569,36 +814,14 @@ __device__ __forceinline__ void en_decode_tile(const EnArgs &a, const uint32_t t
     uint64_t tile_total = 0, row;
     if (MODE == 0) {
         row = (uint64_t)rec0 + lane;
-        if (lane < nrec && count != 1) atomicOr(a.not_dense, 1u);
+        if (mine && count != 1) atomicOr(a.not_dense, 1u);
     } else {
         row = sw_block_ordered_offset<EN_THREADS>(count, a.tile_state, tile, s_warp, &tile_total);
     }
     const uint64_t row_base = a.row_base ? (uint64_t)__ldg(a.row_base) : 0ull;
-    if (lane < nrec) {
+    if (mine) {
         a.first_row[rec0 + lane] = (uint32_t)(row_base + row);
-        if (count && row < a.max_rows) {
-            a.cols.meta[row] = r.meta;
-            a.cols.token_hash[row] = r.th;
-            a.cols.name_hash[row] = r.nh;
-            a.cols.event_date[row] = r.date;
-            a.cols.v0[row] = __longlong_as_double((long long)r.v0);
-            a.cols.v1[row] = __longlong_as_double((long long)r.v1);
-            a.cols.v2[row] = __longlong_as_double((long long)r.v2);
-            a.cols.token_span[row] = 0;
-            a.cols.name_span[row] = r.nspan;
-            if (a.cols.originator_span) a.cols.originator_span[row] = 0;
-            if (a.cols.message_span) a.cols.message_span[row] = r.mspan;
-            if (a.cols.metadata_span) a.cols.metadata_span[row] = r.mdspan;
-            if (a.cols.alternate_id_span) a.cols.alternate_id_span[row] = r.aspan;
-            if (a.ids.event_hi) {
-                a.ids.event_hi[row] = r.event_hi;
-                a.ids.event_lo[row] = r.event_lo;
-                a.ids.assignment_hi[row] = r.asg_hi;
-                a.ids.assignment_lo[row] = r.asg_lo;
-                a.ids.device_hi[row] = r.dev_hi;
-                a.ids.device_lo[row] = r.dev_lo;
-            }
-        }
+        if (count && row < a.max_rows) en_write_row(a, row, r);
     }
     if ((uint64_t)tile * EN_THREADS + EN_THREADS >= a.n && tid == 0) {  // the tile holding the last record
         const uint64_t total = MODE == 0 ? (uint64_t)a.n : row + tile_total;
@@ -608,24 +831,101 @@ __device__ __forceinline__ void en_decode_tile(const EnArgs &a, const uint32_t t
     }
 }
 
+// Forward pass (option "enriched.fast_path"): one warp per CTA (its staging goes back the moment its 32 records are
+// done), en_fast_parse on each record; MERGE = false: row index = record index as in the dense pass; MERGE = true: the
+// row goes straight into the device-state table, newest records first.  A record that is not in the serialiser's
+// layout is marked EN_ST_PENDING for the general pass that follows.  None of the general parser is in this kernel.
+template <bool MERGE>
+__global__ void __launch_bounds__(32) enriched_fast_kernel(EnArgs a) {
+    extern __shared__ __align__(16) uint8_t smem[];  // EN_WSTAGE + 32
+    __shared__ MgLocalCnt s_cnt[1];
+    const uint32_t lane = threadIdx.x;
+    const uint32_t tile = MERGE ? gridDim.x - 1 - blockIdx.x : blockIdx.x;
+    const uint64_t rec0_64 = (uint64_t)tile * 32;
+    const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
+    const uint32_t nrec = min(32u, a.n - rec0);
+    if (MERGE && lane == 0) s_cnt[0].keys = s_cnt[0].bytes = 0;
+    uint64_t r0 = 0, r1 = 0;
+    if (lane < nrec) {
+        r0 = a.rec_off[rec0 + lane];
+        r1 = a.rec_off[rec0 + lane + 1];
+    }
+    const uint64_t b0 = __shfl_sync(SW_FULL, r0, 0);
+    const uint64_t b1 = __shfl_sync(SW_FULL, r1, nrec ? nrec - 1 : 0);
+    const uintptr_t addr = (uintptr_t)(a.bytes + b0);
+    const uint32_t lead = (uint32_t)(addr & 15);
+    const uint64_t span = (uint64_t)lead + (b1 - b0);
+    const bool staged = span <= EN_WSTAGE;
+    if (staged && nrec) {
+        const uint4 *src = (const uint4 *)(addr - lead);
+        uint4 *dst = (uint4 *)smem;
+        const uint32_t nvec = (uint32_t)((span + 15) >> 4);
+        for (uint32_t i = lane; i < nvec; i += 32) dst[i] = sw_ld_stream_u4(src + i);
+    }
+    __syncwarp();
+    const uint64_t row_base = (!MERGE && a.row_base) ? (uint64_t)__ldg(a.row_base) : 0ull;
+    uint32_t ok = 0, left = 0;
+    if (lane < nrec) {
+        EnRow r;
+        memset(&r, 0, sizeof r);
+        bool hit = false;
+        const SmemBytes rb{smem + lead + (uint32_t)(r0 - b0)};
+        if (staged) {
+            EnAny ev;
+            memset(&ev, 0, sizeof ev);
+            uint32_t asg_status = 0;
+            hit = en_fast_parse(rb.s, (uint32_t)(r1 - r0), ev, asg_status);
+            if (hit) en_finish(rb, a.rec_base + rec0 + lane, ev, asg_status, r);
+        }
+        a.status[rec0 + lane] = hit ? (uint8_t)r.status : (uint8_t)EN_ST_PENDING;
+        left = hit ? 0u : 1u;
+        ok = hit && r.status == SWGPU_ST_OK ? 1u : 0u;
+        if (MERGE) {
+            if (ok) en_merge_row(a, &s_cnt[0], rb, r, rec0 + lane);
+        } else {
+            const uint64_t row = (uint64_t)rec0 + lane;
+            a.first_row[rec0 + lane] = (uint32_t)(row_base + row);
+            if (hit && !ok) atomicOr(a.not_dense, 1u);  // decoded here, to no row: the ordered pass will place the rows
+            if (ok && row < a.max_rows) en_write_row(a, row, r);
+        }
+    }
+    __syncwarp();
+    left = __reduce_add_sync(SW_FULL, left);
+    if (MERGE) {
+        ok = __reduce_add_sync(SW_FULL, ok);
+        if (lane == 0) {
+            if (ok) atomicAdd(a.out_rows, ok);
+            mg_flush_counts(a.mt, &s_cnt[0]);
+        }
+    } else if ((uint64_t)tile * 32 + 32 >= a.n && lane == 0) {  // the tile holding the last record
+        a.first_row[a.n] = (uint32_t)(row_base + a.n);
+        *a.out_rows = a.n;
+        if (a.row_next) *a.row_next = (uint32_t)(row_base + a.n);
+    }
+    if (lane == 0 && left) atomicOr(a.pending, 1u);
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(EN_THREADS) enriched_decode_kernel(EnArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];  // EN_WARPS * (EN_WSTAGE + 32)
     __shared__ uint64_t s_warp[EN_THREADS / 32 + 2];
     __shared__ MgLocalCnt s_cnt[EN_WARPS];
     __shared__ uint32_t s_tile;
+    const uint32_t ntiles = (uint32_t)(((uint64_t)a.n + EN_THREADS - 1) / EN_THREADS);
     if (MODE == 0) {
-        en_decode_tile<0>(a, blockIdx.x, smem, s_warp, s_cnt);
+        if (a.fast && __ldg(a.pending) == 0) return;  // the forward pass took every record
+        for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) en_decode_tile<0>(a, t, smem, s_warp, s_cnt);
         return;
     }
     if (MODE == 2) {
+        if (a.fast && __ldg(a.pending) == 0) return;
         if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5].keys = s_cnt[threadIdx.x >> 5].bytes = 0;
         __syncwarp();
-        en_decode_tile<2>(a, gridDim.x - 1 - blockIdx.x, smem, s_warp, s_cnt);  // newest records first
+        for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x)
+            en_decode_tile<2>(a, ntiles - 1 - t, smem, s_warp, s_cnt);  // newest records first
         return;
     }
     if (__ldg(a.not_dense) == 0) return;
-    const uint32_t ntiles = (uint32_t)(((uint64_t)a.n + EN_THREADS - 1) / EN_THREADS);
     for (;;) {
         if (threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u);
         __syncthreads();
@@ -646,6 +946,8 @@ static int en_attr(swgpu_ctx *ctx) {
         SW_CUDA(ctx, cudaFuncSetAttribute(enriched_decode_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         SW_CUDA(ctx, cudaFuncSetAttribute(enriched_decode_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         SW_CUDA(ctx, cudaFuncSetAttribute(enriched_decode_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        SW_CUDA(ctx, cudaFuncSetAttribute(enriched_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, EN_WSTAGE + 32));
+        SW_CUDA(ctx, cudaFuncSetAttribute(enriched_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, EN_WSTAGE + 32));
         done[d] = true;
     }
     return SWGPU_OK;
@@ -698,9 +1000,15 @@ int sw_decode_enriched_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64
     a.not_dense = (uint32_t *)ctx->scratch + 1;
     if (int rc = en_attr(ctx)) return rc;
     const int smem = EN_WARPS * (EN_WSTAGE + 32);
-    enriched_decode_kernel<0><<<ntiles, EN_THREADS, smem, ctx->stream>>>(a);
-    SW_CUDA(ctx, cudaGetLastError());
     const uint32_t nredo = ntiles < (uint32_t)ctx->sm_count * 4u ? ntiles : (uint32_t)ctx->sm_count * 4u;
+    a.fast = ctx->opt_enriched_fast;
+    a.pending = (uint32_t *)ctx->scratch + 3;
+    if (a.fast) {
+        enriched_fast_kernel<false><<<(n + 31) / 32, 32, EN_WSTAGE + 32, ctx->stream>>>(a);
+        SW_CUDA(ctx, cudaGetLastError());
+    }
+    enriched_decode_kernel<0><<<a.fast ? nredo : ntiles, EN_THREADS, smem, ctx->stream>>>(a);
+    SW_CUDA(ctx, cudaGetLastError());
     enriched_decode_kernel<1><<<nredo, EN_THREADS, smem, ctx->stream>>>(a);
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
@@ -719,7 +1027,17 @@ int sw_decode_merge_enriched_launch(swgpu_ctx *ctx, const uint8_t *bytes, const 
     a.seq_base = seq_base;
     if (int rc = en_attr(ctx)) return rc;
     const int smem = EN_WARPS * (EN_WSTAGE + 32);
-    enriched_decode_kernel<2><<<(n + EN_THREADS - 1) / EN_THREADS, EN_THREADS, smem, ctx->stream>>>(a);
+    const uint32_t ntiles = (n + EN_THREADS - 1) / EN_THREADS;
+    a.fast = ctx->opt_enriched_fast;
+    if (a.fast) {
+        if (int rc = sw_ensure_scratch(ctx, SW_SCRATCH_HDR)) return rc;
+        a.pending = (uint32_t *)ctx->scratch + 3;
+        SW_CUDA(ctx, cudaMemsetAsync(a.pending, 0, sizeof(uint32_t), ctx->stream));
+        enriched_fast_kernel<true><<<(n + 31) / 32, 32, EN_WSTAGE + 32, ctx->stream>>>(a);
+        SW_CUDA(ctx, cudaGetLastError());
+    }
+    const uint32_t ngen = a.fast ? std::min<uint32_t>(ntiles, (uint32_t)ctx->sm_count * 4u) : ntiles;
+    enriched_decode_kernel<2><<<ngen, EN_THREADS, smem, ctx->stream>>>(a);
     SW_CUDA(ctx, cudaGetLastError());
     return SWGPU_OK;
 }

@@ -52,6 +52,7 @@ struct swgpu_ctx {
     uint32_t opt_zone_force_ray = 0;        // "zone.force_ray": 0 = choose per point, 1..4 = +x, -x, +y, -y (tests)
     uint32_t opt_zone_scan_sequential = 0;  // "zone.scan_sequential": 1 = single-CTA scan of the tile totals (tests)
     uint64_t opt_presence_now1 = 0;         // "state.presence_now_ms" + 1: folded events touch their device's presence row
+    uint32_t opt_enriched_fast = 1;         // "enriched.fast_path": 0 = every enriched record takes the general parser (tests)
     uint32_t opt_json_fast = 1;             // "json.fast_path": 0 = no template recogniser, every record takes the general pass (tests)
     uint32_t opt_json_stats = 0;            // "json.stats": 1 = count the records the template recogniser takes
     uint32_t opt_zone_stats = 0;            // "zone.stats": 1 = count cell / edge records and straddle tests

@@ -196,6 +196,67 @@ def pb_locations(n: int, n_devices: int, lon: np.ndarray, lat: np.ndarray, seed:
     return rec.reshape(-1), rec_off, dict(dev=dev, lat=lat, lon=lon, elev=elev, date=date)
 
 
+def enriched_locations(n: int, n_assignments: int, lon: np.ndarray, lat: np.ndarray, seed: int, date0=EVENT_DATE_BASE):
+    """n serialised ``GEnrichedEventPayload`` records holding a location event (159 B each), as the
+    ``inbound-enriched-events`` topic carries them (device-event-model.proto:139-150, 171-176, 204-213, 288-296,
+    321-324): context {deviceId, deviceTypeId, assignmentStatus = ACTIVE}, event.location {latitude, longitude,
+    elevation, event {id, eventType = LOCATION, deviceId, deviceAssignmentId, eventDate, receivedDate}}.  Event
+    dates must lie in [2^35, 2^42) ms (six-byte varints).  Returns bytes, rec_off, truth dict."""
+    rng = np.random.default_rng(seed)
+    asg = rng.integers(0, n_assignments, size=n).astype(np.uint64)
+    elev = np.round(rng.uniform(0, 500, size=n), 1)
+    date = (date0 + np.arange(n, dtype=np.int64)).astype(np.uint64)
+    assert int(date.min()) >= 1 << 35 and int(date.max()) < 1 << 42
+    ev_id = np.arange(n, dtype=np.uint64) + np.uint64(seed) * np.uint64(1 << 40)
+
+    def guuid(rec, at, tag, msb, lsb):       # tag 0x12 (len 18): 09 msb(fixed64) 11 lsb(fixed64)
+        rec[:, at:at + 2] = (tag, 18)
+        rec[:, at + 2] = 0x09
+        rec[:, at + 3:at + 11] = _u64_bytes(msb)
+        rec[:, at + 11] = 0x11
+        rec[:, at + 12:at + 20] = _u64_bytes(lsb)
+        return at + 20
+
+    def optd(rec, at, tag, v):                # GOptionalDouble{value}: tag 09 09 f64  (values are never 0.0 here)
+        rec[:, at:at + 3] = (tag, 9, 0x09)
+        rec[:, at + 3:at + 11] = _f64_bytes(v)
+        return at + 11
+
+    def varint6(rec, at, tag, v):
+        rec[:, at] = tag
+        for k in range(6):
+            rec[:, at + 1 + k] = ((v >> np.uint64(7 * k)) & np.uint64(0x7f)).astype(np.uint8) | (0x80 if k < 5 else 0)
+        return at + 7
+    L = 159
+    rec = np.empty((n, L), dtype=np.uint8)
+    one = np.ones(n, dtype=np.uint64)
+    rec[:, 0:2] = (0x0A, 42)                 # context
+    at = guuid(rec, 2, 0x0A, asg * np.uint64(3) + one, asg)               # deviceId
+    at = guuid(rec, at, 0x12, one * np.uint64(77), one * np.uint64(78))   # deviceTypeId
+    rec[:, at:at + 2] = (0x30, 1)            # assignmentStatus = ACTIVE
+    at += 2
+    rec[:, at:at + 2] = (0x12, 113)          # event (GAnyDeviceEvent)
+    rec[:, at + 2:at + 4] = (0x1A, 111)      # location
+    at += 4
+    lat_ = np.where(np.asarray(lat) == 0.0, 1e-9, lat)
+    lon_ = np.where(np.asarray(lon) == 0.0, 1e-9, lon)
+    at = optd(rec, at, 0x0A, lat_)
+    at = optd(rec, at, 0x12, lon_)
+    at = optd(rec, at, 0x1A, np.where(elev == 0.0, 0.5, elev))
+    rec[:, at:at + 2] = (0x22, 76)           # GDeviceEvent
+    at += 2
+    at = guuid(rec, at, 0x0A, ev_id, ev_id ^ np.uint64(0x5555))           # id
+    rec[:, at:at + 2] = (0x18, 1)            # eventType = EVENT_TYPE_LOCATION
+    at += 2
+    at = guuid(rec, at, 0x22, asg * np.uint64(3) + one, asg)              # deviceId
+    at = guuid(rec, at, 0x2A, asg + np.uint64(1 << 32), asg * np.uint64(0x9E3779B1) + one)   # deviceAssignmentId
+    at = varint6(rec, at, 0x48, date)        # eventDate
+    at = varint6(rec, at, 0x50, date + np.uint64(5))                      # receivedDate
+    assert at == L, at
+    rec_off = (np.arange(n + 1, dtype=np.uint64) * L)
+    return rec.reshape(-1), rec_off, dict(assignment=asg, lat=lat_, lon=lon_, date=date.astype(np.int64), event_id=ev_id)
+
+
 def _ragged_from_groups(n, group_id, templates):
     """Assemble n variable-length records where record i is built from templates[group_id[i]]
     (a function (idx) -> uint8[len(idx), L_g])."""

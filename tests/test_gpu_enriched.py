@@ -133,3 +133,46 @@ def test_zone_test_and_state_merge_on_enriched_events(ctx):
     ctx.state_restore(snap)
     snap_equal(ctx.state_snapshot(), st.snapshot())
     ctx.state_clear()
+
+
+def test_forward_pass_equals_general_pass(ctx):
+    """the forward pass over the serialiser's own field order (option enriched.fast_path, default on) and the general
+    proto3 parser must give identical results: serialised payloads (taken by the forward pass), the same concatenated
+    (fields twice: merge), damaged, with multi-byte lengths and non-ASCII strings, and the bench generator's records"""
+    rnd = random.Random(17)
+    base = [E.random_payload(rnd, kinds=(1, 2, 3, 6)).SerializeToString() for _ in range(3000)]
+    lon, lat = S.locations_for_zones(4000, *S.star_zones(4)[:3], seed=6)
+    gd, goff, truth = S.enriched_locations(4000, 100, lon, lat, seed=6)
+    graw = gd.tobytes()
+    recs = base + [rnd.choice(base) + rnd.choice(base) for _ in range(1000)] + _damage(rnd, base[:300], 8000)
+    recs += [graw[int(goff[i]): int(goff[i + 1])] for i in range(4000)]
+    C = E.classes()
+    for k in range(100):
+        p = C["GEnrichedEventPayload"]()
+        p.context.deviceStatus.value = "status" * (k % 30)
+        for j in range(k % 5):
+            p.context.deviceMetadata["k%d" % j] = "v" * (40 * j)
+        p.context.assignmentStatus = k % 4
+        p.event.measurement.name = ("n" * (k % 200)) if k % 7 else "é"
+        p.event.measurement.value = float(k) - 3.5
+        p.event.measurement.event.eventDate = k * 1_000_003
+        p.event.measurement.event.deviceAssignmentId.lsb = k
+        recs.append(p.SerializeToString())
+    rnd.shuffle(recs)
+    _, _, (data, rec_off, ocols, oids, total) = _check(ctx, recs)          # forward pass + general pass vs oracle
+    fast, fids = ctx.decode_enriched(data, rec_off)
+    ctx.set_option("enriched.fast_path", 0)
+    try:
+        slow, sids = ctx.decode_enriched(data, rec_off)
+        _check(ctx, recs)                                                   # general pass alone vs oracle
+    finally:
+        ctx.set_option("enriched.fast_path", 1)
+    assert fast.n_rows == slow.n_rows and np.array_equal(fast.status, slow.status) and np.array_equal(fast.first_row, slow.first_row)
+    assert_cols_equal(fast.cols, slow.cols, fast.n_rows)
+    for k in L.ID_NAMES:
+        assert np.array_equal(fids[k], sids[k]), k
+    # the generator's records decode to the generator's truth
+    d2, o2 = S.pack_records([graw[int(goff[i]): int(goff[i + 1])] for i in range(4000)])
+    res, ids = ctx.decode_enriched(d2, o2)
+    assert res.n_rows == 4000 and np.array_equal(res.cols.v0[:4000], truth["lat"]) and np.array_equal(res.cols.v1[:4000], truth["lon"])
+    assert np.array_equal(res.cols.event_date[:4000], truth["date"]) and np.array_equal(ids["event_hi"], truth["event_id"])
