@@ -16,7 +16,7 @@ NVCC_FLAGS = [
     "--expt-relaxed-constexpr", "--extended-lambda",
     "-Xcompiler", "-fPIC,-O2,-ffp-contract=off",
     "-Xptxas", "-v", "--fmad=false",
-] + os.environ.get("SWGPU_NVCC_EXTRA", "").split()   # e.g. -DSWGPU_DEBUG_BOUNDS for an instrumented build
+] + os.environ.get("SWGPU_NVCC_EXTRA", "").split()   # extra flags for experiment builds (e.g. -DPB_MIN_CTAS=2)
 
 
 def nvcc() -> str:

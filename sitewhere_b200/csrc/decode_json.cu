@@ -20,6 +20,7 @@
 #define JS_THREADS 128
 #define JS_WARPS (JS_THREADS / 32)
 #define JS_AHEAD 4096         // template pass: warp tiles between an L2 prefetch and its use (about one wave of resident warps)
+#define JS_SLACK 64            // bytes after a warp's stage: the template's word-wise reads run up to 36 bytes past a record's end
 #define JS_WSTAGE (8 * 1024)  // bytes staged per warp tile: 32 records of up to 256 B on average (more CTAs per SM than 12 KiB)
 #define JS_MAX_DEPTH 256
 
@@ -1344,7 +1345,7 @@ __device__ __forceinline__ void json_decode_tile(const JsArgs &a, const uint32_t
     const uint64_t rec0_64 = (uint64_t)tile * JS_THREADS + warp * 32;
     const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
     const uint32_t nrec = min(32u, a.n - rec0);
-    uint8_t *ws = smem + warp * (JS_WSTAGE + 32);
+    uint8_t *ws = smem + warp * (JS_WSTAGE + JS_SLACK);
     uint64_t r0 = 0, r1 = 0;
     if (lane < nrec) {
         r0 = a.rec_off[rec0 + lane];
@@ -1407,12 +1408,12 @@ __device__ __forceinline__ void json_decode_tile(const JsArgs &a, const uint32_t
 // serialiser's layout is decoded here, every other one is marked JS_ST_PENDING for the dense pass that follows.
 // Nothing of the general parser is in this kernel: it stays small enough for the instruction cache.
 __global__ void __launch_bounds__(JS_THREADS) json_template_kernel(JsArgs a) {
-    extern __shared__ __align__(16) uint8_t smem[];  // (JS_WSTAGE + 32) per warp of the CTA
+    extern __shared__ __align__(16) uint8_t smem[];  // (JS_WSTAGE + JS_SLACK) per warp of the CTA
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint64_t rec0_64 = (uint64_t)blockIdx.x * blockDim.x + warp * 32;
     const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
     const uint32_t nrec = min(32u, a.n - rec0);
-    uint8_t *ws = smem + warp * (JS_WSTAGE + 32);
+    uint8_t *ws = smem + warp * (JS_WSTAGE + JS_SLACK);
     uint64_t r0 = 0, r1 = 0;
     if (lane < nrec) {
         r0 = a.rec_off[rec0 + lane];
@@ -1474,7 +1475,7 @@ __global__ void __launch_bounds__(JS_THREADS) json_template_kernel(JsArgs a) {
 // (Same scheme as pb_decode_kernel.)
 template <bool DENSE>
 __global__ void __launch_bounds__(JS_THREADS) json_decode_kernel(JsArgs a) {
-    extern __shared__ __align__(16) uint8_t smem[];  // JS_WARPS * (JS_WSTAGE + 32)
+    extern __shared__ __align__(16) uint8_t smem[];  // JS_WARPS * (JS_WSTAGE + JS_SLACK)
     __shared__ uint64_t s_warp[JS_THREADS / 32 + 2];
     __shared__ uint32_t s_tile;
     if (DENSE) {
@@ -1498,7 +1499,7 @@ __global__ void __launch_bounds__(JS_THREADS) json_decode_kernel(JsArgs a) {
 // ---- fused decode + merge: the same staging and record decode, the row goes straight into the device-state
 // table (merge_table.cuh) with sequence number seq_base + (record << SWGPU_SEQ_RECORD_SHIFT); no columns.
 __global__ void __launch_bounds__(JS_THREADS) json_decode_merge_kernel(JsArgs a) {
-    extern __shared__ __align__(16) uint8_t smem[];  // JS_WARPS * (JS_WSTAGE + 32)
+    extern __shared__ __align__(16) uint8_t smem[];  // JS_WARPS * (JS_WSTAGE + JS_SLACK)
     __shared__ MgLocalCnt s_cnt[JS_WARPS];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (lane == 0) s_cnt[warp].keys = s_cnt[warp].bytes = 0;
@@ -1506,7 +1507,7 @@ __global__ void __launch_bounds__(JS_THREADS) json_decode_merge_kernel(JsArgs a)
     const uint64_t rec0_64 = (uint64_t)(gridDim.x - 1 - blockIdx.x) * JS_THREADS + (JS_WARPS - 1 - warp) * 32;
     const uint32_t rec0 = rec0_64 < a.n ? (uint32_t)rec0_64 : a.n;
     const uint32_t nrec = min(32u, a.n - rec0);
-    uint8_t *ws = smem + warp * (JS_WSTAGE + 32);
+    uint8_t *ws = smem + warp * (JS_WSTAGE + JS_SLACK);
     uint64_t r0 = 0, r1 = 0;
     if (lane < nrec) {
         r0 = a.rec_off[rec0 + lane];
@@ -1579,7 +1580,7 @@ int sw_decode_merge_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint
     a.id_lo = id_lo;
     a.seq_base = seq_base;
     a.fast = ctx->opt_json_fast;
-    const int smem = JS_WARPS * (JS_WSTAGE + 32);
+    const int smem = JS_WARPS * (JS_WSTAGE + JS_SLACK);
     {
         static std::mutex mu;
         static bool done[64] = {false};
@@ -1640,7 +1641,7 @@ int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *
     a.fast = ctx->opt_json_fast;
     a.pending = (uint32_t *)ctx->scratch + 3;
     a.hits = ctx->opt_json_stats ? (uint32_t *)ctx->scratch + 2 : nullptr;
-    const int smem = JS_WARPS * (JS_WSTAGE + 32);
+    const int smem = JS_WARPS * (JS_WSTAGE + JS_SLACK);
     {
         // per device, once: the attribute is a property of the loaded function
         static std::mutex mu;
@@ -1657,7 +1658,7 @@ int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *
     if (a.fast) {
         // one warp per CTA: a CTA's shared memory goes back the moment its 32 records are done (measured: 27 resident
         // warps per SM against 17 with four-warp CTAs, 0.114 -> 0.105 ms per 1 M records)
-        json_template_kernel<<<(n + 31) / 32, 32, JS_WSTAGE + 32, ctx->stream>>>(a);  // the serialiser's layout
+        json_template_kernel<<<(n + 31) / 32, 32, JS_WSTAGE + JS_SLACK, ctx->stream>>>(a);  // the serialiser's layout
         SW_CUDA(ctx, cudaGetLastError());
     }
     const uint32_t nredo = ntiles < (uint32_t)ctx->sm_count * 4u ? ntiles : (uint32_t)ctx->sm_count * 4u;

@@ -210,3 +210,25 @@ def test_fast_structural_pass_equals_general_pass(ctx):
     assert_cols_equal(fast.cols, slow.cols, fast.n_rows)
     check_decode_parity(fast, data, rec_off, fn="decode_json")
     assert (fast.status == 0).sum() > 7000
+
+
+def test_template_reads_at_the_end_of_a_full_staging_tile(ctx):
+    """a warp tile whose bytes fill the 8 KiB stage exactly, its last record cut inside the device token: the
+    template's four-byte reads run past the record's end into the stage's slack, never out of the CTA's shared
+    memory, and the record is left to the general pass (a decode exception, as in the oracle)"""
+    canon = S.json_measurement(S.token_str(7), "fuel.level", "12.5", S.EVENT_DATE_BASE)
+    for tile_bytes in (8192, 8191, 8176, 8160):
+        recs = []
+        for rep in range(3):                      # three such tiles one after another (16-byte aligned starts)
+            body = [canon] * 31
+            used = sum(len(r) for r in body)
+            pad = tile_bytes - used
+            assert pad > 20
+            last = (b'{"deviceToken":"' + b"x" * pad)[:pad]
+            recs += body + [last]
+            if tile_bytes % 16:
+                recs[-1] = recs[-1] + b"y" * (16 - tile_bytes % 16) if rep < 2 else recs[-1]
+        data, rec_off = S.pack_records(recs)
+        res = ctx.decode_json(data, rec_off)
+        check_decode_parity(res, data, rec_off, fn="decode_json")
+        assert int((res.status == 0).sum()) == 93
