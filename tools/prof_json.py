@@ -8,6 +8,19 @@ dev = torch.device("cuda", 0)
 stream = torch.cuda.Stream(device=dev)
 ctx = sw.Context(0, stream=stream.cuda_stream)
 data, rec_off, _ = S.json_measurements(200_000, 50_000, seed=5)
+if len(sys.argv) > 1 and sys.argv[1] == "shuffled":     # the same requests in another member order, ", " / ": " separators
+    import json, random
+    rnd = random.Random(3)
+    raw = data.tobytes()
+    recs = []
+    for i in range(200_000):
+        o = json.loads(raw[int(rec_off[i]): int(rec_off[i + 1])], parse_float=lambda t: t)
+        req = list(o["request"].items()); rnd.shuffle(req)
+        top = list(o.items()); rnd.shuffle(top)
+        def dump(items):
+            return "{" + ", ".join(json.dumps(k) + ": " + (dump(req) if k == "request" else (v if isinstance(v, str) and k == "value" else json.dumps(v))) for k, v in items) + "}"
+        recs.append(dump(top).encode())
+    data, rec_off = S.pack_records(recs)
 lens = np.diff(rec_off.astype(np.int64)); data = np.tile(data, 5)
 rec_off = np.concatenate([[0], np.cumsum(np.tile(lens, 5))]).astype(np.uint64)
 n = rec_off.shape[0] - 1
