@@ -82,6 +82,54 @@ while time.time() < t_end:
         assert np.array_equal(a[k], b[k]), "state mismatch %s round %d seed %d" % (k, rnd, seed)
     assert np.array_equal(a["value"].view(np.uint64), b["value"].view(np.uint64))
     tot["merge"] = tot.get("merge", 0) + ototal
+    # enriched payloads: serialised (forward pass), concatenated (merge semantics) and damaged (general parser)
+    import random as _random
+    from tests import enriched_proto as EP
+    from tests.test_gpu_enriched import _damage
+    from sitewhere_b200 import _lib as L
+    prnd = _random.Random(seed + rnd)
+    ebase = [EP.random_payload(prnd, kinds=(1, 2, 3, 6)).SerializeToString() for _ in range(1500)]
+    erecs = ebase + [prnd.choice(ebase) + prnd.choice(ebase) for _ in range(500)] + _damage(prnd, ebase[:300], 6000)
+    prnd.shuffle(erecs)
+    data, off = S.pack_records(erecs)
+    res, ids = ctx.decode_enriched(data, off)
+    ocols, oids, ostatus, ofirst, ototal = oracle.decode_enriched(data, off)
+    assert res.n_rows == ototal and np.array_equal(res.status, ostatus) and np.array_equal(res.first_row, ofirst), "enriched %d %d" % (rnd, seed)
+    from tests.helpers import assert_cols_equal
+    assert_cols_equal(res.cols, ocols, ototal)
+    for k in L.ID_NAMES:
+        assert np.array_equal(ids[k], getattr(oids, k)[:ototal]), k
+    tot["enriched"] = tot.get("enriched", 0) + len(erecs)
+    # outbound encode of the rows of a mutated batch (device buffers)
+    import torch
+    for fmt, base, spec in (("pb", pb_base, F.PB_SPECIALS), ("json", js_base, F.JSON_SPECIALS)):
+        recs = F._mutate(rng, base, spec, 8000, max_mut=1) + list(base[:500])
+        data, off = S.pack_records(recs)
+        ocols, ostatus, ofirst, ototal = getattr(oracle, "decode_" + fmt)(data, off)
+        want, woff, wst = oracle.encode_inbound(fmt, data, off, ocols, ototal, b"soak", 1_700_000_000_000)
+        dev = torch.device("cuda", 0)
+        n = off.shape[0] - 1
+        d_bytes = torch.zeros(data.shape[0] + 64, dtype=torch.uint8, device=dev)
+        d_bytes[: data.shape[0]].copy_(torch.from_numpy(data))
+        d_off = torch.from_numpy(off.view(np.int64)).to(dev)
+        cap = max(ototal, n, 1)
+        cols = sw.DeviceCols(cap, dev, optional=True)
+        d_st = torch.zeros(max(n, 1), dtype=torch.uint8, device=dev)
+        d_first = torch.zeros(n + 1, dtype=torch.int32, device=dev)
+        d_rows = torch.zeros(1, dtype=torch.int32, device=dev)
+        torch.cuda.synchronize()
+        getattr(ctx, "decode_%s_dev" % fmt)(d_bytes, d_off, n, cols, d_st, d_first, d_rows)
+        d_out = torch.zeros(want.shape[0] + 16, dtype=torch.uint8, device=dev)
+        d_ooff = torch.zeros(cap + 1, dtype=torch.int64, device=dev)
+        d_est = torch.zeros(cap, dtype=torch.uint8, device=dev)
+        d_tot = torch.zeros(1, dtype=torch.int64, device=dev)
+        ctx.encode_inbound_dev(fmt, d_bytes, d_off, cols, cap, d_rows, b"soak", 1_700_000_000_000, d_out, d_ooff, d_est, d_tot)
+        ctx.sync() if hasattr(ctx, "sync") else None
+        torch.cuda.synchronize()
+        assert int(d_tot.item()) == want.shape[0], "encode size %s %d %d" % (fmt, rnd, seed)
+        assert np.array_equal(d_est.cpu().numpy()[:ototal], wst) and np.array_equal(d_out.cpu().numpy()[: want.shape[0]], want), "encode %s %d %d" % (fmt, rnd, seed)
+        assert np.array_equal(d_ooff.cpu().numpy().view(np.uint64)[: ototal + 1], woff)
+        tot["encode"] = tot.get("encode", 0) + ototal
     rnd += 1
     print("round", rnd, tot, flush=True)
 print("soak ok: seed", seed, "rounds", rnd, tot)
