@@ -67,6 +67,14 @@ public final class SwGpu {
     static final MethodHandle WAIT = h("swgpu_wait", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG));
     static final MethodHandle PRESENCE_SCAN = h("swgpu_presence_scan", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG,
 	    JAVA_LONG, JAVA_LONG, JAVA_LONG, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
+    /** device-buffer forms, for callers that stage their own buffers (pointers are CUdeviceptr values) */
+    static final MethodHandle DECODE_ZONE_TEST_DEV = h("swgpu_decode_zone_test_dev",
+	    FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS, ADDRESS,
+		    ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS));
+    /** the GInboundEventPayload bytes of every decoded row (EventSourcesManager.handleDecodedEvent's marshal step) */
+    static final MethodHandle ENCODE_INBOUND_DEV = h("swgpu_encode_inbound_dev",
+	    FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, JAVA_INT, ADDRESS, ADDRESS, JAVA_INT,
+		    JAVA_LONG, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, ADDRESS));
     static final MethodHandle PARTITION = h("swgpu_partition", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_INT));
 
     /** One native context: one GPU, one calling thread. */
