@@ -264,6 +264,30 @@ int32_t swgpu_zone_stats(swgpu_ctx *ctx, uint64_t out[4]);
  * the ordered second pass ran.  Waits for the context's stream.                                            */
 int32_t swgpu_json_stats(swgpu_ctx *ctx, uint64_t out[2]);
 
+/* ---- alternate-id set --------------------------------------------------
+ * AlternateIdDeduplicator.isDuplicate (ES/deduplicator/AlternateIdDeduplicator.java:42-57) asks the event
+ * store, for every decoded request with an alternateId, whether an event with that id exists.  The context
+ * keeps the set of alternate ids it has been shown (bytes decide, hashes only pick the bucket); for each decoded
+ * row, in row order:                                                                                       */
+#define SWGPU_DEDUP_NEW 0  /* no alternate id, or an id the set did not hold: it is in the set now          */
+#define SWGPU_DEDUP_SEEN 1 /* the id was shown before: by an earlier call or by an earlier row of this one  */
+#define SWGPU_DEDUP_ASK 2  /* the span's bytes are not the id's characters (JSON escapes, a coerced token),
+                            * the id is longer than SWGPU_DEDUP_MAX_ID_BYTES, or it found no room: the store
+                            * decides, as in the reference                                                   */
+#define SWGPU_DEDUP_MAX_ID_BYTES 72u /* (a UUID string is 36) */
+/* SEEN is the reference's "duplicate" whenever every id the set holds is an id of a stored event; NEW is
+ * authoritative only for a set that was seeded with the store's ids (probe them once: any batch whose rows
+ * carry them) — otherwise the caller still asks the store for NEW rows and saves the round trip for SEEN ones.
+ * meta / alternate_id_span: the decoded columns over the same bytes / rec_off.  Asynchronous on the context's
+ * stream.  swgpu_dedup_reserve sizes the set beforehand (it grows by itself otherwise), swgpu_dedup_size reads
+ * the number of distinct ids (waits for the stream), swgpu_dedup_clear empties it.                           */
+int32_t swgpu_dedup_probe_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, const uint64_t *meta,
+                              const uint64_t *alternate_id_span, uint32_t n_rows, const uint32_t *n_rows_dev,
+                              uint8_t *dup);
+int32_t swgpu_dedup_reserve(swgpu_ctx *ctx, uint64_t max_ids);
+int32_t swgpu_dedup_size(swgpu_ctx *ctx, uint64_t *n_ids);
+int32_t swgpu_dedup_clear(swgpu_ctx *ctx);
+
 /* ---- outbound payload -------------------------------------------------
  * The GInboundEventPayload every decoded request is forwarded as, built on the device from the decoded rows.
  * Replaces, per decoded request, EventSourcesManager.handleDecodedEvent's

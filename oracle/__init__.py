@@ -343,3 +343,36 @@ class State:
                                             ("seq", "id_hi", "id_lo", "event_date", "value", "key_off", "key_bytes")])
         out["key_bytes"] = out["key_bytes"][: int(kb.value)]
         return out
+
+
+class AltIdSet:
+    """CPU restatement of the alternate-id probe (test infrastructure only).  Reference:
+    AlternateIdDeduplicator.isDuplicate, service-event-sources/.../deduplicator/AlternateIdDeduplicator.java:42-57 — a
+    request with an alternateId is a duplicate when the event store already holds an event with that id.  Restated as
+    the set of ids shown so far, walked in row order (a plain Python loop: small cases only): 0 = new (or no id),
+    1 = seen before, 2 = ask the store: the span's bytes are not the id's characters (escapes / coerced token), or the
+    id is longer than the 72 bytes the device set keeps."""
+
+    def __init__(self):
+        self.seen = set()
+
+    def probe(self, data, rec_off, cols, total):
+        data = _u8(data)
+        out = np.zeros(total, dtype=np.uint8)
+        for i in range(total):
+            m = int(cols.meta[i])
+            fl = (m >> 8) & 0xffff
+            if not fl & (1 << 4):            # SWGPU_F_HAS_ALT_ID
+                continue
+            sp = int(cols.alternate_id_span[i])
+            off, ln = sp & 0xffffffff, sp >> 32
+            if fl & ((1 << 9) | (1 << 12)) or ln > 72:    # SWGPU_F_STR_ESCAPED, SWGPU_F_NAME_COERCED; SWGPU_DEDUP_MAX_ID_BYTES
+                out[i] = 2
+                continue
+            base = int(rec_off[m >> 32])
+            key = bytes(data[base + off: base + off + ln])
+            if key in self.seen:
+                out[i] = 1
+            else:
+                self.seen.add(key)
+        return out

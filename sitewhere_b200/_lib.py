@@ -87,6 +87,10 @@ SIGNATURES = {
     "swgpu_zone_stats": (_I32, [_P, _P]),
     "swgpu_json_stats": (_I32, [_P, _P]),
     "swgpu_decode_zone_test": (_I32, [_P, _I32, _P, _P, _U32, _U32, _COLS, _P, _P, _P, _U64, _P, _P, _U32]),
+    "swgpu_dedup_probe_dev": (_I32, [_P, _P, _P, _P, _P, _U32, _P, _P]),
+    "swgpu_dedup_reserve": (_I32, [_P, _U64]),
+    "swgpu_dedup_size": (_I32, [_P, _P]),
+    "swgpu_dedup_clear": (_I32, [_P]),
     "swgpu_encode_inbound_dev": (_I32, [_P, _I32, _P, _P, _COLS, _U32, _P, _P, _U32, C.c_int64, _P, _U64, _P, _P, _P]),
     "swgpu_decode_zone_test_dev": (_I32, [_P, _I32, _P, _P, _U32, _U32, _COLS, _P, _P, _P, _U64, _P, _P]),
     "swgpu_reserve_batch": (_I32, [_P, _U32, _U64]),

@@ -278,6 +278,23 @@ class Context:
             cols.capacity, C.byref(s), status_t.data_ptr(), first_row_t.data_ptr(), n_rows_t.data_ptr(), pairs_t.numel(),
             pairs_t.data_ptr(), n_pairs_t.data_ptr()))
 
+    def dedup_probe_dev(self, bytes_t, off_t, cols, n_rows, n_rows_t, dup_t):
+        """swgpu_dedup_probe_dev: per decoded row 0 = new alternate id (or none), 1 = seen before, 2 = ask the store"""
+        self._check(self.lib.swgpu_dedup_probe_dev(self.h, bytes_t.data_ptr(), off_t.data_ptr(), cols.meta.data_ptr(),
+                                                   cols.alternate_id_span.data_ptr(), int(n_rows),
+                                                   n_rows_t.data_ptr() if n_rows_t is not None else None, dup_t.data_ptr()))
+
+    def dedup_size(self) -> int:
+        v = C.c_uint64()
+        self._check(self.lib.swgpu_dedup_size(self.h, C.byref(v)))
+        return int(v.value)
+
+    def dedup_clear(self):
+        self._check(self.lib.swgpu_dedup_clear(self.h))
+
+    def dedup_reserve(self, max_ids: int):
+        self._check(self.lib.swgpu_dedup_reserve(self.h, int(max_ids)))
+
     def encode_inbound_dev(self, fmt, bytes_t, off_t, cols, n_rows, n_rows_t, source_id: bytes, now_ms, out_t, out_off_t,
                            enc_status_t, out_bytes_t):
         """swgpu_encode_inbound_dev: the GInboundEventPayload bytes of every decoded row, back to back in `out_t`"""

@@ -1,4 +1,6 @@
 // ctx.cu — context lifetime, buffers, pinned staging, host-side Kafka partition helper.
+#include <utility>
+
 #include "swgpu_common.cuh"
 
 static thread_local std::string g_create_err;
@@ -125,6 +127,8 @@ extern "C" void swgpu_destroy(swgpu_ctx *ctx) {
     if (ctx->scratch) cudaFree(ctx->scratch);
     sw_pipeline_free(ctx);
     sw_zone_free(ctx);
+    sw_state_free(ctx);
+    std::swap(ctx->state, ctx->dedup_state);  // the alternate-id set is a table of the same kind
     sw_state_free(ctx);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;

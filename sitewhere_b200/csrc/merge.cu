@@ -811,3 +811,123 @@ extern "C" int32_t swgpu_state_restore(swgpu_ctx *ctx, const swgpu_state_rows *i
     }
     return rc;
 }
+
+// ---- alternate-id set --------------------------------------------------------------------
+// AlternateIdDeduplicator.isDuplicate (service-event-sources/.../deduplicator/AlternateIdDeduplicator.java:42-57) asks
+// the event store, per decoded request that carries an alternateId, whether an event with that id exists.  Here the
+// context keeps the set of alternate ids it has been shown, in a second table of the device-state kind (key = the id's
+// bytes, kind byte 0x7e, no name; `best` = a sequence number that DEcreases with arrival, so that the maximum is the
+// first arrival).  Two passes of the same kernel over the rows: the first inserts / raises, the second reads who won.
+#define DD_KIND 0x7eu
+#define DD_SEQ_TOP (1ull << 62)
+struct DdArgs {
+    MgTable t;
+    const uint8_t *bytes;
+    const uint64_t *rec_off, *meta, *span;
+    uint32_t n;
+    const uint32_t *n_dev;
+    uint64_t first_row;  // rows probed before this call
+    uint8_t *dup;
+};
+struct DdKey {  // the id's bytes as key words
+    const uint8_t *p;
+    uint32_t len;
+    __device__ __forceinline__ uint64_t word(uint32_t i) const { return mg_payload_word(p + 8 * (i - 1), min(8u, len - 8 * (i - 1))); }
+};
+template <int PASS>
+__global__ void __launch_bounds__(MG_THREADS) dedup_kernel(DdArgs a) {
+    __shared__ MgLocalCnt s_cnt[MG_THREADS / 32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) s_cnt[warp].keys = s_cnt[warp].bytes = 0;
+    __syncwarp();
+    const uint32_t n_live = a.n_dev ? min(__ldg(a.n_dev), a.n) : a.n;
+    const uint32_t r = blockIdx.x * MG_THREADS + threadIdx.x;
+    if (r < n_live) {
+        const uint64_t m = __ldg(a.meta + r);
+        const uint32_t fl = SWGPU_META_FLAGS(m);
+        uint32_t verdict = SWGPU_DEDUP_NEW;
+        if (fl & SWGPU_F_HAS_ALT_ID) {
+            const uint64_t sp = __ldg(a.span + r);
+            const uint32_t len = SWGPU_SPAN_LEN(sp);
+            if ((fl & (SWGPU_F_STR_ESCAPED | SWGPU_F_NAME_COERCED)) || len > SWGPU_DEDUP_MAX_ID_BYTES) {
+                // the id's characters are not the span's bytes, or the id does not fit a slot (the set keeps no arena:
+                // a probe is asynchronous and cannot grow one): the store decides
+                verdict = SWGPU_DEDUP_ASK;
+            } else {
+                const uint8_t *id = a.bytes + __ldg(a.rec_off + SWGPU_META_REC(m)) + SWGPU_SPAN_OFF(sp);
+                DdKey key{id, len};
+                const uint64_t ih = sw_hash64(GmemBytes{id}, 0, len);
+                const uint64_t seq1 = DD_SEQ_TOP - (a.first_row + r);
+                const unsigned long long old =
+                    mg_upsert_one<true>(a.t, &s_cnt[warp], mg_mix(ih, 0ull, DD_KIND), len, 0u, DD_KIND, key, seq1, 0ull, 0ull, 0ull, 0ull);
+                // second pass: `old` is the final maximum = the first arrival of this id
+                verdict = old == MG_NOT_STORED ? SWGPU_DEDUP_ASK : (old > seq1 ? SWGPU_DEDUP_SEEN : SWGPU_DEDUP_NEW);
+            }
+        }
+        if (PASS == 2) a.dup[r] = (uint8_t)verdict;
+    }
+    __syncwarp();
+    if (lane == 0) mg_flush_counts(a.t, &s_cnt[warp]);
+}
+
+struct DdSwap {  // the state functions work on ctx->state: point it at the set for the duration of a call
+    swgpu_ctx *c;
+    explicit DdSwap(swgpu_ctx *ctx) : c(ctx) { std::swap(c->state, c->dedup_state); }
+    ~DdSwap() { std::swap(c->state, c->dedup_state); }
+};
+
+extern "C" int32_t swgpu_dedup_probe_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, const uint64_t *meta,
+                                         const uint64_t *alternate_id_span, uint32_t n_rows, const uint32_t *n_rows_dev,
+                                         uint8_t *dup) {
+    if (!ctx) return SWGPU_E_INVALID;
+    if (n_rows == 0) return SWGPU_OK;
+    if (!bytes || !rec_off || !meta || !alternate_id_span || !dup) {
+        SW_SET_ERR(ctx, "swgpu_dedup_probe_dev: NULL argument");
+        return SWGPU_E_INVALID;
+    }
+    DdSwap swap(ctx);
+    DdArgs a;
+    if (int rc = sw_state_prepare(ctx, n_rows, n_rows, 0, &a.t)) return rc;
+    a.t.presence_now1 = 0;
+    a.bytes = bytes;
+    a.rec_off = rec_off;
+    a.meta = meta;
+    a.span = alternate_id_span;
+    a.n = n_rows;
+    a.n_dev = n_rows_dev;
+    a.first_row = ctx->dedup_rows;
+    a.dup = dup;
+    ctx->dedup_rows += n_rows;
+    const unsigned nb = (n_rows + MG_THREADS - 1) / MG_THREADS;
+    dedup_kernel<1><<<nb, MG_THREADS, 0, ctx->stream>>>(a);
+    SW_CUDA(ctx, cudaGetLastError());
+    dedup_kernel<2><<<nb, MG_THREADS, 0, ctx->stream>>>(a);
+    SW_CUDA(ctx, cudaGetLastError());
+    return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_dedup_reserve(swgpu_ctx *ctx, uint64_t max_ids) {
+    if (!ctx) return SWGPU_E_INVALID;
+    DdSwap swap(ctx);
+    return mg_reserve(ctx, max_ids, 0);
+}
+
+extern "C" int32_t swgpu_dedup_size(swgpu_ctx *ctx, uint64_t *n_ids) {
+    if (!ctx || !n_ids) return SWGPU_E_INVALID;
+    *n_ids = 0;
+    DdSwap swap(ctx);
+    MgState *st = (MgState *)ctx->state;
+    if (!st || !st->ctr) return SWGPU_OK;
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    MgCounters c;
+    if (int rc = mg_read_counters(ctx, st, &c)) return rc;
+    *n_ids = c.n_keys;
+    return SWGPU_OK;
+}
+
+extern "C" int32_t swgpu_dedup_clear(swgpu_ctx *ctx) {
+    if (!ctx) return SWGPU_E_INVALID;
+    DdSwap swap(ctx);
+    ctx->dedup_rows = 0;
+    return swgpu_state_clear(ctx);
+}

@@ -140,10 +140,12 @@ __device__ __forceinline__ void mg_flush_counts(const MgTable &t, MgLocalCnt *lo
 }
 // One upsert.  DEVICE = true: the device's presence row (see mg_upsert): every writer stores the same values, so no
 // fix-up, and a row that finds the batch's timestamp already there has nothing to do.
+// Returns the key's `best` as it was before this row (0 for a new key), MG_NOT_STORED when the row found no room.
+#define MG_NOT_STORED (~0ull)
 template <bool DEVICE, typename KeyRd>
-__device__ __forceinline__ void mg_upsert_one(const MgTable &t, MgLocalCnt *local, uint64_t h, uint32_t tl, uint32_t nl,
-                                              uint32_t kindbyte, const KeyRd &key, uint64_t seq1, uint64_t id_hi, uint64_t id_lo,
-                                              uint64_t date, uint64_t value) {
+__device__ __forceinline__ unsigned long long mg_upsert_one(const MgTable &t, MgLocalCnt *local, uint64_t h, uint32_t tl,
+                                                            uint32_t nl, uint32_t kindbyte, const KeyRd &key, uint64_t seq1,
+                                                            uint64_t id_hi, uint64_t id_lo, uint64_t date, uint64_t value) {
     const uint32_t nw = mg_key_words(tl, nl);
     const bool inl = nw <= MG_KEY_INLINE_WORDS;
     const uint64_t hdr = mg_key_hdr(tl, nl, kindbyte) | (inl ? 0ull : MG_HDR_LONG);
@@ -243,12 +245,12 @@ __device__ __forceinline__ void mg_upsert_one(const MgTable &t, MgLocalCnt *loca
     }
     if (!found) {
         if (!dropped) atomicAdd(&t.ctr->table_full, 1ull);  // every slot probed
-        return;
+        return MG_NOT_STORED;
     }
     uint64_t *w = t.slots[s].w;
     const unsigned long long old = atomicMax((unsigned long long *)(w + MG_W_BEST), (unsigned long long)seq1);
-    if (old > seq1) return;                // a newer event is already there
-    if (DEVICE && old == seq1) return;     // the device row was touched by another row of this batch already
+    if (old > seq1) return old;                // a newer event is already there
+    if (DEVICE && old == seq1) return old;     // the device row was touched by another row of this batch already
     mg_store_payload(w, id_hi, id_lo, date, value);
     if (!DEVICE && old > t.seq_floor && old != seq1) {  // the previous value was set by an older row of this launch
         const unsigned long long k = atomicAdd(&t.ctr->n_fix, 1ull);
@@ -264,6 +266,7 @@ __device__ __forceinline__ void mg_upsert_one(const MgTable &t, MgLocalCnt *loca
         } else
             atomicAdd(&t.ctr->fix_overflow, 1ull);
     }
+    return old;
 }
 // the device row of a merged event, out of line: the hot path's registers are not shared with it
 template <typename KeyRd>

@@ -45,6 +45,8 @@ struct swgpu_ctx {
 
     // device state (merge.cu)
     void *state = nullptr;
+    void *dedup_state = nullptr;  // a second table of the same kind: the alternate ids seen (swgpu_dedup_probe_dev)
+    uint64_t dedup_rows = 0;      // rows probed so far: earlier rows carry larger sequence numbers
     // chunked host-buffer pipeline (pipeline.cu)
     void *pipeline = nullptr;
 
