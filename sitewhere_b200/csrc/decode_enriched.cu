@@ -48,6 +48,7 @@ struct EnArgs {
     const uint32_t *row_base;
     uint32_t *row_next;
     uint32_t *not_dense;
+    uint32_t force_ordered;  // small batches: only the ordered pass is launched and it decodes the batch
     MgTable mt;  // fused decode + merge
     uint64_t seq_base;
     uint32_t fast;      // option "enriched.fast_path": the forward-pass kernel ran first, this pass takes what it left
@@ -925,7 +926,7 @@ __global__ void __launch_bounds__(EN_THREADS) enriched_decode_kernel(EnArgs a) {
             en_decode_tile<2>(a, ntiles - 1 - t, smem, s_warp, s_cnt);  // newest records first
         return;
     }
-    if (__ldg(a.not_dense) == 0) return;
+    if (!a.force_ordered && __ldg(a.not_dense) == 0) return;
     for (;;) {
         if (threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u);
         __syncthreads();
@@ -955,7 +956,7 @@ static int en_attr(swgpu_ctx *ctx) {
 
 int sw_decode_enriched_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
                               const swgpu_decoded_cols *out, const swgpu_event_ids *ids, uint8_t *status, uint32_t *first_row,
-                              uint32_t *out_rows_dev, uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next) {
+                              uint32_t *out_rows_dev, uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next, bool small) {
     if (!ctx) return SWGPU_E_INVALID;
     if (!out || !out->meta || !out->token_hash || !out->name_hash || !out->event_date || !out->v0 || !out->v1 ||
         !out->v2 || !out->token_span || !out->name_span) {
@@ -979,10 +980,13 @@ int sw_decode_enriched_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64
     }
     const uint32_t ntiles = (n + EN_THREADS - 1) / EN_THREADS;
     const size_t sbytes = SW_SCRATCH_HDR + (size_t)ntiles * 8;
-    if (int rc = sw_ensure_scratch(ctx, sbytes)) return rc;
-    SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, sbytes, ctx->stream));
+    if (!small) {  // (small: the caller has sized and cleared the scratch; see sw_decode_pb_launch)
+        if (int rc = sw_ensure_scratch(ctx, sbytes)) return rc;
+        SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, sbytes, ctx->stream));
+    }
     EnArgs a;
     memset(&a, 0, sizeof a);
+    a.force_ordered = small ? 1u : 0u;
     a.bytes = bytes;
     a.rec_off = rec_off;
     a.n = n;
@@ -1001,6 +1005,11 @@ int sw_decode_enriched_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64
     if (int rc = en_attr(ctx)) return rc;
     const int smem = EN_WARPS * (EN_WSTAGE + 32);
     const uint32_t nredo = ntiles < (uint32_t)ctx->sm_count * 4u ? ntiles : (uint32_t)ctx->sm_count * 4u;
+    if (small) {
+        enriched_decode_kernel<1><<<nredo, EN_THREADS, smem, ctx->stream>>>(a);  // the ordered pass decodes the batch
+        SW_CUDA(ctx, cudaGetLastError());
+        return SWGPU_OK;
+    }
     a.fast = ctx->opt_enriched_fast;
     a.pending = (uint32_t *)ctx->scratch + 3;
     if (a.fast) {
@@ -1046,7 +1055,7 @@ extern "C" int32_t swgpu_decode_enriched_dev(swgpu_ctx *ctx, const uint8_t *byte
                                              uint32_t max_rows, const swgpu_decoded_cols *out, const swgpu_event_ids *ids,
                                              uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev) {
     return sw_decode_enriched_launch(ctx, bytes, rec_off, n, max_rows, out, ids, status, first_row, out_rows_dev, 0, nullptr,
-                                     nullptr);
+                                     nullptr, false);
 }
 
 // host-pointer entry point: stage in, decode, stage out

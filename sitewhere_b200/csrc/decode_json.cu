@@ -39,6 +39,7 @@ struct JsArgs {
     const uint32_t *row_base;
     uint32_t *row_next;
     uint32_t *not_dense;
+    uint32_t force_ordered;  // small batches: only the ordered pass is launched and it decodes the batch
     // fused decode + merge (json_decode_merge_kernel): the state table, per-RECORD event ids, sequence base
     MgTable mt;
     const uint64_t *id_hi, *id_lo;
@@ -1484,7 +1485,7 @@ __global__ void __launch_bounds__(JS_THREADS) json_decode_kernel(JsArgs a) {
             json_decode_tile<true>(a, tile, smem, s_warp);
         return;
     }
-    if (__ldg(a.not_dense) == 0) return;
+    if (!a.force_ordered && __ldg(a.not_dense) == 0) return;
     const uint32_t ntiles = (uint32_t)(((uint64_t)a.n + JS_THREADS - 1) / JS_THREADS);
     for (;;) {
         if (threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u);
@@ -1602,7 +1603,7 @@ int sw_stage_decode(swgpu_ctx *ctx, bool json, const uint8_t *bytes, const uint6
 
 int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
                           const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev,
-                          uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next) {
+                          uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next, bool small) {
     if (!ctx) return SWGPU_E_INVALID;
     if (!out || !out->meta || !out->token_hash || !out->name_hash || !out->event_date || !out->v0 || !out->v1 ||
         !out->v2 || !out->token_span || !out->name_span) {
@@ -1621,9 +1622,12 @@ int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *
     }
     const uint32_t ntiles = (n + JS_THREADS - 1) / JS_THREADS;
     const size_t sbytes = SW_SCRATCH_HDR + (size_t)ntiles * 8;  // one scan state per tile
-    if (int rc = sw_ensure_scratch(ctx, sbytes)) return rc;
-    SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, sbytes, ctx->stream));
+    if (!small) {  // (small: the caller has sized and cleared the scratch; see sw_decode_pb_launch)
+        if (int rc = sw_ensure_scratch(ctx, sbytes)) return rc;
+        SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, sbytes, ctx->stream));
+    }
     JsArgs a;
+    a.force_ordered = small ? 1u : 0u;
     a.bytes = bytes;
     a.rec_off = rec_off;
     a.n = n;
@@ -1655,13 +1659,18 @@ int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *
             done[d] = true;
         }
     }
+    const uint32_t nredo = ntiles < (uint32_t)ctx->sm_count * 4u ? ntiles : (uint32_t)ctx->sm_count * 4u;
+    if (small) {
+        json_decode_kernel<false><<<nredo, JS_THREADS, smem, ctx->stream>>>(a);  // the ordered pass decodes the batch
+        SW_CUDA(ctx, cudaGetLastError());
+        return SWGPU_OK;
+    }
     if (a.fast) {
         // one warp per CTA: a CTA's shared memory goes back the moment its 32 records are done (measured: 27 resident
         // warps per SM against 17 with four-warp CTAs, 0.114 -> 0.105 ms per 1 M records)
         json_template_kernel<<<(n + 31) / 32, 32, JS_WSTAGE + JS_SLACK, ctx->stream>>>(a);  // the serialiser's layout
         SW_CUDA(ctx, cudaGetLastError());
     }
-    const uint32_t nredo = ntiles < (uint32_t)ctx->sm_count * 4u ? ntiles : (uint32_t)ctx->sm_count * 4u;
     // after the template pass the dense pass usually has little or nothing to do: a few CTAs per SM walk the tiles
     json_decode_kernel<true><<<a.fast ? nredo : ntiles, JS_THREADS, smem, ctx->stream>>>(a);  // optimistic: rows = records
     SW_CUDA(ctx, cudaGetLastError());
@@ -1688,7 +1697,7 @@ extern "C" int32_t swgpu_decode_json_dev(swgpu_ctx *ctx, const uint8_t *bytes, c
                                          uint32_t max_rows, const swgpu_decoded_cols *out, uint8_t *status,
                                          uint32_t *first_row, uint32_t *out_rows_dev) {
     return sw_decode_json_launch(ctx, bytes, rec_off, n, max_rows, out, status, first_row, out_rows_dev, 0, nullptr,
-                                 nullptr);
+                                 nullptr, false);
 }
 
 extern "C" int32_t swgpu_decode_json(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,

@@ -35,6 +35,7 @@ struct PbArgs {
     const uint32_t *row_base;
     uint32_t *row_next;
     uint32_t *not_dense;  // raised by the dense pass when some record does not yield exactly one row
+    uint32_t force_ordered;  // small batches: no dense pass, the ordered pass decodes the batch (one launch)
     // fused decode + merge (pb_decode_dense_kernel<true>): the state table, per-RECORD event ids, sequence base
     MgTable mt;
     const uint64_t *id_hi, *id_lo;
@@ -397,7 +398,7 @@ __global__ void __launch_bounds__(PB_THREADS) pb_decode_ordered_kernel(PbArgs a)
     extern __shared__ __align__(16) uint8_t smem[];  // PB_WARPS * (PB_WSTAGE + 32)
     __shared__ uint64_t s_warp[PB_THREADS / 32 + 2];
     __shared__ uint32_t s_tile;
-    if (__ldg(a.not_dense) == 0) return;  // the dense pass was exact: nothing to redo
+    if (!a.force_ordered && __ldg(a.not_dense) == 0) return;  // the dense pass was exact: nothing to redo
     const uint32_t ntiles = (uint32_t)(((uint64_t)a.n + PB_THREADS - 1) / PB_THREADS);
     for (;;) {
         if (threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u);
@@ -597,9 +598,11 @@ static int check_cols(swgpu_ctx *ctx, const swgpu_decoded_cols *c) {
     return SWGPU_OK;
 }
 
+// small = true (batches of a few thousand records, where launches are what costs): the caller has sized and cleared the
+// scratch (SW_SCRATCH_HDR + one word per 256 records); only the ordered pass is launched and it decodes the batch.
 int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
                         const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev,
-                        uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next) {
+                        uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next, bool small) {
     if (!ctx) return SWGPU_E_INVALID;
     if (int rc = check_cols(ctx, out)) return rc;
     if (!rec_off || !first_row || !out_rows_dev || (n && !status)) {
@@ -614,9 +617,12 @@ int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
     }
     const uint32_t ntiles = (n + PB_THREADS - 1) / PB_THREADS;             // CTAs
     const size_t sbytes = SW_SCRATCH_HDR + (size_t)ntiles * 8;              // one scan state per tile
-    if (int rc = sw_ensure_scratch(ctx, sbytes)) return rc;
-    SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, sbytes, ctx->stream));
+    if (!small) {
+        if (int rc = sw_ensure_scratch(ctx, sbytes)) return rc;
+        SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, sbytes, ctx->stream));
+    }
     PbArgs a;
+    a.force_ordered = small ? 1u : 0u;
     a.bytes = bytes;
     a.rec_off = rec_off;
     a.n = n;
@@ -647,7 +653,7 @@ int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *re
             done[d] = true;
         }
     }
-    {
+    if (!small) {
         // optimistic: rows = records.  Pipelined kernel: PD_TILES warp tiles per warp.
         const int dsmem = PB_WARPS * 2 * (PD_STAGE + 32);
         const uint32_t nwt = (n + 31u) / 32u;
@@ -698,7 +704,7 @@ extern "C" int32_t swgpu_decode_pb_dev(swgpu_ctx *ctx, const uint8_t *bytes, con
                                        uint32_t n, uint32_t max_rows, const swgpu_decoded_cols *out,
                                        uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev) {
     return sw_decode_pb_launch(ctx, bytes, rec_off, n, max_rows, out, status, first_row, out_rows_dev, 0, nullptr,
-                               nullptr);
+                               nullptr, false);
 }
 
 // ---- host-pointer entry point: stage in, decode, stage out ------------------------------------------

@@ -17,34 +17,56 @@
 
 int sw_decode_pb_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
                         const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev,
-                        uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next);
+                        uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next, bool small);
 int sw_decode_json_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
                           const swgpu_decoded_cols *out, uint8_t *status, uint32_t *first_row, uint32_t *out_rows_dev,
-                          uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next);
+                          uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next, bool small);
 int sw_decode_enriched_launch(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n, uint32_t max_rows,
                               const swgpu_decoded_cols *out, const swgpu_event_ids *ids, uint8_t *status, uint32_t *first_row,
-                              uint32_t *out_rows_dev, uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next);
+                              uint32_t *out_rows_dev, uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next,
+                              bool small);
 int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta, uint32_t n,
                    const uint32_t *n_rows_dev, uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev,
                    const uint32_t *row_base);
+int sw_zone_single_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta, uint32_t n,
+                          const uint32_t *n_rows_dev, uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev,
+                          void *scratch);
+
+#define PL_SMALL_MAX 16384u  // records: up to here a batch takes the few-launch path below
+#define PL_SMALL_MAX_ROWS 65536u
 
 // decode + zone test of one batch or chunk on the context's stream: decode, then test the decoded columns.  (Testing
 // a location inside the protobuf decode kernel, while its row is in registers, was built and measured: 0.71 ms per
 // 10 M locations against 0.57 for the two kernels — both are latency-bound and the fused kernel has a third of the
 // zone kernel's resident warps)
+// A small batch is bound by launches, not by bytes (a 64 KB poll: eight stream operations of 3-5 us each): it takes
+// THREE — one clear of a scratch that serves both kernels, the decoder's ordered pass alone (exact placement by
+// look-back; with a few dozen tiles nobody waits long), and the single-launch zone kernel.
 static int pl_decode_zone(swgpu_ctx *ctx, int32_t format, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,
                           uint32_t rows_cap, const swgpu_decoded_cols *d, uint8_t *status, uint32_t *first_row,
                           uint32_t *d_rows, uint32_t rec_base, const uint32_t *row_base, uint32_t *row_next,
                           uint64_t pairs_cap, uint64_t *pairs, uint64_t *d_pairs_n) {
+    const bool small = n != 0 && n <= PL_SMALL_MAX && rows_cap <= PL_SMALL_MAX_ROWS && !rec_base && !row_base && !row_next &&
+                       !ctx->opt_zone_stats;
+    size_t dec_bytes = 0;
+    if (small) {
+        dec_bytes = (SW_SCRATCH_HDR + ((size_t)n / 128 + 2) * 8 + 255) / 256 * 256;
+        const size_t zone_bytes = SW_SCRATCH_HDR + ((size_t)rows_cap / 256 + 2) * 8;
+        if (int rc = sw_ensure_scratch(ctx, dec_bytes + zone_bytes)) return rc;
+        SW_CUDA(ctx, cudaMemsetAsync(ctx->scratch, 0, dec_bytes + zone_bytes, ctx->stream));
+    }
     int rc = format == SWGPU_FMT_ENRICHED
                  ? sw_decode_enriched_launch(ctx, bytes, rec_off, n, rows_cap, d, nullptr, status, first_row, d_rows, rec_base,
-                                             row_base, row_next)
+                                             row_base, row_next, small)
              : format == SWGPU_FMT_JSON
                  ? sw_decode_json_launch(ctx, bytes, rec_off, n, rows_cap, d, status, first_row, d_rows, rec_base, row_base,
-                                         row_next)
+                                         row_next, small)
                  : sw_decode_pb_launch(ctx, bytes, rec_off, n, rows_cap, d, status, first_row, d_rows, rec_base, row_base,
-                                       row_next);
+                                       row_next, small);
     if (rc) return rc;
+    if (small)
+        return sw_zone_single_launch(ctx, d->v1, d->v0, d->meta, rows_cap, d_rows, pairs_cap, pairs, d_pairs_n,
+                                     (uint8_t *)ctx->scratch + dec_bytes);
     return sw_zone_launch(ctx, d->v1, d->v0, d->meta, rows_cap, d_rows, pairs_cap, pairs, d_pairs_n, row_base);
 }
 
@@ -183,7 +205,6 @@ void sw_pipeline_free(swgpu_ctx *ctx) {
 // (counts, first_row, status, all columns, alert pairs: laid out back to back on the device), one stream
 // synchronise, and the results are copied out to the caller's arrays.  Returns 1 when the batch did not fit
 // the block's row / alert capacity (fan-out, many Outside-condition alerts): the caller then takes the ring.
-#define PL_SMALL_MAX 16384u
 #define PL_ALIGN(x) (((x) + 255) / 256 * 256)
 
 static int pl_small(swgpu_ctx *ctx, Pipeline *p, int32_t format, const uint8_t *bytes, const uint64_t *rec_off, uint32_t n,

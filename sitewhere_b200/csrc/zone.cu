@@ -760,6 +760,25 @@ int sw_zone_run(swgpu_ctx *ctx, const SwZonePlan &pl) {
     return SWGPU_OK;
 }
 
+// Single-launch form for small batches (launches are what costs there): zone_test_kernel with in-kernel ordered
+// placement; `scratch` = SW_SCRATCH_HDR + 8 bytes per 256 locations of device memory the caller has cleared.
+int sw_zone_single_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta, uint32_t n,
+                          const uint32_t *n_rows_dev, uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev,
+                          void *scratch) {
+    SwZonePlan pl;
+    if (int rc = sw_zone_plan(ctx, lon, lat, meta, 0, n_rows_dev, max_pairs, pairs, n_pairs_dev, nullptr, &pl)) return rc;
+    if (n == 0) {
+        SW_CUDA(ctx, cudaMemsetAsync(n_pairs_dev, 0, sizeof(uint64_t), ctx->stream));
+        return SWGPU_OK;
+    }
+    pl.a.n = n;
+    pl.a.ticket = (uint32_t *)scratch;
+    pl.a.tile_state = (uint64_t *)((uint8_t *)scratch + SW_SCRATCH_HDR);
+    zone_test_kernel<<<(n + ZN_THREADS - 1) / ZN_THREADS, ZN_THREADS, 0, ctx->stream>>>(pl.a);
+    SW_CUDA(ctx, cudaGetLastError());
+    return SWGPU_OK;
+}
+
 int sw_zone_launch(swgpu_ctx *ctx, const double *lon, const double *lat, const uint64_t *meta, uint32_t n,
                    const uint32_t *n_rows_dev, uint64_t max_pairs, uint64_t *pairs, uint64_t *n_pairs_dev,
                    const uint32_t *row_base) {
