@@ -19,7 +19,8 @@
 #include "tile_scan.cuh"
 
 #define EC_THREADS 256
-#define EC_STAGE (48 * 1024)  // a tile whose records fit is assembled in shared memory and copied out coalesced
+#define EC_STAGE (32 * 1024)  // a tile whose records fit (128 bytes per row on average) is assembled in shared memory and
+                              // copied out coalesced; 32 KiB keeps seven CTAs on an SM
 #define EC_MAX_SOURCE 256
 
 struct EcArgs {
@@ -74,6 +75,24 @@ struct EcWords {
     }
 };
 __device__ __forceinline__ bool ec_ascii(const uint8_t *s, uint32_t n) {
+    if (n <= 28) {  // all the words of a short string at once (one round trip); bytes outside the string are masked off
+        const uintptr_t a = (uintptr_t)s;
+        const uint32_t *w = (const uint32_t *)(a & ~(uintptr_t)3);
+        const uint32_t lead = (uint32_t)(a & 3), nw = (lead + n + 3) >> 2;
+        uint32_t acc = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            if ((uint32_t)k < nw) {
+                uint32_t v = __ldg(w + k);
+                const uint32_t lo = 4 * k, first = lead > lo ? lead - lo : 0u;              // string bytes of this word:
+                const uint32_t last = min(4u, lead + n - lo);                               // [first, last)
+                if (first) v &= ~((1u << (8 * first)) - 1u);
+                if (last < 4) v &= (1u << (8 * last)) - 1u;
+                acc |= v;
+            }
+        }
+        return (acc & 0x80808080u) == 0;
+    }
     EcWords ws;
     ws.open(s, n);
     uint32_t acc = 0;
@@ -170,6 +189,30 @@ struct EcWr {  // byte writer (generic address: shared-memory stage or global me
         if (!len) return;
         b(tag);
         varint(len);
+        if (len <= 28) {
+            // the usual string (a 21-byte token, a short name): all of its aligned words are asked for at once, so that
+            // the row waits for one round trip, not for one per word
+            const uintptr_t a = (uintptr_t)s;
+            const uint32_t *w = (const uint32_t *)(a & ~(uintptr_t)3);
+            const uint32_t sh = (uint32_t)(a & 3) * 8, nw = ((uint32_t)(a & 3) + len + 3) >> 2;
+            uint32_t wb[9];
+#pragma unroll
+            for (int k = 0; k < 8; k++) wb[k] = (uint32_t)k < nw ? __ldg(w + k) : 0u;
+            wb[8] = 0;
+#pragma unroll
+            for (int k = 0; k < 7; k++) {
+                if ((uint32_t)(4 * k) < len) {
+                    const uint32_t v = __funnelshift_r(wb[k], wb[k + 1], sh);
+                    const uint32_t m = len - 4 * k;  // bytes of this word that belong to the string
+                    p[4 * k] = (uint8_t)v;
+                    if (m > 1) p[4 * k + 1] = (uint8_t)(v >> 8);
+                    if (m > 2) p[4 * k + 2] = (uint8_t)(v >> 16);
+                    if (m > 3) p[4 * k + 3] = (uint8_t)(v >> 24);
+                }
+            }
+            p += len;
+            return;
+        }
         EcWords ws;
         ws.open(s, len);
         uint32_t i = 0;
