@@ -284,6 +284,10 @@ int32_t swgpu_json_stats(swgpu_ctx *ctx, uint64_t out[2]);
 int32_t swgpu_dedup_probe_dev(swgpu_ctx *ctx, const uint8_t *bytes, const uint64_t *rec_off, const uint64_t *meta,
                               const uint64_t *alternate_id_span, uint32_t n_rows, const uint32_t *n_rows_dev,
                               uint8_t *dup);
+/* host form: the alternate ids back to back (id_off[n + 1]), one per row; waits for the result.  This is what a
+ * deduplicator bean calls per request or per micro-batch (IDeviceEventDeduplicator.isDuplicate,
+ * ES/spi/IDeviceEventDeduplicator.java:29, called at ES/InboundEventSource.java:226-227).                   */
+int32_t swgpu_dedup_probe(swgpu_ctx *ctx, const uint8_t *ids, const uint64_t *id_off, uint32_t n, uint8_t *dup);
 int32_t swgpu_dedup_reserve(swgpu_ctx *ctx, uint64_t max_ids);
 int32_t swgpu_dedup_size(swgpu_ctx *ctx, uint64_t *n_ids);
 int32_t swgpu_dedup_clear(swgpu_ctx *ctx);

@@ -78,6 +78,8 @@ public final class SwGpu {
     /** AlternateIdDeduplicator.isDuplicate as a set probe: dup[row] = 0 new, 1 seen, 2 ask the store */
     static final MethodHandle DEDUP_PROBE_DEV = h("swgpu_dedup_probe_dev", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS,
 	    ADDRESS, ADDRESS, ADDRESS, JAVA_INT, ADDRESS, ADDRESS));
+    static final MethodHandle DEDUP_PROBE = h("swgpu_dedup_probe", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
+	    JAVA_INT, ADDRESS));
     static final MethodHandle PARTITION = h("swgpu_partition", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_INT));
 
     /** One native context: one GPU, one calling thread. */

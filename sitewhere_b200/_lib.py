@@ -88,6 +88,7 @@ SIGNATURES = {
     "swgpu_json_stats": (_I32, [_P, _P]),
     "swgpu_decode_zone_test": (_I32, [_P, _I32, _P, _P, _U32, _U32, _COLS, _P, _P, _P, _U64, _P, _P, _U32]),
     "swgpu_dedup_probe_dev": (_I32, [_P, _P, _P, _P, _P, _U32, _P, _P]),
+    "swgpu_dedup_probe": (_I32, [_P, _P, _P, _U32, _P]),
     "swgpu_dedup_reserve": (_I32, [_P, _U64]),
     "swgpu_dedup_size": (_I32, [_P, _P]),
     "swgpu_dedup_clear": (_I32, [_P]),

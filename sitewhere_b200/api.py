@@ -284,6 +284,17 @@ class Context:
                                                    cols.alternate_id_span.data_ptr(), int(n_rows),
                                                    n_rows_t.data_ptr() if n_rows_t is not None else None, dup_t.data_ptr()))
 
+    def dedup_probe(self, ids) -> np.ndarray:
+        """swgpu_dedup_probe: list of alternate ids (bytes) -> uint8 verdicts (0 new, 1 seen, 2 ask the store)"""
+        ids = [bytes(x) for x in ids]
+        n = len(ids)
+        off = np.zeros(n + 1, dtype=np.uint64)
+        np.cumsum([len(x) for x in ids], out=off[1:].view(np.int64)) if n else None
+        data = np.frombuffer(b"".join(ids), dtype=np.uint8).copy() if n and off[-1] else np.zeros(1, np.uint8)
+        dup = np.zeros(max(n, 1), dtype=np.uint8)
+        self._check(self.lib.swgpu_dedup_probe(self.h, data.ctypes.data, off.ctypes.data, n, dup.ctypes.data))
+        return dup[:n]
+
     def dedup_size(self) -> int:
         v = C.c_uint64()
         self._check(self.lib.swgpu_dedup_size(self.h, C.byref(v)))

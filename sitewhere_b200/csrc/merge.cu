@@ -931,3 +931,38 @@ extern "C" int32_t swgpu_dedup_clear(swgpu_ctx *ctx) {
     ctx->dedup_rows = 0;
     return swgpu_state_clear(ctx);
 }
+
+// host form: `ids` = the alternate ids back to back, id_off[n + 1]; every row carries one.  Stages the ids, builds the
+// two columns the device form reads (record index + "has an alternate id", span = the whole record), probes, waits.
+__global__ void dedup_cols_kernel(const uint64_t *id_off, uint32_t n, uint64_t *meta, uint64_t *span) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    meta[i] = ((uint64_t)i << 32) | ((uint64_t)SWGPU_F_HAS_ALT_ID << 8);
+    span[i] = (id_off[i + 1] - id_off[i]) << 32;
+}
+extern "C" int32_t swgpu_dedup_probe(swgpu_ctx *ctx, const uint8_t *ids, const uint64_t *id_off, uint32_t n, uint8_t *dup) {
+    if (!ctx) return SWGPU_E_INVALID;
+    if (n == 0) return SWGPU_OK;
+    if (!id_off || !dup || (id_off[n] && !ids)) {
+        SW_SET_ERR(ctx, "swgpu_dedup_probe: NULL argument");
+        return SWGPU_E_INVALID;
+    }
+    SW_CUDA(ctx, cudaSetDevice(ctx->device));
+    const uint64_t total = id_off[n];
+    if (int rc = sw_ensure(ctx, ctx->d_bytes, total + 64)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_off, (size_t)(n + 1) * 8)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_cols, (size_t)n * 16 + 64)) return rc;
+    if (int rc = sw_ensure(ctx, ctx->d_status, (size_t)n + 16)) return rc;
+    cudaStream_t st = ctx->stream;
+    if (total) SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_bytes.p, ids, total, cudaMemcpyHostToDevice, st));
+    SW_CUDA(ctx, cudaMemcpyAsync(ctx->d_off.p, id_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, st));
+    uint64_t *meta = (uint64_t *)ctx->d_cols.p, *span = meta + n;
+    dedup_cols_kernel<<<(n + 255) / 256, 256, 0, st>>>((const uint64_t *)ctx->d_off.p, n, meta, span);
+    SW_CUDA(ctx, cudaGetLastError());
+    if (int rc = swgpu_dedup_probe_dev(ctx, (const uint8_t *)ctx->d_bytes.p, (const uint64_t *)ctx->d_off.p, meta, span, n, nullptr,
+                                       (uint8_t *)ctx->d_status.p))
+        return rc;
+    SW_CUDA(ctx, cudaMemcpyAsync(dup, ctx->d_status.p, n, cudaMemcpyDeviceToHost, st));
+    SW_CUDA(ctx, cudaStreamSynchronize(st));
+    return SWGPU_OK;
+}

@@ -75,3 +75,12 @@ def test_alternate_id_set_equals_row_order_restatement():
         assert ctx.state_size()[0] == 0
     finally:
         ctx.close()
+
+
+def test_host_form(ctx):
+    ctx.dedup_clear()
+    got = ctx.dedup_probe([b"a", b"b", b"a", b"", b"", b"x" * 72, b"x" * 73, b"b"])
+    assert got.tolist() == [0, 0, 1, 0, 1, 0, 2, 1]
+    assert ctx.dedup_probe([b"b", b"c", b"x" * 72]).tolist() == [1, 0, 1]
+    assert ctx.dedup_size() == 5 and ctx.dedup_probe([]).shape[0] == 0
+    ctx.dedup_clear()
