@@ -49,14 +49,23 @@ while time.time() < t_end:
     assert got.shape[0] == total and np.array_equal(got, want), "zone mismatch round %d seed %d" % (rnd, seed)
     tot["zone"] += n
     # the fused pipeline on a mutated protobuf batch with random chunking
-    recs = F._mutate(rng, pb_base, F.PB_SPECIALS, 20_000, max_mut=1)
+    recs = F._mutate(rng, pb_base, F.PB_SPECIALS, int(rng.choice([700, 5000, 16_384, 20_000])), max_mut=1)   # (small-batch path too)
     data, off = S.pack_records(recs)
-    chunk = int(rng.choice([0, 333, 1000, 4096, 7777]))
+    chunk = int(rng.choice([0, 0, 333, 1000, 4096, 7777]))
     cols, status, first_row, n_rows, pairs = ctx.decode_zone_test("pb", data, off, chunk_records=chunk)
     ocols, ostatus, ofirst, ototal = oracle.decode_pb(data, off)
     assert n_rows == ototal and np.array_equal(status, ostatus) and np.array_equal(first_row, ofirst)
     want, total = oracle.zone_test(*zones, ocols.v1[:ototal], ocols.v0[:ototal], meta=ocols.meta[:ototal])
     assert np.array_equal(pairs, want), "pipeline mismatch round %d seed %d chunk %d" % (rnd, seed, chunk)
+    tot["pipe"] += len(recs)
+    # the same through the small-batch path for JSON (ordered pass alone + single-launch zone kernel)
+    recs = F._mutate(rng, js_base, F.JSON_SPECIALS, int(rng.choice([300, 3000, 12_000])), max_mut=1) + list(js_base[-2:]) * 50
+    data, off = S.pack_records(recs)
+    cols, status, first_row, n_rows, pairs = ctx.decode_zone_test("json", data, off)
+    ocols, ostatus, ofirst, ototal = oracle.decode_json(data, off)
+    assert n_rows == ototal and np.array_equal(status, ostatus) and np.array_equal(first_row, ofirst)
+    want, total = oracle.zone_test(*zones, ocols.v1[:ototal], ocols.v0[:ototal], meta=ocols.meta[:ototal])
+    assert np.array_equal(pairs, want), "small json pipeline mismatch round %d seed %d" % (rnd, seed)
     tot["pipe"] += len(recs)
     # device-state fold: a fresh state every fourth round, hot keys (few devices) or many keys, damaged records
     if rnd % 4 == 0:
