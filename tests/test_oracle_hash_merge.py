@@ -57,3 +57,18 @@ def test_state_fold_matches_python_dict():
         assert snap["value"][i] == v
     # 50 devices x (1 location + 16 names + 8 alert types) is the key-space bound
     assert len(keys) <= 50 * 25
+
+
+def test_alt_id_set_known_answers():
+    """oracle.AltIdSet (the restatement of AlternateIdDeduplicator as a set probe): first arrival is new, every later
+    one is seen, requests without an alternate id are never duplicates, escaped ids are left to the store"""
+    import oracle
+    from sitewhere_b200 import synth as S
+    mk = lambda alt: ('{"deviceToken":"t","type":"DeviceLocation","request":{"latitude":1,"alternateId":%s}}' % alt).encode()
+    recs = [mk('"a"'), mk('"b"'), mk('"a"'), S.json_location("t", "1", "2", "3", 5), mk('"es\\u0063"'), mk('"b"'), mk('""'), mk('""')]
+    data, off = S.pack_records(recs)
+    cols, status, first, total = oracle.decode_json(data, off)
+    assert total == len(recs)
+    st = oracle.AltIdSet()
+    assert st.probe(data, off, cols, total).tolist() == [0, 0, 1, 0, 2, 1, 0, 1]
+    assert st.probe(data, off, cols, total).tolist() == [1, 1, 1, 0, 2, 1, 1, 1]
